@@ -1,0 +1,191 @@
+/*
+ * stepth_cuda.h -- C ABI of libstepth_cuda.so, the B200 (sm_100a) implementation of nikilark/stepth's
+ * depth-from-additional hot path.  This is the drop-in boundary: the patched `stepth` crate (rust/) binds
+ * exactly these symbols through its `stepth-cuda-sys` FFI crate; stepth_b200/ (Python) and include/stepth.hpp
+ * (C++) bind the same symbols.  Plain pointers and sizes only; no exceptions cross the boundary.
+ *
+ * Reference interfaces replaced (file:line into nikilark/stepth):
+ *   src/depth_image.rs:110-134  per-block ring search, `as u8`, global max, normalise, paint, luma, Gaussian resample
+ *   src/helpers.rs:3-54         distance_dot_dot / distance_dot_array (the search itself)
+ *   src/depth_image.rs:225-227  invert_depth
+ *   src/depth_image.rs:162-218  depth_split
+ *   src/depth_image.rs:220-245  select_foreground / slice
+ *   src/mask_image.rs:205-213   MaskImage::apply_mask
+ *   src/operations.rs:3-80      normalize_brightness_{luma16,rgb16}   
+ *
+ * Ownership: the caller owns every buffer; the library borrows pointers for the duration of a call and
+ * never frees or retains them.  Device buffers, pinned staging and streams live in the context.
+ * Threading: one call at a time per context; different contexts may be used from different threads.
+ * All `stepth_cuda_*` host-buffer calls are synchronous (they return after the device->host copies finish),
+ * like the reference.  `stepth_cuda_dev_*` calls take DEVICE pointers and a CUDA stream and only enqueue work.
+ *
+ * There is NO CPU fallback: every entry point fails with STEPTH_ERR_CUDA when no sm_100 device is usable.
+ */
+#ifndef STEPTH_CUDA_H
+#define STEPTH_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- status codes -------------------------------------------------------------------------------------- */
+#define STEPTH_OK 0
+#define STEPTH_ERR_INVALID_ARG 1      /* -> io::Error(InvalidInput)                                           */
+#define STEPTH_ERR_SIZE_MISMATCH 2    /* -> io::Error(InvalidInput, "Sizes don't match")  depth_image.rs:41-48 */
+#define STEPTH_ERR_DIV_BY_ZERO_MAX 3  /* -> panic "attempt to divide by zero"             depth_image.rs:127   */
+#define STEPTH_ERR_TOO_FEW_BLOCKS 4   /* -> panic (par_chunks_mut(0))                     depth_image.rs:111-112 */
+#define STEPTH_ERR_DEGENERATE_DEPTH 5 /* -> panic (step_by(0) / underflow / unwrap(None)) depth_image.rs:212-216 */
+#define STEPTH_ERR_NO_CONVERGENCE 6   /* k-means did not converge (reference: unbounded recursion)             */
+#define STEPTH_ERR_CUDA 100           /* CUDA runtime failure; text in stepth_cuda_last_error()                */
+
+/* ---- flags (stepth_params.flags) ------------------------------------------------------------------------ */
+#define STEPTH_RESAMPLE_OFF 0u        /* skip depth_image.rs:133 (debug / raw distance maps)                   */
+#define STEPTH_RESAMPLE_U8 1u         /* image 0.23.x sampler: u8 intermediate between the two passes (default) */
+#define STEPTH_RESAMPLE_F32 2u        /* 0.24-style f32 intermediate                                           */
+#define STEPTH_RESAMPLE_MASK 3u
+#define STEPTH_FLAG_INVERT (1u << 2)      /* fuse invert_depth                depth_image.rs:225-227 */
+#define STEPTH_FLAG_FOREGROUND (1u << 3)  /* fuse select_foreground -> mask   depth_image.rs:220-245 */
+#define STEPTH_FLAG_APPLY (1u << 4)       /* fuse MaskImage::apply_mask       mask_image.rs:205-213  */
+#define STEPTH_FLAG_PIXELOPPS_SAT (1u << 5) /* PixelOpps = saturating-sub / all-lt instead of abs-diff / all-lt */
+#define STEPTH_FLAG_LITERAL_SEARCH (1u << 6) /* debug: one thread per query walking the reference's probe order */
+
+typedef struct stepth_ctx stepth_ctx;
+
+/* disage::DiscretePixel<[u8;3]> as it crosses the boundary (depth_image.rs:110-121): 20 bytes */
+typedef struct {
+    uint32_t x, y, w, h; /* position.x, position.y, size.width, size.height */
+    uint8_t value[3];    /* block value ([u8;3]) BEFORE it is overwritten by the distance */
+    uint8_t pad;
+} stepth_block;
+
+typedef struct {
+    uint8_t precision[3]; /* depth_precision: [u8;3]             depth_image.rs:79 */
+    uint8_t pad;
+    uint32_t max_rings;   /* `max` of distance_dot_array; the reference hard-codes 255   depth_image.rs:119 */
+    uint32_t flags;
+} stepth_params;
+
+/* ---- context --------------------------------------------------------------------------------------------- */
+int32_t stepth_cuda_device_count(int32_t *count_out);
+int32_t stepth_cuda_ctx_create(int32_t device, stepth_ctx **ctx_out);
+void stepth_cuda_ctx_destroy(stepth_ctx *ctx);
+const char *stepth_cuda_last_error(const stepth_ctx *ctx); /* ctx may be NULL: last create() error */
+const char *stepth_cuda_version(void);
+
+/* ---- the hot path, host buffers (what load_depth_from_additional calls) ---------------------------------- */
+
+/* depth_image.rs:110-134 from a block list (the disage discretiser stays on the host).
+ *   add_rgb   : additional image, RGB8 row-major, wa*ha*3
+ *   blocks    : n_blocks DiscretePixels that tile the w*h main image
+ *   depth_out : w*h Luma8 (the value handed to load_depth, depth_image.rs:135)
+ *   raw_d8_out: optional n_blocks bytes, `d as u8` per block before normalisation
+ * fused tail (flags): rgba_in (w*h*4, required for APPLY), rgba_out (w*h*4), mask_out (w*h), from_to_out[2]. */
+int32_t stepth_cuda_depth_from_blocks(stepth_ctx *ctx, const uint8_t *add_rgb, uint32_t wa, uint32_t ha,
+                                      const stepth_block *blocks, size_t n_blocks, uint32_t w, uint32_t h,
+                                      const stepth_params *params, uint8_t *depth_out, uint8_t *raw_d8_out,
+                                      const uint8_t *rgba_in, uint8_t *rgba_out, uint8_t *mask_out,
+                                      uint8_t *from_to_out);
+
+/* limit case: every main pixel is its own 1x1 block whose value is the pixel (alpha ignored). */
+int32_t stepth_cuda_depth_dense(stepth_ctx *ctx, const uint8_t *main_rgba, uint32_t w, uint32_t h,
+                                const uint8_t *add_rgb, uint32_t wa, uint32_t ha, const stepth_params *params,
+                                uint8_t *depth_out, uint8_t *raw_d8_out, uint8_t *rgba_out, uint8_t *mask_out,
+                                uint8_t *from_to_out);
+
+/* a batch of independent pairs of identical shape, one launch sequence for all of them.
+ * status_out[i] receives the per-pair status (a pair with max == 0 does not fail the others). */
+int32_t stepth_cuda_depth_dense_batch(stepth_ctx *ctx, uint32_t n_pairs, const uint8_t *const *main_rgba,
+                                      uint32_t w, uint32_t h, const uint8_t *const *add_rgb, uint32_t wa,
+                                      uint32_t ha, const stepth_params *params, uint8_t *const *depth_out,
+                                      uint8_t *const *rgba_out, uint8_t *const *mask_out, uint8_t *from_to_out,
+                                      int32_t *status_out);
+
+/* ---- tail operations, host buffers ----------------------------------------------------------------------- */
+int32_t stepth_cuda_invert_depth(stepth_ctx *ctx, uint8_t *depth_inout, size_t n);             /* :225-227 */
+/* ranges_out: 2*256 bytes, (min,max) per cluster; has_values_out = 0 for the zones<2 answer [(None,None)] */
+int32_t stepth_cuda_depth_split(stepth_ctx *ctx, const uint8_t *depth, size_t n, uint8_t zones,
+                                uint8_t *ranges_out, uint32_t *n_out, int32_t *has_values_out); /* :162-218 */
+/* from / to < 0 mean None */
+int32_t stepth_cuda_slice(stepth_ctx *ctx, const uint8_t *depth, size_t n, int32_t from, int32_t to,
+                          uint8_t *mask_out);                                                   /* :229-245 */
+int32_t stepth_cuda_select_foreground(stepth_ctx *ctx, const uint8_t *depth, size_t n, uint8_t *mask_out,
+                                      uint8_t *from_to_out);                                    /* :220-223 */
+int32_t stepth_cuda_apply_mask(stepth_ctx *ctx, uint8_t *rgba_inout, const uint8_t *mask, size_t n); /* mask_image.rs:205-213 */
+
+/* operations.rs:3-36 / 38-80 (n = pixel counts) */
+int32_t stepth_cuda_normalize_brightness_luma16(stepth_ctx *ctx, const uint16_t *img1, size_t n1,
+                                                const uint16_t *img2, size_t n2, double percent, uint16_t *out);
+int32_t stepth_cuda_normalize_brightness_rgb16(stepth_ctx *ctx, const uint16_t *img1, size_t n1,
+                                               const uint16_t *img2, size_t n2, double percent, uint16_t *out);
+
+/* ---- host-side stand-in for disage::open::rgb_discrete (depth_image.rs:104-109; disage source absent) ----- */
+/* kd-splits the main image into blocks ("disc_v0", documented in DESIGN.md as NOT disage).  Returns the number
+ * of blocks, writing at most `cap` of them; call with cap = 0 to size the buffer. */
+size_t stepth_host_discretise_v0(const uint8_t *main_px, uint32_t stride, uint32_t w, uint32_t h,
+                                 const uint8_t precision[3], uint32_t min_splits, uint32_t max_splits,
+                                 stepth_block *blocks_out, size_t cap);
+
+/* ---- device-resident stage API (device pointers; work is enqueued on `stream`, a cudaStream_t) ------------ */
+/* Used by the batch / row-band orchestration (one process per GPU) and by the device-resident benchmark. */
+
+typedef struct {
+    uint32_t n_pairs;  /* images in the batch (contiguous, identical shape)                          */
+    uint32_t w, h;     /* main band: width and rows held on this device                              */
+    uint32_t img_h;    /* rows of the whole main image (== h unless row-banded)                      */
+    uint32_t y0;       /* global row index of band row 0                                             */
+    uint32_t wa, ha;   /* additional sub-image held on this device                                   */
+    uint32_t add_y0;   /* global row index of its row 0                                              */
+    uint32_t add_img_h;/* rows of the whole additional image (for the origin-out-of-bounds rule)     */
+} stepth_dev_shape;
+
+/* K0+K1: ring search for every main pixel of the band.  main_rgba [n,h,w,4], add_rgb [n,ha,wa,3],
+ * d8_out [n,h,w]; max_out [n] u32 receives max(d8) per pair (zeroed by the call). */
+int32_t stepth_cuda_dev_search_dense(stepth_ctx *ctx, void *stream, const stepth_dev_shape *shape,
+                                     const stepth_params *params, const uint8_t *main_rgba,
+                                     const uint8_t *add_rgb, uint8_t *d8_out, uint32_t *max_out);
+
+/* block-list search: blocks [n_blocks] (device), add_rgb [ha,wa,3]; d8_out [n_blocks]; max_out [1] */
+int32_t stepth_cuda_dev_search_blocks(stepth_ctx *ctx, void *stream, const stepth_params *params,
+                                      const uint8_t *add_rgb, uint32_t wa, uint32_t ha,
+                                      const stepth_block *blocks, size_t n_blocks, uint8_t *d8_out,
+                                      uint32_t *max_out);
+
+/* paint: plane_out[h,w] = d8[b] over each block rectangle (DiscreteImage::collect + luma, depth_image.rs:130-132).
+ * The plane holds RAW distances: the normalisation of :125-129 is a per-byte map and is applied by dev_finish. */
+int32_t stepth_cuda_dev_paint_blocks(stepth_ctx *ctx, void *stream, const stepth_block *blocks,
+                                     const uint8_t *d8, size_t n_blocks, uint32_t w, uint32_t h,
+                                     uint8_t *plane_out);
+
+/* K2: normalise by max_in[n] (depth_image.rs:125-129), unit-scale Gaussian (:133), optional invert, histogram.
+ * src [n, src_rows, w] holds global rows [src_y0, src_y0+src_rows); depth_out [n, out_rows, w] receives global
+ * rows [out_y0, out_y0+out_rows); hist_out [n,256] u32 is ACCUMULATED into (zero it first); status_out [n]. */
+int32_t stepth_cuda_dev_finish(stepth_ctx *ctx, void *stream, uint32_t n_pairs, uint32_t w, uint32_t img_h,
+                               const uint8_t *src, uint32_t src_y0, uint32_t src_rows, const uint32_t *max_in,
+                               uint32_t flags, uint8_t *depth_out, uint32_t out_y0, uint32_t out_rows,
+                               uint32_t *hist_out, int32_t *status_out);
+
+/* K3: depth_split(zones) from 256-bin histograms [n,256]; ranges_out [n, 512] bytes, n_out [n], status_out [n] */
+int32_t stepth_cuda_dev_depth_split(stepth_ctx *ctx, void *stream, uint32_t n_pairs, const uint32_t *hist,
+                                    uint8_t zones, uint8_t *ranges_out, uint32_t *n_out, int32_t *status_out);
+
+/* K4: slice + apply_mask.  from_to [n, stride_ft] bytes (device): cluster 0's (min,max).
+ * mask_out [n,px] and/or rgba_out [n,px,4] (rgba_in may equal rgba_out) */
+int32_t stepth_cuda_dev_mask_apply(stepth_ctx *ctx, void *stream, uint32_t n_pairs, size_t px,
+                                   const uint8_t *depth, const uint8_t *from_to, uint32_t stride_ft,
+                                   const int32_t *status_in, const uint8_t *rgba_in, uint8_t *mask_out,
+                                   uint8_t *rgba_out);
+
+/* 256-bin histogram of a device buffer, accumulated into hist_out[256] */
+int32_t stepth_cuda_dev_histogram(stepth_ctx *ctx, void *stream, const uint8_t *data, size_t n,
+                                  uint32_t *hist_out);
+
+/* number of kernel launches issued by this context so far (bench.py's gpu_launches) */
+uint64_t stepth_cuda_launch_count(const stepth_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* STEPTH_CUDA_H */

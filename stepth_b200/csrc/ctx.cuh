@@ -1,0 +1,124 @@
+// ctx.cuh -- the library context: one device, one stream, scratch buffers that grow on demand, the cached
+// Gaussian tap tables and the last error text.  Nothing here is visible through the C ABI except as an
+// opaque `stepth_ctx *`.
+#pragma once
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "finish.cuh"
+
+struct stepth_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    uint64_t launches = 0;
+    int sm_count = 148;
+
+    struct Buf {
+        void *p = nullptr;
+        size_t cap = 0;
+    };
+    // scratch for the host-buffer entry points
+    Buf main_rgba, add_rgb, d8, depth, mask, rgba_out, blocks, plane, small, u16a, u16b, u16o, work;
+    // small per-pair state: [max u32][hist 256 u32][status i32][n_out u32][ranges 512 B] per pair
+    void *h_small = nullptr;  // pinned mirror
+    size_t h_small_cap = 0;
+
+    struct Taps {
+        std::vector<stepth::TapRow> host;
+        stepth::TapRow *dev = nullptr;
+    };
+    std::map<uint32_t, Taps> taps;  // keyed by axis length
+};
+
+namespace stepth {
+
+inline int32_t set_err(stepth_ctx *ctx, int32_t code, const char *fmt, ...) {
+    if (ctx) {
+        char buf[512];
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, sizeof buf, fmt, ap);
+        va_end(ap);
+        ctx->err = buf;
+    }
+    return code;
+}
+
+#define STEPTH_CUDA_TRY(ctx, expr)                                                                          \
+    do {                                                                                                    \
+        cudaError_t e__ = (expr);                                                                           \
+        if (e__ != cudaSuccess)                                                                             \
+            return stepth::set_err((ctx), STEPTH_ERR_CUDA, "%s failed: %s (%s:%d)", #expr,                 \
+                                   cudaGetErrorString(e__), __FILE__, __LINE__);                            \
+    } while (0)
+
+inline int32_t ensure(stepth_ctx *ctx, stepth_ctx::Buf &b, size_t bytes) {
+    if (bytes <= b.cap && b.p) return STEPTH_OK;
+    if (b.p) STEPTH_CUDA_TRY(ctx, cudaFree(b.p));
+    b.p = nullptr;
+    b.cap = 0;
+    size_t want = bytes < 256 ? 256 : bytes;
+    STEPTH_CUDA_TRY(ctx, cudaMalloc(&b.p, want));
+    b.cap = want;
+    return STEPTH_OK;
+}
+
+// image 0.23.14 imageops/sample.rs: gaussian(x, r = 0.5) = 1/(sqrt(2 pi) r) * exp(-x^2 / (2 r^2)), support 3.0.
+// Tap tables for a unit-scale resample along an axis of n samples (see finish.cuh).  Plain f32 arithmetic in
+// the crate's order; this translation unit is compiled with -fmad=false / no fast-math on the host side.
+inline float gaussian_r05(float x) {
+    const float r = 0.5f;
+    float norm = 1.0f / (sqrtf(2.0f * 3.14159265358979323846f) * r);
+    return norm * expf(-(x * x) / (2.0f * (r * r)));
+}
+
+inline void build_taps(uint32_t n, std::vector<TapRow> &out) {
+    out.resize(n);
+    const float ratio = 1.0f, sratio = 1.0f, support = 3.0f * sratio;
+    for (uint32_t o = 0; o < n; ++o) {
+        float in = ((float)o + 0.5f) * ratio;
+        long long left = (long long)floorf(in - support);
+        if (left < 0) left = 0;
+        if (left > (long long)n - 1) left = (long long)n - 1;
+        long long right = (long long)ceilf(in + support);
+        if (right < left + 1) right = left + 1;
+        if (right > (long long)n) right = (long long)n;
+        in = in - 0.5f;
+        TapRow t;
+        memset(&t, 0, sizeof t);
+        t.left = (int32_t)left;
+        float sum = 0.0f;
+        int cnt = 0;
+        for (long long i = left; i < right && cnt < 7; ++i) {
+            volatile float wgt = gaussian_r05(((float)i - in) / sratio);
+            t.w[cnt++] = wgt;
+            sum = sum + wgt;
+        }
+        for (int k = 0; k < cnt; ++k) t.w[k] = t.w[k] / sum;
+        t.cnt = cnt;
+        out[o] = t;
+    }
+}
+
+inline int32_t get_taps(stepth_ctx *ctx, cudaStream_t st, uint32_t n, const TapRow **dev_out) {
+    auto it = ctx->taps.find(n);
+    if (it == ctx->taps.end()) {
+        stepth_ctx::Taps t;
+        build_taps(n, t.host);
+        STEPTH_CUDA_TRY(ctx, cudaMalloc((void **)&t.dev, sizeof(TapRow) * (n ? n : 1)));
+        // synchronous copy: the table is immutable afterwards and shared by every later launch
+        STEPTH_CUDA_TRY(ctx, cudaMemcpy(t.dev, t.host.data(), sizeof(TapRow) * n, cudaMemcpyHostToDevice));
+        it = ctx->taps.emplace(n, std::move(t)).first;
+    }
+    (void)st;
+    *dev_out = it->second.dev;
+    return STEPTH_OK;
+}
+
+}  // namespace stepth

@@ -1,0 +1,114 @@
+"""The C-ABI boundary without a GPU: the library builds for sm_100a, loads, exports every symbol the header
+declares, fails loudly (no CPU fallback) when no device is present, and the host-side pieces work."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import ROOT
+
+HEADER = os.path.join(ROOT, "include", "stepth_cuda.h")
+no_gpu = not torch.cuda.is_available()
+
+
+def declared_symbols():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(stepth_(?:cuda|host)_\w+)\s*\(", src)))
+
+
+def test_library_builds_and_exports_every_declared_symbol():
+    from stepth_b200 import _build, _ffi
+
+    if no_gpu:
+        _build.build()          # stale-aware: nvcc cross-compiles for sm_100a here
+    lib = _ffi.lib()
+    syms = declared_symbols()
+    assert len(syms) >= 24
+    for name in syms:
+        assert hasattr(lib, name), f"{name} declared in include/stepth_cuda.h but not exported"
+    # and the Python binding covers exactly the header
+    assert sorted(_ffi.SIGNATURES) == syms
+    assert b"sm_100a" in lib.stepth_cuda_version()
+
+
+def test_library_carries_sm100a_sass_only():
+    import shutil
+    import subprocess
+
+    from stepth_b200 import _build, _ffi
+
+    _ffi.lib()
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump):
+        pytest.skip("cuobjdump not available")
+    out = subprocess.run([cuobjdump, "-lelf", _build.LIB_PATH], capture_output=True, text=True).stdout
+    archs = set(re.findall(r"sm_(\d+a?)", out))
+    assert archs == {"100a"}, archs
+
+
+@pytest.mark.skipif(not no_gpu, reason="needs a box without a GPU")
+def test_no_cpu_fallback_without_a_device():
+    import stepth_b200
+    from stepth_b200 import _ffi
+
+    with pytest.raises(stepth_b200.StepthError) as e:
+        stepth_b200.Context(0)
+    assert e.value.code == _ffi.ERR_CUDA
+    assert "no CPU fallback" in str(e.value)
+    lib = _ffi.lib()
+    # every compute entry point rejects a null context instead of computing anything on the host
+    assert lib.stepth_cuda_invert_depth(None, None, 0) == _ffi.ERR_INVALID_ARG
+    assert lib.stepth_cuda_launch_count(None) == 0
+
+
+def test_product_package_never_imports_the_oracle():
+    import stepth_b200  # noqa: F401
+
+    pkg = os.path.join(ROOT, "stepth_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in text and "from oracle" not in text and "stepth_oracle" not in text, f
+
+
+def test_params_struct_layout():
+    from stepth_b200 import _ffi
+
+    assert C.sizeof(_ffi.Params) == 12
+    assert C.sizeof(_ffi.DevShape) == 36
+    assert _ffi.BLOCK_DTYPE.itemsize == 20
+    p = _ffi.make_params([1, 2, 3], 128, _ffi.RESAMPLE_U8 | _ffi.FLAG_INVERT)
+    assert bytes(p)[:4] == b"\x01\x02\x03\x00" and p.max_rings == 128
+    with pytest.raises(ValueError):
+        _ffi.make_params([1, 2], 5)
+
+
+def test_discretise_v0_tiles_the_image():
+    import stepth_b200
+
+    rng = np.random.default_rng(0)
+    h, w = 37, 53
+    img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+    img[:20, :30] = (90, 91, 92)   # a uniform region
+    for stride_img in (img, np.concatenate([img, np.full((h, w, 1), 255, np.uint8)], -1)):
+        blocks = stepth_b200.discretise_v0(stride_img, [36, 36, 36], min_splits=4, max_splits=11)
+        cover = np.zeros((h, w), np.int32)
+        for b in blocks:
+            cover[b["y"]:b["y"] + b["h"], b["x"]:b["x"] + b["w"]] += 1
+            region = img[b["y"]:b["y"] + b["h"], b["x"]:b["x"] + b["w"]].reshape(-1, 3).astype(np.int64)
+            assert b["value"].tolist() == (region.sum(0) // len(region)).tolist()   # floor mean
+        assert (cover == 1).all()
+        assert len(blocks) >= 16   # forced splits down to depth 4
+    # the reference's parameters: min 16 splits -> at least 2^16 blocks once the image has that many pixels
+    big = rng.integers(0, 256, (300, 400, 3), dtype=np.uint8)
+    blocks = stepth_b200.discretise_v0(big, [36, 36, 36])
+    assert 65536 <= len(blocks) <= 300 * 400
+    assert int((blocks["w"].astype(np.int64) * blocks["h"]).sum()) == 300 * 400
+    # identical pixels everywhere: stops right at the forced depth
+    flat = np.full((256, 256, 3), 7, np.uint8)
+    assert len(stepth_b200.discretise_v0(flat, [36, 36, 36])) == 65536
