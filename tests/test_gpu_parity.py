@@ -1,0 +1,409 @@
+"""GPU parity: libstepth_cuda.so (through the C ABI) against the CPU oracle, bit for bit, on the same bytes.
+
+Everything here is integer / byte / index work except the unit-scale Gaussian resample (f32, image 0.23.14);
+that one is also required to be bit-exact because both sides use the same tap tables, tap order and rounding.
+"""
+import numpy as np
+import pytest
+import torch
+
+from conftest import rgba_of
+
+pytestmark = pytest.mark.gpu
+
+P36 = [36, 36, 36]
+
+
+def synth_pair(kind, w, h, seed=1):
+    from stepth_b200 import synth
+
+    m, a = synth.make_pair(kind, w, h, seed)
+    return m.numpy(), a.numpy()
+
+
+def rand_pair(w, h, wa=None, ha=None, seed=0, levels=256):
+    rng = np.random.default_rng(seed)
+    wa, ha = wa or w, ha or h
+    step = 256 // levels
+    m = (rng.integers(0, levels, (h, w, 3)) * step).astype(np.uint8)
+    a = (rng.integers(0, levels, (ha, wa, 3)) * step).astype(np.uint8)
+    return rgba_of(m), a
+
+
+def gpu_raw(ctx, m, a, prec, rings, flags=0):
+    import stepth_b200 as sb
+
+    try:
+        return ctx.depth_dense(m, a, prec, rings, flags | sb.RESAMPLE_OFF, want_raw=True)["raw"]
+    except sb.StepthPanic as e:   # max == 0: the raw plane is still returned
+        assert e.code == 3
+        return e.partial["raw"]
+
+
+# ---- K1: raw distances --------------------------------------------------------------------------------------
+@pytest.mark.parametrize("kind", ["nat", "geo", "worst"])
+@pytest.mark.parametrize("w,h,rings", [(96, 64, 128), (161, 77, 255), (64, 200, 40)])
+def test_search_dense_vs_oracle(ctx, orc, kind, w, h, rings):
+    import stepth_b200 as sb
+
+    m, a = synth_pair(kind, w, h, seed=w + h)
+    ref = orc.search_dense(m, a, P36, rings, threads=8)
+    assert np.array_equal(gpu_raw(ctx, m, a, P36, rings), ref)
+    assert np.array_equal(gpu_raw(ctx, m, a, P36, rings, sb.FLAG_LITERAL_SEARCH), ref)
+
+
+@pytest.mark.parametrize(
+    "w,h,wa,ha",
+    [(8, 1, 8, 1), (1, 8, 1, 8), (3, 5, 3, 5), (17, 33, 17, 33), (129, 67, 129, 67), (40, 30, 7, 5), (40, 30, 90, 70),
+     (33, 9, 4, 40), (2, 4, 300, 2), (257, 3, 129, 2)],
+)
+def test_search_dense_ragged_shapes(ctx, orc, w, h, wa, ha):
+    m, a = rand_pair(w, h, wa, ha, seed=w * 31 + h, levels=6)
+    for prec in ([60, 60, 60], [44, 90, 130]):
+        ref = orc.search_dense(m, a, prec, 255, threads=4)
+        assert np.array_equal(gpu_raw(ctx, m, a, prec, 255), ref), (w, h, wa, ha, prec)
+
+
+@pytest.mark.parametrize("rings", [1, 2, 3, 17, 255, 256, 300, 512])
+def test_search_max_rings_and_u8_wrap(ctx, orc, rings):
+    # a far planted match: origins near (0,0), the only matching pixels sit 280..420 away -> d >= 256 wraps
+    h, w = 24, 24
+    m = rgba_of(np.full((h, w, 3), 10, np.uint8))
+    a = np.full((420, 420, 3), 200, np.uint8)
+    a[300:, 300:] = 10
+    a[5, 290] = 10
+    ref = orc.search_dense(m, a, P36, rings, threads=8)
+    got = gpu_raw(ctx, m, a, P36, rings)
+    assert np.array_equal(got, ref)
+    if rings >= 300:
+        assert (ref.astype(int) != 0).any()
+
+
+@pytest.mark.parametrize("prec", [[0, 36, 36], [1, 1, 1], [255, 255, 255], [36, 1, 255], [128, 128, 128]])
+def test_search_precision_edges(ctx, orc, prec):
+    import stepth_b200 as sb
+
+    m, a = rand_pair(50, 40, seed=7, levels=256)
+    m[..., :3][::3, ::5] = a[::3, ::5][:, :, :]   # some exact matches so that precision 1 finds something
+    for flags in (0, sb.FLAG_PIXELOPPS_SAT):
+        mode = orc.PIXELOPPS_SAT_ALL if flags else orc.PIXELOPPS_ABS_ALL
+        ref = orc.search_dense(m, a, prec, 64, pixelopps=mode, threads=4)
+        assert np.array_equal(gpu_raw(ctx, m, a, prec, 64, flags), ref), (prec, flags)
+
+
+def test_origin_outside_additional(ctx, orc):
+    # additional much smaller than main/2: origins beyond it give None -> 0 (helpers.rs:49-51)
+    m, a = rand_pair(64, 48, 10, 6, seed=5, levels=3)
+    ref = orc.search_dense(m, a, [100] * 3, 255, threads=4)
+    assert np.array_equal(gpu_raw(ctx, m, a, [100] * 3, 255), ref)
+    assert (ref[20:, :] == 0).all()
+
+
+# ---- whole path ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("resample", ["off", "u8", "f32"])
+@pytest.mark.parametrize("kind,w,h", [("nat", 150, 90), ("geo", 131, 70)])
+def test_depth_dense_vs_oracle(ctx, orc, resample, kind, w, h):
+    import stepth_b200 as sb
+
+    m, a = synth_pair(kind, w, h, seed=11)
+    g = {"off": sb.RESAMPLE_OFF, "u8": sb.RESAMPLE_U8, "f32": sb.RESAMPLE_F32}[resample]
+    o = {"off": orc.RESAMPLE_OFF, "u8": orc.RESAMPLE_U8, "f32": orc.RESAMPLE_F32}[resample]
+    ref, raw = orc.depth_dense(m, a, P36, 128, resample=o, threads=8, want_raw=True)
+    out = ctx.depth_dense(m, a, P36, 128, g, want_raw=True)
+    assert np.array_equal(out["raw"], raw)
+    assert np.array_equal(out["depth"], ref)
+
+
+@pytest.mark.parametrize("shape", [(8, 1), (1, 9), (2, 7), (5, 5), (6, 300), (300, 6), (40, 129)])
+def test_finish_small_and_border_shapes(ctx, orc, shape):
+    """the Gaussian's border renormalisation and tiny images (fewer than 7 taps), through the band-capable K2"""
+    from stepth_b200 import device
+
+    h, w = shape
+    rng = np.random.default_rng(h * 1000 + w)
+    raw = rng.integers(0, 200, (h, w), dtype=np.uint8)
+    raw[0, 0] = 199
+    norm, mx = orc.normalise(raw)
+    src = torch.from_numpy(raw).cuda().unsqueeze(0)
+    mxt = torch.tensor([mx], dtype=torch.int32, device="cuda")
+    for g, o in ((1, orc.RESAMPLE_U8), (2, orc.RESAMPLE_F32), (0, orc.RESAMPLE_OFF)):
+        depth, status = device.finish(ctx, src, mxt, h, g)
+        assert int(status[0]) == 0
+        assert np.array_equal(depth[0].cpu().numpy(), orc.gaussian_resample_unit(norm, o)), (shape, g)
+
+
+def test_fused_tail_vs_oracle(ctx, orc):
+    import stepth_b200 as sb
+
+    m, a = synth_pair("nat", 200, 120, seed=3)
+    flags = sb.RESAMPLE_U8 | sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY
+    out = ctx.depth_dense(m, a, P36, 128, flags)
+    depth = orc.invert_depth(orc.depth_dense(m, a, P36, 128, resample=orc.RESAMPLE_U8, threads=8))
+    mask, ft = orc.select_foreground(depth)
+    assert np.array_equal(out["depth"], depth)
+    assert out["from_to"] == ft
+    assert np.array_equal(out["mask"], mask)
+    assert np.array_equal(out["rgba"], orc.apply_mask(m, mask))
+
+
+def test_blocks_vs_oracle(ctx, orc):
+    import stepth_b200 as sb
+
+    m, a = synth_pair("nat", 180, 100, seed=9)
+    blocks = sb.discretise_v0(m, P36, min_splits=10)
+    assert 1024 <= len(blocks) < 180 * 100
+    ref, raw = orc.depth_from_blocks(a, blocks, P36, 180, 100, 255, resample=orc.RESAMPLE_U8, want_raw=True)
+    out = ctx.depth_from_blocks(a, blocks, 180, 100, P36, 255, sb.RESAMPLE_U8, want_raw=True)
+    assert np.array_equal(out["raw"], raw)
+    assert np.array_equal(out["depth"], ref)
+    # fused tail in block mode
+    flags = sb.RESAMPLE_U8 | sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY
+    out = ctx.depth_from_blocks(a, blocks, 180, 100, P36, 255, flags, rgba_in=m)
+    depth = orc.invert_depth(ref)
+    mask, ft = orc.select_foreground(depth)
+    assert out["from_to"] == ft and np.array_equal(out["mask"], mask)
+    assert np.array_equal(out["rgba"], orc.apply_mask(m, mask))
+
+
+def test_blocks_handmade_literal_origin(ctx, orc):
+    a = np.full((40, 60, 3), 200, np.uint8)
+    a[2, 4] = (10, 10, 10)
+    a[30, 50] = (90, 10, 10)
+    blocks = np.zeros(9, orc.BLOCK_DTYPE)
+    blocks[0] = (0, 0, 30, 20, (10, 10, 10), 0)      # origin (15, 10)
+    blocks[1] = (30, 0, 30, 20, (90, 12, 8), 0)      # origin (30, 10)
+    blocks[2] = (0, 20, 60, 20, (10, 10, 10), 0)     # origin (30, 20)
+    for i in range(3, 9):                            # zero-area filler blocks (>= 8 needed): origin (x/2, y/2)
+        blocks[i] = (i, i, 0, 0, (200, 200, 200), 0)
+    raw = orc.search_blocks(a, blocks, P36, 255)
+    out = ctx.depth_from_blocks(a, blocks, 60, 40, P36, 255, 0, want_raw=True)
+    assert np.array_equal(out["raw"], raw)
+    assert np.array_equal(out["depth"], orc.depth_from_blocks(a, blocks, P36, 60, 40, 255, resample=orc.RESAMPLE_OFF))
+
+
+# ---- error behaviour -----------------------------------------------------------------------------------------
+def test_errors_mirror_the_reference_panics(ctx, orc):
+    import stepth_b200 as sb
+
+    same = np.full((16, 16, 3), 50, np.uint8)
+    with pytest.raises(sb.StepthPanic) as e:           # every distance 0 -> max 0 -> divide by zero (:127)
+        ctx.depth_dense(rgba_of(same), same, P36, 255)
+    assert e.value.code == 3 and "divide by zero" in str(e.value)
+    with pytest.raises(sb.StepthPanic) as e:           # precision 0: nothing matches -> None -> 0 -> max 0
+        ctx.depth_dense(*rand_pair(16, 16), [0, 0, 0], 255)
+    assert e.value.code == 3
+    with pytest.raises(sb.StepthPanic) as e:           # < 8 blocks: par_chunks_mut(0)
+        ctx.depth_dense(rgba_of(same[:1, :7]), same, P36, 255)
+    assert e.value.code == 4
+    blocks = np.zeros(7, sb.BLOCK_DTYPE)
+    blocks[:] = (0, 0, 1, 1, (1, 2, 3), 0)
+    with pytest.raises(sb.StepthPanic):
+        ctx.depth_from_blocks(same, blocks, 16, 16, P36)
+    with pytest.raises(sb.StepthIOError):              # a block outside the image
+        bad = np.zeros(8, sb.BLOCK_DTYPE)
+        bad[:] = (10, 10, 10, 10, (1, 2, 3), 0)
+        ctx.depth_from_blocks(same, bad, 16, 16, P36)
+    with pytest.raises(sb.StepthPanic) as e:           # flat depth: depth_split underflows
+        ctx.select_foreground(np.full((4, 4), 9, np.uint8))
+    assert e.value.code == 5
+    with pytest.raises(sb.StepthPanic):
+        ctx.depth_split(np.array([5, 6], np.uint8), 2)
+    with pytest.raises(sb.StepthIOError):
+        ctx.apply_mask(np.zeros((4, 4, 4), np.uint8), np.zeros((3, 4), np.uint8))
+    d = sb.DepthImage.from_image(np.zeros((4, 6, 3), np.uint8), ctx)
+    with pytest.raises(sb.StepthIOError, match="Sizes don't match"):
+        d.load_depth(np.zeros((6, 4), np.uint8))
+    with pytest.raises(sb.StepthIOError, match="Failed to open image"):
+        sb.DepthImage.open("/nonexistent/file.jpg")
+
+
+# ---- tail, stand-alone ---------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n", [1, 3, 4, 17, 1000, 4099, 65536 + 5])
+def test_invert_slice_apply(ctx, orc, n):
+    rng = np.random.default_rng(n)
+    d = rng.integers(0, 256, n, dtype=np.uint8)
+    assert np.array_equal(ctx.invert_depth(d), orc.invert_depth(d))
+    for frm, to in [(None, None), (10, 200), (200, 10), (0, 0), (255, None), (None, 0)]:
+        assert np.array_equal(ctx.slice(d, frm, to), orc.slice_mask(d, frm, to))
+    rgba = rng.integers(0, 256, (n, 4), dtype=np.uint8)
+    mask = rng.choice(np.array([0, 1, 255], np.uint8), n)
+    assert np.array_equal(ctx.apply_mask(rgba, mask), orc.apply_mask(rgba, mask))
+
+
+@pytest.mark.parametrize("zones", [1, 2, 3, 4, 7, 16, 100, 255])
+def test_depth_split_vs_oracle(ctx, orc, zones, assets):
+    rng = np.random.default_rng(zones)
+    planes = [assets["depth"], orc.invert_depth(assets["depth"]),
+              rng.integers(0, 256, 5000, dtype=np.uint8),
+              np.clip(rng.normal(120, 30, 20000), 0, 255).astype(np.uint8),
+              np.array([0] * 50 + [255] * 3 + [100] * 20, np.uint8)]
+    import stepth_b200 as sb
+
+    for d in planes:
+        try:
+            ref = orc.depth_split(d, zones)
+        except orc.OracleError as e:
+            with pytest.raises(sb.StepthPanic) as g:
+                ctx.depth_split(d, zones)
+            assert g.value.code == e.code
+            continue
+        assert ctx.depth_split(d, zones) == ref
+
+
+def test_assets_through_the_public_api(ctx, orc, assets, tmp_path):
+    """Readme.md:9-24 end to end with the reference's own images (decoded pixels from tests/golden)."""
+    import stepth_b200 as sb
+
+    main, add = assets["main"], assets["additional"]
+    img = sb.DepthImage.from_image(main, ctx)
+    img.load_depth_from_additional(add, [255 // 7] * 3, mode="dense")
+    ref = orc.depth_dense(rgba_of(main), add, [36] * 3, 255, resample=orc.RESAMPLE_U8, threads=8)
+    assert np.array_equal(img.depth_plane, ref)
+    r = np.corrcoef(img.depth_plane.reshape(-1).astype(float), assets["depth"].reshape(-1).astype(float))[0, 1]
+    assert r >= 0.97
+    # block mode with the stand-in discretiser == oracle on the same block list
+    blocks = sb.discretise_v0(img.image, [36] * 3)
+    img2 = sb.DepthImage.from_image(main, ctx)
+    img2.load_depth_from_additional(add, [36] * 3, blocks=blocks)
+    assert np.array_equal(img2.depth_plane, orc.depth_from_blocks(add, blocks, [36] * 3, 600, 400, 255))
+    # the tail on the reference's own depth map: the known answer (0, 201)
+    img.load_depth(assets["depth"])
+    img.invert_depth()
+    assert img.depth_split(2) == [(0, 201), (202, 255)]
+    fg = img.select_foreground()
+    fg.apply_mask()
+    mask_ref, ft = orc.select_foreground(orc.invert_depth(assets["depth"]))
+    assert ft == (0, 201) and np.array_equal(fg.mask, mask_ref)
+    assert np.array_equal(fg.image, orc.apply_mask(rgba_of(main), mask_ref))
+    fg.save(str(tmp_path / "fg.png"))
+    assert img.depth().size == (600, 400)
+
+
+def test_batch_and_per_pair_status(ctx, orc):
+    import stepth_b200 as sb
+
+    pairs = [synth_pair("nat", 120, 80, seed=s) for s in (1, 2, 3)]
+    same = np.full((80, 120, 3), 77, np.uint8)
+    pairs.insert(1, (rgba_of(same), same))   # this pair has max == 0
+    flags = sb.RESAMPLE_U8 | sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY
+    out = ctx.depth_dense_batch([p[0] for p in pairs], [p[1] for p in pairs], P36, 128, flags)
+    assert out["status"].tolist() == [0, 3, 0, 0]
+    for i in (0, 2, 3):
+        m, a = pairs[i]
+        depth = orc.invert_depth(orc.depth_dense(m, a, P36, 128, resample=orc.RESAMPLE_U8, threads=8))
+        mask, ft = orc.select_foreground(depth)
+        assert np.array_equal(out["depth"][i], depth)
+        assert tuple(out["from_to"][i]) == ft
+        assert np.array_equal(out["mask"][i], mask)
+        assert np.array_equal(out["rgba"][i], orc.apply_mask(m, mask))
+
+
+def test_device_pipeline_matches_host_api(ctx, orc):
+    import stepth_b200 as sb
+    from stepth_b200 import device
+
+    pairs = [synth_pair("geo", 100, 60, seed=s) for s in (4, 5)]
+    flags = sb.RESAMPLE_U8 | sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY
+    mains = torch.from_numpy(np.stack([p[0] for p in pairs])).cuda()
+    adds = torch.from_numpy(np.stack([p[1] for p in pairs])).cuda()
+    pipe = device.DensePipeline(ctx, 2, 100, 60, 100, 60, P36, 64, flags)
+    pipe.run(mains, adds)
+    torch.cuda.synchronize()
+    for i, (m, a) in enumerate(pairs):
+        host = ctx.depth_dense(m, a, P36, 64, flags)
+        assert np.array_equal(pipe.depth[i].cpu().numpy(), host["depth"])
+        assert np.array_equal(pipe.mask[i].cpu().numpy(), host["mask"])
+        assert np.array_equal(pipe.rgba_out[i].cpu().numpy(), host["rgba"])
+        assert tuple(pipe.ranges[i, :2].tolist()) == host["from_to"]
+
+
+def test_row_bands_equal_whole_image(ctx, orc):
+    """config 5's decomposition on one GPU: search + finish per row band (with halos) == the whole image"""
+    from stepth_b200 import device
+
+    m, a = synth_pair("nat", 96, 120, seed=21)
+    rings = 20
+    whole = orc.depth_dense(m, a, P36, rings, resample=orc.RESAMPLE_U8, threads=8)
+    mt, at = torch.from_numpy(m).cuda(), torch.from_numpy(a).cuda()
+    h = 120
+    bands = [(0, 37), (37, 80), (80, 120)]
+    d8 = torch.empty((1, h, 96), dtype=torch.uint8, device="cuda")
+    mx_all = torch.zeros(1, dtype=torch.int32, device="cuda")
+    for y0, y1 in bands:
+        ay0 = max(0, (y0 + 1) // 2 - rings)
+        ay1 = min(h, y1 // 2 + rings + 1)
+        band_d8, mx = device.search_dense(ctx, mt[None, y0:y1].contiguous(), at[None, ay0:ay1].contiguous(), P36, rings,
+                                          y0=y0, add_y0=ay0, add_img_h=h, img_h=h)
+        d8[0, y0:y1] = band_d8[0]
+        mx_all = torch.maximum(mx_all, mx)   # the 1-byte MAX all-reduce of the multi-GPU path
+    out = torch.empty((h, 96), dtype=torch.uint8, device="cuda")
+    for y0, y1 in bands:
+        s0, s1 = max(0, y0 - 3), min(h, y1 + 3)   # 3-row halo for the vertical pass
+        depth, status = device.finish(ctx, d8[:, s0:s1].contiguous(), mx_all, h, 1, src_y0=s0, out_y0=y0, out_rows=y1 - y0)
+        out[y0:y1] = depth[0]
+    assert np.array_equal(out.cpu().numpy(), whole)
+
+
+def test_normalize_brightness_vs_oracle(ctx, orc):
+    rng = np.random.default_rng(0)
+    for n1, n2 in [(1000, 1000), (12345, 999), (7, 5000)]:
+        a = rng.integers(0, 65536, n1, dtype=np.uint16)
+        b = (rng.integers(0, 65536, n2) * 0.6).astype(np.uint16)
+        for pct in (0.01, 0.9):
+            assert np.array_equal(ctx.normalize_brightness_luma16(a, b, pct), orc.normalize_brightness_luma16(a, b, pct))
+        a3 = rng.integers(0, 65536, (n1, 3), dtype=np.uint16)
+        b3 = (rng.integers(0, 65536, (n2, 3)) * np.array([0.5, 1.0, 1.7])).clip(0, 65535).astype(np.uint16)
+        for pct in (0.01, 0.9):
+            assert np.array_equal(ctx.normalize_brightness_rgb16(a3, b3, pct), orc.normalize_brightness_rgb16(a3, b3, pct))
+
+
+# ---- BASELINE.json's full sizes: size-independent properties + sampled oracle checks -----------------------------
+@pytest.mark.parametrize("kind,w,h,rings", [("nat", 1920, 1080, 128), ("geo", 1920, 1080, 128), ("nat", 3840, 2160, 256)])
+def test_full_size_production_equals_in_order_kernel(ctx, orc, kind, w, h, rings):
+    import stepth_b200 as sb
+    from stepth_b200 import device, synth
+
+    m, a = synth.make_pair(kind, w, h, 1, device="cuda")
+    d8, mx = device.search_dense(ctx, m[None], a[None], P36, rings)
+    d8_lit, mx_lit = device.search_dense(ctx, m[None], a[None], P36, rings, flags=sb.FLAG_LITERAL_SEARCH)
+    assert torch.equal(d8, d8_lit) and torch.equal(mx, mx_lit)
+    assert int(mx[0]) == int(d8.max())
+    # sampled oracle check on the same bytes
+    rng = np.random.default_rng(1)
+    idx = rng.choice(w * h, 3000, replace=False).astype(np.uint32)
+    sub, _ = orc.search_dense_subset(m.cpu().numpy(), a.cpu().numpy(), P36, idx, rings, threads=8)
+    assert np.array_equal(d8[0].reshape(-1).cpu().numpy()[idx], sub)
+    # the fused tail's invariants: invert is an involution, the mask is a pure function of depth and (from,to),
+    # apply only ever clears, and clears exactly the masked-out pixels
+    flags = sb.RESAMPLE_U8 | sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY
+    pipe = device.DensePipeline(ctx, 1, w, h, w, h, P36, rings, flags)
+    pipe.run(m[None], a[None])
+    plain = device.DensePipeline(ctx, 1, w, h, w, h, P36, rings, sb.RESAMPLE_U8)
+    plain.run(m[None], a[None])
+    torch.cuda.synchronize()
+    assert int(pipe.status[0]) == 0
+    assert torch.equal(pipe.depth, 255 - plain.depth)
+    hist = torch.bincount(pipe.depth.reshape(-1).int(), minlength=256).int()
+    assert torch.equal(hist, pipe.hist[0])
+    frm, to = int(pipe.ranges[0, 0]), int(pipe.ranges[0, 1])
+    assert orc.depth_split(pipe.depth[0].cpu().numpy(), 2)[0] == (frm, to)
+    keep = (pipe.depth >= frm) & (pipe.depth <= to)
+    assert torch.equal(pipe.mask, torch.where(keep, 255, 0).to(torch.uint8))
+    assert torch.equal(pipe.rgba_out, m[None] * keep.unsqueeze(-1))
+
+
+def test_full_size_worst_case_sampled(ctx, orc):
+    from stepth_b200 import device, synth
+
+    w, h, rings = 1920, 1080, 128
+    m, a = synth.make_pair("worst", w, h, 1, device="cuda")
+    d8, mx = device.search_dense(ctx, m[None], a[None], P36, rings)
+    rng = np.random.default_rng(2)
+    idx = rng.choice(w * h, 1500, replace=False).astype(np.uint32)
+    # make sure some sampled queries can see the planted pixel at (w/4, h/4): they are the only non-zero ones
+    ys, xs = np.mgrid[h // 2 - 60:h // 2 + 60:7, w // 2 - 60:w // 2 + 60:7]
+    idx = np.concatenate([idx, (ys * w + xs).reshape(-1).astype(np.uint32)])
+    sub, _ = orc.search_dense_subset(m.cpu().numpy(), a.cpu().numpy(), P36, idx, rings, threads=8)
+    got = d8[0].reshape(-1).cpu().numpy()[idx]
+    assert np.array_equal(got, sub)
+    assert (sub != 0).any() and int(mx[0]) > 0
