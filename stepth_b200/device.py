@@ -44,8 +44,9 @@ class DensePipeline:
         self.ranges = torch.zeros((self.n, 512), **u8)
         self.shape = _ffi.DevShape(self.n, self.w, self.h, self.h, 0, self.wa, self.ha, 0, self.ha)
 
-    def run(self, main_rgba: torch.Tensor, add_rgb: torch.Tensor) -> None:
-        """Enqueue the whole path on the current stream (asynchronous)."""
+    def run(self, main_rgba: torch.Tensor, add_rgb: torch.Tensor, search_events=None) -> None:
+        """Enqueue the whole path on the current stream (asynchronous).  `search_events` = (start, end) CUDA events
+        recorded around the ring-search stage (bench.py's roofline timing)."""
         assert main_rgba.is_cuda and add_rgb.is_cuda and main_rgba.dtype == torch.uint8 and add_rgb.dtype == torch.uint8
         assert tuple(main_rgba.shape) == (self.n, self.h, self.w, 4) and tuple(add_rgb.shape) == (self.n, self.ha, self.wa, 3)
         lib, ctx, st = self.ctx._lib, self.ctx, _stream_handle()
@@ -53,8 +54,12 @@ class DensePipeline:
         if self.fg:
             self.hist.zero_()
         self.status.zero_()
+        if search_events is not None:
+            search_events[0].record()
         ctx.check(lib.stepth_cuda_dev_search_dense(ctx.handle, st, C.byref(self.shape), p, _ffi.ptr(main_rgba),
                                                    _ffi.ptr(add_rgb), _ffi.ptr(self.d8), _ffi.ptr(self.max)))
+        if search_events is not None:
+            search_events[1].record()
         ctx.check(lib.stepth_cuda_dev_finish(ctx.handle, st, self.n, self.w, self.h, _ffi.ptr(self.d8), 0, self.h,
                                              _ffi.ptr(self.max), self.flags, _ffi.ptr(self.depth), 0, self.h,
                                              _ffi.ptr(self.hist) if self.fg else None, _ffi.ptr(self.status)))
