@@ -87,7 +87,7 @@ extern "C" void stepth_cuda_ctx_destroy(stepth_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     stepth_ctx::Buf *bufs[] = {&ctx->main_rgba, &ctx->add_rgb, &ctx->d8,   &ctx->depth, &ctx->mask, &ctx->rgba_out,
                                &ctx->blocks,    &ctx->plane,   &ctx->small, &ctx->u16a,  &ctx->u16b, &ctx->u16o,
-                               &ctx->work};
+                               &ctx->work,      &ctx->planes};
     for (auto *b : bufs)
         if (b->p) cudaFree(b->p);
     for (auto &kv : ctx->taps)
@@ -157,7 +157,7 @@ extern "C" int32_t stepth_cuda_dev_search_dense(stepth_ctx *ctx, void *stream, c
         LAUNCH_CHECK(ctx);
         return STEPTH_OK;
     }
-    return launch_search_tiles_dense(ctx, st, a, s->n_pairs);
+    return launch_search_tiles(ctx, st, a, s->n_pairs);
 }
 
 extern "C" int32_t stepth_cuda_dev_search_blocks(stepth_ctx *ctx, void *stream, const stepth_params *params,
@@ -182,10 +182,13 @@ extern "C" int32_t stepth_cuda_dev_search_blocks(stepth_ctx *ctx, void *stream, 
     a.wa = wa; a.ha = ha; a.add_y0 = 0; a.add_img_h = ha;
     a.d8 = d8_out;
     a.max_out = max_out;
-    dim3 grid((a.n_queries + 255) / 256, 1);
-    search_literal_kernel<<<grid, 256, 0, st>>>(a);
-    LAUNCH_CHECK(ctx);
-    return STEPTH_OK;
+    if (params->flags & STEPTH_FLAG_LITERAL_SEARCH) {
+        dim3 grid((a.n_queries + 255) / 256, 1);
+        search_literal_kernel<<<grid, 256, 0, st>>>(a);
+        LAUNCH_CHECK(ctx);
+        return STEPTH_OK;
+    }
+    return launch_search_tiles(ctx, st, a, 1);
 }
 
 extern "C" int32_t stepth_cuda_dev_paint_blocks(stepth_ctx *ctx, void *stream, const stepth_block *blocks,
