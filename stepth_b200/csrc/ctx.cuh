@@ -25,6 +25,8 @@ struct stepth_ctx {
     };
     // scratch for the host-buffer entry points
     Buf main_rgba, add_rgb, d8, depth, mask, rgba_out, blocks, plane, small, u16a, u16b, u16o, work;
+    Buf worklist;  // [count, cursor, pad..][uint2 entries]: origins exported to the warp-per-origin tail kernel
+    uint32_t export_below = 48;  // STEPTH_EXPORT_BELOW overrides (0 disables the tail kernel)
     Buf planes;  // candidate bit-planes of the additional image(s) (planes.cuh), rebuilt by every search
     // small per-pair state: [max u32][hist 256 u32][status i32][n_out u32][ranges 512 B] per pair
     void *h_small = nullptr;  // pinned mirror

@@ -18,6 +18,8 @@
 //
 // The same kernel serves the block list (one CTA per 256 consecutive DiscretePixels; list order is kept).
 #pragma once
+#include <algorithm>
+
 #include "ctx.cuh"
 #include "planes.cuh"
 #include "search_literal.cuh"
@@ -32,6 +34,10 @@ struct TileArgs {
     const uint32_t *planes;
     PlaneGeom g;
     uint32_t by0;  // first tile row (global tile coordinates) of a row band
+    // sparse-tail export (search_origins.cuh -> search_tail.cuh)
+    uint2 *wl;              // exported origins
+    uint32_t *wl_count;     // [0] = number of entries, [1] = tail cursor
+    uint32_t export_below;  // a tile exports its unresolved origins once fewer than this many are left (0 = never)
 };
 
 __device__ __forceinline__ bool verify_px(const uint8_t *add, uint32_t wa, int x, int y, const ColourBox &box) {
@@ -44,7 +50,7 @@ __device__ __forceinline__ bool verify_px(const uint8_t *add, uint32_t wa, int x
 template <bool COLS>
 __device__ __forceinline__ int scan_line(const uint32_t *__restrict__ planes, uint32_t words_per_line, int line,
                                          int n_lines, int lo, int hi, int n, uint32_t jr, uint32_t jg, uint32_t jb,
-                                         const uint8_t *add, uint32_t wa, const ColourBox &box) {
+                                         uint32_t col) {
     if ((unsigned)line >= (unsigned)n_lines) return -1;
     if (lo < 0) lo = 0;
     if (hi > n - 1) hi = n - 1;
@@ -55,11 +61,8 @@ __device__ __forceinline__ int scan_line(const uint32_t *__restrict__ planes, ui
         uint32_t m = __ldg(cell + jr) & __ldg(cell + jg) & __ldg(cell + jb);
         if (w == w0) m &= 0xffffffffu << (lo & 31);
         if (w == w1) m &= 0xffffffffu >> (31 - (hi & 31));
-        while (m) {
-            const int p = (w << 5) + __ffs(m) - 1;
-            if (COLS ? verify_px(add, wa, line, p, box) : verify_px(add, wa, p, line, box)) return p;
-            m &= m - 1;
-        }
+        if (m) m = refine_exact(cell, col, m);
+        if (m) return (w << 5) + __ffs(m) - 1;
     }
     return -1;
 }
@@ -74,8 +77,9 @@ __global__ void __launch_bounds__(256) search_tiles_kernel(TileArgs a) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t pair = BLOCKS ? 0u : blockIdx.z;
     const int wa = (int)a.g.wa, ha = (int)a.g.ha;
+    const int src_wa = (int)a.s.wa, src_ha = (int)a.s.ha;
     const int add_y0 = (int)a.s.add_y0, img_h = (int)a.s.add_img_h;
-    const uint8_t *add = a.s.add_rgb + (size_t)pair * ha * wa * 3;
+    const uint8_t *add = a.s.add_rgb + (size_t)pair * src_ha * src_wa * 3;
     const uint32_t *rp = a.planes + (size_t)pair * a.g.pair_words;
     const uint32_t *cp = rp + a.g.rp_words;
     const bool sat = a.s.sat != 0;
@@ -110,12 +114,12 @@ __global__ void __launch_bounds__(256) search_tiles_kernel(TileArgs a) {
     }
     {
         uint32_t key = KEY_NONE;
-        if (!valid || ox >= wa || oyg >= img_h || ox > 0xffff || oyg > 0xffff) {
+        if (!valid || ox >= src_wa || oyg >= img_h || ox > 0xffff || oyg > 0xffff) {
             key = KEY_DEAD;  // ring 0 has no in-bounds probe: `still_in_bounds` stays false -> None (helpers.rs:49-51)
         } else {
             const int oyl = oyg - add_y0;
             const ColourBox box = make_box(col & 0xff, (col >> 8) & 0xff, (col >> 16) & 0xff, a.s.pr, a.s.pg, a.s.pb, sat);
-            if (oyl >= 0 && oyl < ha && verify_px(add, (uint32_t)wa, ox, oyl, box)) key = 0;  // ring 0
+            if (oyl >= 0 && oyl < src_ha && verify_px(add, (uint32_t)src_wa, ox, oyl, box)) key = 0;  // ring 0
         }
         q_pos[tid] = (uint32_t)ox | ((uint32_t)oyg << 16);
         q_col[tid] = col;
@@ -153,15 +157,14 @@ __global__ void __launch_bounds__(256) search_tiles_kernel(TileArgs a) {
             const uint32_t pos = q_pos[q], c = q_col[q];
             const int qx = (int)(pos & 0xffff), qyg = (int)(pos >> 16), qy = qyg - add_y0;
             const uint32_t r = c & 0xff, g = (c >> 8) & 0xff, b = (c >> 16) & 0xff;
-            const ColourBox box = make_box(r, g, b, a.s.pr, a.s.pg, a.s.pb, sat);
-            const uint32_t jr = r >> QSHIFT, jg = NB + (g >> QSHIFT), jb = 2 * NB + (b >> QSHIFT);
+            const uint32_t jr = w_u(r), jg = CH_WORDS + w_u(g), jb = 2 * CH_WORDS + w_u(b);
             uint32_t key = KEY_NONE;
             for (int s = s0; s < s1; ++s) {
                 // no in-bounds probe from ring s on (helpers.rs:49-51): the column pass may still own rings < s
-                if (qx - s < 0 && qx + s >= wa && qyg - s < 0 && qyg + s >= img_h) { key = KEY_DEAD_FROM | (uint32_t)s; break; }
-                int x = scan_line<false>(rp, a.g.nxw, qy + s, ha, qx - s, qx + s, wa, jr, jg, jb, add, (uint32_t)wa, box);
+                if (qx - s < 0 && qx + s >= src_wa && qyg - s < 0 && qyg + s >= img_h) { key = KEY_DEAD_FROM | (uint32_t)s; break; }
+                int x = scan_line<false>(rp, a.g.nxw, qy + s, ha, qx - s, qx + s, wa, jr, jg, jb, c);
                 if (x >= 0) { key = ring_key(x - qx, s); break; }
-                x = scan_line<false>(rp, a.g.nxw, qy - s, ha, qx - s, qx + s, wa, jr, jg, jb, add, (uint32_t)wa, box);
+                x = scan_line<false>(rp, a.g.nxw, qy - s, ha, qx - s, qx + s, wa, jr, jg, jb, c);
                 if (x >= 0) { key = ring_key(x - qx, -s); break; }
             }
             if (key != KEY_NONE) q_key[q] = key;
@@ -175,15 +178,14 @@ __global__ void __launch_bounds__(256) search_tiles_kernel(TileArgs a) {
                 const uint32_t pos = q_pos[q], c = q_col[q];
                 const int qx = (int)(pos & 0xffff), qyg = (int)(pos >> 16), qy = qyg - add_y0;
                 const uint32_t r = c & 0xff, g = (c >> 8) & 0xff, b = (c >> 16) & 0xff;
-                const ColourBox box = make_box(r, g, b, a.s.pr, a.s.pg, a.s.pb, sat);
-                const uint32_t jr = r >> QSHIFT, jg = NB + (g >> QSHIFT), jb = 2 * NB + (b >> QSHIFT);
+                    const uint32_t jr = w_u(r), jg = CH_WORDS + w_u(g), jb = 2 * CH_WORDS + w_u(b);
                 const bool dead_from = krow != KEY_NONE && (krow & KEY_DEAD_FROM) != 0;
                 const int lim = krow == KEY_NONE ? s1 : dead_from ? (int)(krow & 0xffffu) : (int)(krow >> 12);
                 uint32_t key = dead_from ? KEY_DEAD : krow;
                 for (int s = s0; s < lim; ++s) {
-                    int y = scan_line<true>(cp, a.g.nyw, qx + s, wa, qy - s + 1, qy + s - 1, ha, jr, jg, jb, add, (uint32_t)wa, box);
+                    int y = scan_line<true>(cp, a.g.nyw, qx + s, wa, qy - s + 1, qy + s - 1, ha, jr, jg, jb, c);
                     if (y >= 0) { key = ring_key(s, y - qy); break; }
-                    y = scan_line<true>(cp, a.g.nyw, qx - s, wa, qy - s + 1, qy + s - 1, ha, jr, jg, jb, add, (uint32_t)wa, box);
+                    y = scan_line<true>(cp, a.g.nyw, qx - s, wa, qy - s + 1, qy + s - 1, ha, jr, jg, jb, c);
                     if (y >= 0) { key = ring_key(-s, y - qy); break; }
                 }
                 if (key != krow) q_key[q] = key;
@@ -203,18 +205,32 @@ __global__ void __launch_bounds__(256) search_tiles_kernel(TileArgs a) {
     if (tid == 0 && s_max) atomicMax(a.s.max_out + pair, s_max);
 }
 
-// planes (K0) + tiles (K1) for n_pairs dense pairs, or for one block list (a.blocks != nullptr)
+// forward: the dense-mode kernel lives in search_origins.cuh
+constexpr int ORG_NT_FWD = 64;
+__global__ void search_origins_kernel(TileArgs a);
+void launch_search_tail(stepth_ctx *ctx, cudaStream_t st, const TileArgs &t);  // search_tail.cuh
+
+// planes (K0) + search (K1) for n_pairs dense pairs, or for one block list (a.blocks != nullptr)
 inline int32_t launch_search_tiles(stepth_ctx *ctx, cudaStream_t st, const SearchArgs &a, uint32_t n_pairs) {
     if (a.wa > 0xffffu || a.add_img_h > 0xffffu)
         return set_err(ctx, STEPTH_ERR_INVALID_ARG, "additional image larger than 65535 in one dimension");
     TileArgs t;
+    memset(&t, 0, sizeof t);
     t.s = a;
-    t.g = make_plane_geom(a.wa, a.ha);
+    // planes only cover what a query can reach: dense origins are half-coordinates (depth_image.rs:114-117), so columns
+    // [0, w/2 + max_rings) and local rows [0, (y0+h)/2 + max_rings - add_y0) -- the rest of the image is never probed
+    uint32_t cover_w = a.wa, cover_h = a.ha;
+    if (!a.blocks) {
+        cover_w = (uint32_t)std::min<uint64_t>(a.wa, (uint64_t)a.w / 2 + a.max_rings);
+        const int64_t last_row = (int64_t)(a.y0 + a.h) / 2 + a.max_rings - 1 - (int64_t)a.add_y0;  // local, inclusive
+        cover_h = (uint32_t)std::max<int64_t>(1, std::min<int64_t>(a.ha, last_row + 1));
+    }
+    t.g = make_plane_geom(cover_w, cover_h, a.wa);
     const size_t plane_bytes = t.g.pair_words * sizeof(uint32_t) * n_pairs;
     int32_t rc = ensure(ctx, ctx->planes, plane_bytes);
     if (rc != STEPTH_OK) return rc;
     t.planes = (const uint32_t *)ctx->planes.p;
-    PlaneArgs p{a.add_rgb, (uint32_t *)ctx->planes.p, t.g, a.pr, a.pg, a.pb, a.sat};
+    PlaneArgs p{a.add_rgb, (size_t)a.ha * a.wa * 3, (uint32_t *)ctx->planes.p, t.g, a.pr, a.pg, a.pb, a.sat};
     if (t.g.nyw > 65535u || n_pairs > 65535u)
         return set_err(ctx, STEPTH_ERR_INVALID_ARG, "too many plane tile rows or pairs for one launch");
     planes_kernel<<<dim3(t.g.nxw, t.g.nyw, n_pairs), 256, 0, st>>>(p);
@@ -224,11 +240,25 @@ inline int32_t launch_search_tiles(stepth_ctx *ctx, cudaStream_t st, const Searc
         t.by0 = 0;
         search_tiles_kernel<true><<<dim3((a.n_queries + 255) / 256, 1, 1), 256, 0, st>>>(t);
     } else {
-        t.by0 = (a.y0 + 1) / 16;
-        const uint32_t by1 = (a.y0 + a.h) / 16;  // tile row of the last band row y0 + h - 1
-        const uint32_t tiles_y = by1 - t.by0 + 1, tiles_x = a.w / 16 + 1;
-        if (tiles_y > 65535u) return set_err(ctx, STEPTH_ERR_INVALID_ARG, "band taller than 1M rows");
-        search_tiles_kernel<false><<<dim3(tiles_x, tiles_y, n_pairs), 256, 0, st>>>(t);
+        // 16x16 origins per CTA; origin (k, l) serves main pixels (2k-1 .. 2k, 2l-1 .. 2l)
+        t.by0 = ((a.y0 + 1) / 2) / 16;
+        const uint32_t by1 = ((a.y0 + a.h) / 2) / 16;  // origin row of the last band row y0 + h - 1
+        const uint32_t tiles_y = by1 - t.by0 + 1, tiles_x = (a.w / 2) / 16 + 1;
+        if (tiles_y > 65535u) return set_err(ctx, STEPTH_ERR_INVALID_ARG, "band taller than 2M rows");
+        // work list of the sparse tail: at most one entry per origin
+        const size_t max_entries = (size_t)tiles_x * tiles_y * 256 * n_pairs;
+        rc = ensure(ctx, ctx->worklist, max_entries * sizeof(uint2) + 64);
+        if (rc != STEPTH_OK) return rc;
+        t.wl_count = (uint32_t *)ctx->worklist.p;
+        t.wl = (uint2 *)((char *)ctx->worklist.p + 64);
+        t.export_below = ctx->export_below;
+        STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(t.wl_count, 0, 64, st));
+        search_origins_kernel<<<dim3(tiles_x, tiles_y, n_pairs), ORG_NT_FWD, 0, st>>>(t);
+        if (t.export_below) {
+            ctx->launches++;
+            STEPTH_CUDA_TRY(ctx, cudaGetLastError());
+            launch_search_tail(ctx, st, t);
+        }
     }
     ctx->launches++;
     STEPTH_CUDA_TRY(ctx, cudaGetLastError());

@@ -9,6 +9,8 @@
 #include "ctx.cuh"
 #include "search_literal.cuh"
 #include "search_tiles.cuh"
+#include "search_origins.cuh"
+#include "search_tail.cuh"
 #include "tail.cuh"
 #include "brightness.cuh"
 
@@ -72,6 +74,7 @@ extern "C" int32_t stepth_cuda_ctx_create(int32_t device, stepth_ctx **ctx_out) 
     stepth_ctx *ctx = new stepth_ctx();
     ctx->device = device;
     ctx->sm_count = prop.multiProcessorCount;
+    if (const char *ev = getenv("STEPTH_EXPORT_BELOW")) ctx->export_below = (uint32_t)atoi(ev);  // tuning knob
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
         g_create_err = std::string("cudaStreamCreate failed: ") + cudaGetErrorString(e);
         delete ctx;
@@ -87,7 +90,7 @@ extern "C" void stepth_cuda_ctx_destroy(stepth_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     stepth_ctx::Buf *bufs[] = {&ctx->main_rgba, &ctx->add_rgb, &ctx->d8,   &ctx->depth, &ctx->mask, &ctx->rgba_out,
                                &ctx->blocks,    &ctx->plane,   &ctx->small, &ctx->u16a,  &ctx->u16b, &ctx->u16o,
-                               &ctx->work,      &ctx->planes};
+                               &ctx->work,      &ctx->planes, &ctx->worklist};
     for (auto *b : bufs)
         if (b->p) cudaFree(b->p);
     for (auto &kv : ctx->taps)
