@@ -1,11 +1,53 @@
 // common.cuh -- shared device helpers for the stepth sm_100a kernels.
 #pragma once
+#include <cmath>
 #include <cstdint>
 #include <cuda_runtime.h>
 
 #include "../../include/stepth_cuda.h"
 
 namespace stepth {
+
+// Functions marked STEPTH_HD also compile for the host so that tests/host_emul can unit-test the index math of the
+// kernels without a GPU (test infrastructure; the product library never runs them on the CPU).
+#define STEPTH_HD __host__ __device__ __forceinline__
+
+STEPTH_HD int ffs32(uint32_t x) {
+#ifdef __CUDA_ARCH__
+    return __ffs((int)x);
+#else
+    return __builtin_ffs((int)x);
+#endif
+}
+STEPTH_HD int ffs64(unsigned long long x) {
+#ifdef __CUDA_ARCH__
+    return __ffsll((long long)x);
+#else
+    return __builtin_ffsll((long long)x);
+#endif
+}
+STEPTH_HD int clz32(uint32_t x) {  // x != 0
+#ifdef __CUDA_ARCH__
+    return __clz((int)x);
+#else
+    return __builtin_clz(x);
+#endif
+}
+STEPTH_HD int clz64(unsigned long long x) {  // x != 0
+#ifdef __CUDA_ARCH__
+    return __clzll((long long)x);
+#else
+    return __builtin_clzll(x);
+#endif
+}
+template <typename T>
+STEPTH_HD T ldg(const T *p) {
+#ifdef __CUDA_ARCH__
+    return __ldg(p);
+#else
+    return *p;
+#endif
+}
 
 // Per-query colour box.  The reference's predicate `v.substract(what).lt(precision)` (helpers.rs:35) is a
 // per-channel interval test for both supported PixelOpps readings:
@@ -32,14 +74,18 @@ __host__ __device__ __forceinline__ ColourBox make_box(uint32_t r, uint32_t g, u
     return ColourBox{lo, hi};
 }
 
-__device__ __forceinline__ bool box_contains(const ColourBox &bx, uint32_t r, uint32_t g, uint32_t b) {
+STEPTH_HD bool box_contains(const ColourBox &bx, uint32_t r, uint32_t g, uint32_t b) {
     return r >= (bx.lo & 0xff) && r <= (bx.hi & 0xff) && g >= ((bx.lo >> 8) & 0xff) && g <= ((bx.hi >> 8) & 0xff) &&
            b >= ((bx.lo >> 16) & 0xff) && b <= ((bx.hi >> 16) & 0xff);
 }
 
 // floor(sqrt(n)) for n < 2^24: what `((dx^2 + dy^2) as f64).sqrt() as u32` yields (helpers.rs:3-7).
-__device__ __forceinline__ uint32_t isqrt_u32(uint32_t n) {
+STEPTH_HD uint32_t isqrt_u32(uint32_t n) {
+#ifdef __CUDA_ARCH__
     uint32_t r = (uint32_t)__fsqrt_rn((float)n);
+#else
+    uint32_t r = (uint32_t)sqrtf((float)n);
+#endif
     while (r * r > n) --r;
     while ((r + 1) * (r + 1) <= n) ++r;
     return r;
@@ -54,7 +100,7 @@ __device__ __forceinline__ uint32_t isqrt_u32(uint32_t n) {
 //                               2(2s+1) + (2s-1) + (dy+s-1)  if dx == -s, |dy| < s (left column interior)
 // The first match in reference order is the matching pixel with the smallest key = (s << 12) | pos
 // (pos < 8s <= 4088 for s <= 511).  The search is therefore an arg-min and may visit pixels in ANY order.
-__device__ __forceinline__ uint32_t ring_key(int dx, int dy) {
+STEPTH_HD uint32_t ring_key(int dx, int dy) {
     int ax = dx < 0 ? -dx : dx, ay = dy < 0 ? -dy : dy;
     int s = ax > ay ? ax : ay;
     int pos;
@@ -65,7 +111,7 @@ __device__ __forceinline__ uint32_t ring_key(int dx, int dy) {
     return ((uint32_t)s << 12) | (uint32_t)pos;
 }
 
-__device__ __forceinline__ void key_to_offset(uint32_t key, int &dx, int &dy) {
+STEPTH_HD void key_to_offset(uint32_t key, int &dx, int &dy) {
     int s = (int)(key >> 12), pos = (int)(key & 0xfff);
     if (pos < 2 * s + 1) { dx = pos - s; dy = s; }
     else if (pos < 2 * (2 * s + 1)) { dx = pos - (2 * s + 1) - s; dy = -s; }
@@ -76,7 +122,7 @@ __device__ __forceinline__ void key_to_offset(uint32_t key, int &dx, int &dy) {
 constexpr uint32_t KEY_NONE = 0xffffffffu;
 
 // d as u8 of the winning offset (depth_image.rs:120-121): None -> 0, wraps mod 256
-__device__ __forceinline__ uint8_t key_to_d8(uint32_t key) {
+STEPTH_HD uint8_t key_to_d8(uint32_t key) {
     if (key == KEY_NONE) return 0;
     int dx, dy;
     key_to_offset(key, dx, dy);

@@ -1,0 +1,462 @@
+// search_hier.cuh -- K1: the production ring search (helpers.rs:9-54 + depth_image.rs:113-122), one thread per query.
+//
+// The reference walks ring s = 0, 1, .. around the origin as: row y+s, row y-s (x ascending), column x+s, column x-s
+// (y ascending) and returns the FIRST pixel inside the query's colour box.  That is an arg-min of the ring-order key
+// (common.cuh) over the matching pixels, so pixels may be visited in any order and whole regions without a match may be
+// skipped.  This kernel walks COARSE rings of 8x8-pixel tiles around the origin's tile (tiles.cuh):
+//
+//   * coarse ring S = the tiles at Chebyshev tile distance S.  Its four sides are read from the tile-occupancy planes,
+//     32 tiles per word (3 loads + 2 ANDs): a clear bit proves that the tile holds no match for this query's colour bins;
+//   * a flagged tile is tested on the fine planes: candidate word (3 x 8-byte loads, 64 probes), then the exact word
+//     (12 more loads) -- bit-exact without touching the pixels;
+//   * the first match inside a tile in reference order is found by bit tricks: the tile is cut by the two diagonals
+//     through the origin into the parts that belong to the bottom row / top row / right column / left column of their
+//     rings (corners go to the rows, helpers.rs:28-31); inside a part the ring-order key is monotone in (row, column) or
+//     (column, row), so the winner is a find-first-set on the row-major word or on its column fold;
+//   * every pixel of a tile at coarse ring S+1 lies at ring >= 8S+1, so the walk stops after coarse ring S as soon as the
+//     best key so far has ring <= 8S; a tile whose nearest pixel is farther than the best ring so far (or >= max) is skipped.
+//
+// Work per query is data dependent (most queries stop at ring 0; a few percent walk to the last ring), so the walk is
+// split: the NEAR kernel (one thread per main pixel / per block) does ring 0 and coarse rings 0..1 and appends what is
+// still open to a work list; the FAR kernel(s) resume the listed queries, 32 consecutive entries per warp, pulled with an
+// atomic cursor.  `d as u8` (depth_image.rs:120-121) and the per-pair maximum (:124) leave with the result.
+#pragma once
+#include <algorithm>
+
+#include "ctx.cuh"
+#include "search_literal.cuh"
+#include "tiles.cuh"
+
+namespace stepth {
+
+constexpr uint32_t KEY21_NONE = 0x1fffffu;  // work-list encoding of KEY_NONE (a real key has ring <= 511: 21 bits)
+constexpr uint32_t WL_MAX_PAIRS = 2048;     // pair index travels in the upper 11 bits of a work-list entry
+
+struct HierView {
+    const unsigned long long *fine;  // this pair's fine records
+    const uint32_t *crp, *ccp;       // this pair's coarse planes
+    int ntx, nty, nxw, nyw;
+};
+
+STEPTH_HD HierView make_view(const uint8_t *planes, const TileGeom &g, uint32_t pair) {
+    const uint8_t *base = planes + (size_t)pair * g.pair_bytes;
+    HierView v;
+    v.fine = reinterpret_cast<const unsigned long long *>(base);
+    v.crp = reinterpret_cast<const uint32_t *>(base + g.off_crp);
+    v.ccp = reinterpret_cast<const uint32_t *>(base + g.off_ccp);
+    v.ntx = (int)g.ntx; v.nty = (int)g.nty; v.nxw = (int)g.nxw; v.nyw = (int)g.nyw;
+    return v;
+}
+
+// ---- diagonal masks of an 8x8 tile (bit = ly * 8 + lx) ------------------------------------------------------------
+// diag_le(a) = { lx - ly <= a },  diag_ge(b) = { lx + ly >= b };  any integer a, b
+STEPTH_HD unsigned long long diag_le(int a) {
+    if (a >= 7) return ~0ull;
+    if (a < -7) return 0ull;
+    // row ly keeps lx <= a + ly: the low (a + ly + 1) bits of its byte
+    unsigned long long m = 0;
+#pragma unroll
+    for (int ly = 0; ly < 8; ++ly) {
+        int n = a + ly + 1;
+        n = n < 0 ? 0 : (n > 8 ? 8 : n);
+        m |= (unsigned long long)((1u << n) - 1u) << (8 * ly);
+    }
+    return m;
+}
+STEPTH_HD unsigned long long diag_ge(int b) {
+    if (b <= 0) return ~0ull;
+    if (b > 14) return 0ull;
+    // row ly keeps lx >= b - ly
+    unsigned long long m = 0;
+#pragma unroll
+    for (int ly = 0; ly < 8; ++ly) {
+        int n = b - ly;
+        n = n < 0 ? 0 : (n > 8 ? 8 : n);
+        m |= (unsigned long long)((0xffu << n) & 0xffu) << (8 * ly);
+    }
+    return m;
+}
+
+// tables of the two families for a in [-9, 7] and b in [0, 16]; the kernels keep them in shared memory
+constexpr int DIAG_N = 17;
+STEPTH_HD int diag_le_index(int a) { return (a < -9 ? -9 : (a > 7 ? 7 : a)) + 9; }
+STEPTH_HD int diag_ge_index(int b) { return b < 0 ? 0 : (b > 16 ? 16 : b); }
+
+// The first match (smallest ring-order key) among the set bits of tile mask m; (bx, by) = offset of the tile's pixel
+// (0,0) from the origin.  tab_le / tab_ge: the diagonal tables above.
+STEPTH_HD uint32_t tile_min_key(unsigned long long m, int bx, int by, const unsigned long long *tab_le,
+                                const unsigned long long *tab_ge) {
+    // pixel (lx, ly): dx = bx + lx, dy = by + ly.   dy >= dx <=> lx - ly <= by - bx;   dy >= -dx <=> lx + ly >= -(bx + by)
+    const int a = by - bx, b = -(bx + by);
+    const unsigned long long le = tab_le[diag_le_index(a)], lt = tab_le[diag_le_index(a - 1)];
+    const unsigned long long ge = tab_ge[diag_ge_index(b)], gt = tab_ge[diag_ge_index(b + 1)];
+    uint32_t best = KEY_NONE;
+    const unsigned long long mb = m & le & ge;       // bottom row of its ring: dy = s,  |dx| <= s   (origin included)
+    if (mb) {
+        const int i = ffs64(mb) - 1, ly = i >> 3, lx = i & 7;
+        const int s = by + ly, dx = bx + lx;
+        best = ((uint32_t)s << 12) | (uint32_t)(dx + s);
+    }
+    const unsigned long long mt = m & ~lt & ~gt;     // top row: dy = -s, |dx| <= s
+    if (mt) {
+        const int ly = (63 - clz64(mt)) >> 3;
+        const uint32_t row = (uint32_t)(mt >> (8 * ly)) & 0xffu;
+        const int lx = ffs32(row) - 1;
+        const int s = -(by + ly), dx = bx + lx;
+        const uint32_t k = ((uint32_t)s << 12) | (uint32_t)((2 * s + 1) + dx + s);
+        best = k < best ? k : best;
+    }
+    const unsigned long long mr = m & ~le & gt;      // right column: dx = s, |dy| < s
+    const unsigned long long ml = m & lt & ~ge;      // left column: dx = -s, |dy| < s
+    if (mr) {
+        uint32_t f = (uint32_t)mr | (uint32_t)(mr >> 32);
+        f |= f >> 16;
+        f |= f >> 8;
+        const int lx = ffs32(f & 0xffu) - 1;
+        const unsigned long long colbits = (mr >> lx) & 0x0101010101010101ull;
+        const int ly = (ffs64(colbits) - 1) >> 3;
+        const int s = bx + lx, dy = by + ly;
+        const uint32_t k = ((uint32_t)s << 12) | (uint32_t)(2 * (2 * s + 1) + (dy + s - 1));
+        best = k < best ? k : best;
+    }
+    if (ml) {
+        uint32_t f = (uint32_t)ml | (uint32_t)(ml >> 32);
+        f |= f >> 16;
+        f |= f >> 8;
+        const int lx = 31 - clz32(f & 0xffu);
+        const unsigned long long colbits = (ml >> lx) & 0x0101010101010101ull;
+        const int ly = (ffs64(colbits) - 1) >> 3;
+        const int s = -(bx + lx), dy = by + ly;
+        const uint32_t k = ((uint32_t)s << 12) | (uint32_t)(2 * (2 * s + 1) + (2 * s - 1) + (dy + s - 1));
+        best = k < best ? k : best;
+    }
+    return best;
+}
+
+// One query's walk over coarse rings [S0, S1).  Returns true when the answer is final (`best` = the first match in
+// reference order, or KEY_NONE); false when rings >= S1 still have to be walked.
+struct HierQuery {
+    int ox, oy;            // origin in the coordinates of the plane coverage (oy may lie outside it in a row band)
+    uint32_t col;          // r | g << 8 | b << 16
+    uint32_t jr, jg, jb;   // slot / bin of each channel
+};
+
+STEPTH_HD HierQuery make_query(int ox, int oy, uint32_t col) {
+    HierQuery q;
+    q.ox = ox; q.oy = oy; q.col = col;
+    q.jr = w_u(col & 0xffu);
+    q.jg = w_u((col >> 8) & 0xffu);
+    q.jb = w_u((col >> 16) & 0xffu);
+    return q;
+}
+
+STEPTH_HD void fine_test(const HierView &v, const HierQuery &q, int TX, int TY, int D, const unsigned long long *tab_le,
+                         const unsigned long long *tab_ge, uint32_t &best) {
+    const int bx = TX * 8 - q.ox, by = TY * 8 - q.oy;
+    const int dxm = bx > 0 ? bx : (bx + 7 < 0 ? -(bx + 7) : 0);
+    const int dym = by > 0 ? by : (by + 7 < 0 ? -(by + 7) : 0);
+    const int smin = dxm > dym ? dxm : dym;              // ring of the tile's nearest pixel
+    if (smin >= D || smin > (int)(best >> 12)) return;   // KEY_NONE >> 12 is larger than any ring
+    const unsigned long long *rec = v.fine + ((size_t)TY * v.ntx + TX) * T_REC;
+    unsigned long long m = ldg(rec + q.jr) & ldg(rec + T_SLOTS + q.jg) & ldg(rec + 2 * T_SLOTS + q.jb);
+    if (!m) return;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const uint32_t qc = (q.col >> (8 * c)) & 0xffu;
+        const unsigned long long *ch = rec + c * T_SLOTS;
+        m &= (ldg(ch + w_up1(qc)) | ldg(ch + w_nta(qc))) & (ldg(ch + w_um1(qc)) | ldg(ch + w_ntb(qc)));
+    }
+    if (!m) return;
+    const uint32_t k = tile_min_key(m, bx, by, tab_le, tab_ge);
+    if ((int)(k >> 12) < D && k < best) best = k;
+}
+
+STEPTH_HD bool hier_rings(const HierView &v, const HierQuery &q, int D, int S0, int S1, const unsigned long long *tab_le,
+                          const unsigned long long *tab_ge, uint32_t &best) {
+    const int T0x = q.ox >> 3, T0y = q.oy >> 3;  // arithmetic shift: floor for a negative oy
+    const int Smax = (D + 6) >> 3;               // tiles of coarse ring S start at ring >= 8S - 7
+    const int S_end = S1 < Smax + 1 ? S1 : Smax + 1;
+    for (int S = S0; S < S_end; ++S) {
+        // the coarse square has left the tile grid on all four sides: nothing further out exists
+        if (T0x - S < 0 && T0x + S >= v.ntx && T0y - S < 0 && T0y + S >= v.nty) return true;
+        if (S == 0) {
+            if ((unsigned)T0x < (unsigned)v.ntx && (unsigned)T0y < (unsigned)v.nty)
+                fine_test(v, q, T0x, T0y, D, tab_le, tab_ge, best);
+        } else {
+#pragma unroll 1
+            for (int side = 0; side < 4; ++side) {
+                const bool is_col = side >= 2;
+                const int line = (is_col ? T0x : T0y) + ((side & 1) ? -S : S);
+                const int n_lines = is_col ? v.ntx : v.nty, n = is_col ? v.nty : v.ntx;
+                if ((unsigned)line >= (unsigned)n_lines) continue;
+                const int c0 = is_col ? T0y : T0x;
+                int lo = is_col ? c0 - S + 1 : c0 - S, hi = is_col ? c0 + S - 1 : c0 + S;
+                lo = lo < 0 ? 0 : lo;
+                hi = hi > n - 1 ? n - 1 : hi;
+                if (lo > hi) continue;
+                const int w0 = lo >> 5, w1 = hi >> 5;
+                const uint32_t *cell = (is_col ? v.ccp : v.crp) + ((size_t)line * (is_col ? v.nyw : v.nxw) + w0) * C_CELL;
+                for (int w = w0; w <= w1; ++w, cell += C_CELL) {
+                    uint32_t m = ldg(cell + q.jr) & ldg(cell + NB + q.jg) & ldg(cell + 2 * NB + q.jb);
+                    if (w == w0) m &= 0xffffffffu << (lo & 31);
+                    if (w == w1) m &= 0xffffffffu >> (31 - (hi & 31));
+                    while (m) {
+                        const int p = (w << 5) + ffs32(m) - 1;
+                        m &= m - 1;
+                        fine_test(v, q, is_col ? line : p, is_col ? p : line, D, tab_le, tab_ge, best);
+                    }
+                }
+            }
+        }
+        if (best != KEY_NONE && (int)(best >> 12) <= 8 * S) return true;
+    }
+    return S1 > Smax;
+}
+
+#if defined(__CUDACC__)
+
+struct HierArgs {
+    SearchArgs s;
+    const uint8_t *planes;
+    TileGeom g;
+    // work lists: entry.x = query index inside its pair, entry.y = pair << 21 | key21
+    uint2 *wl_out;
+    uint32_t *wl_out_count;
+    const uint2 *wl_in;
+    const uint32_t *wl_in_count;
+    uint32_t *wl_in_cursor;
+    uint32_t wl_cap;   // entries wl_out can hold
+    int S0, S1;        // coarse rings this launch walks
+};
+
+__device__ __forceinline__ void load_diag_tables(unsigned long long *s_le, unsigned long long *s_ge) {
+    const int t = threadIdx.x;
+    if (t < DIAG_N) s_le[t] = diag_le(t - 9);
+    else if (t < 2 * DIAG_N) s_ge[t - DIAG_N] = diag_ge(t - DIAG_N);
+    __syncthreads();
+}
+
+// origin, colour and output slot of query `qi` of pair `pair` (depth_image.rs:114-118)
+template <bool BLOCKS>
+__device__ __forceinline__ void query_of(const SearchArgs &s, uint32_t pair, uint32_t qi, int &ox, int &oyg, uint32_t &col) {
+    if (BLOCKS) {
+        const stepth_block bl = s.blocks[qi];
+        ox = (int)((bl.x + bl.w) / 2);  // literal (pos + size) / 2, not the centre
+        oyg = (int)((bl.y + bl.h) / 2);
+        col = bl.value[0] | (bl.value[1] << 8) | (bl.value[2] << 16);
+    } else {
+        const uint32_t x = qi % s.w, y = qi / s.w;
+        ox = (int)((x + 1) >> 1);
+        oyg = (int)((y + s.y0 + 1) >> 1);
+        col = reinterpret_cast<const uint32_t *>(s.main_rgba)[(size_t)pair * s.n_queries + qi] & 0xffffffu;
+    }
+}
+
+__device__ __forceinline__ void publish_result(const SearchArgs &s, uint32_t pair, uint32_t qi, uint32_t key, bool active) {
+    uint32_t d = 0;
+    if (active) {
+        d = key == KEY_NONE ? 0u : (uint32_t)key_to_d8(key);
+        s.d8[(size_t)pair * s.n_queries + qi] = (uint8_t)d;
+    }
+    // per-pair maximum: lanes of a warp may belong to different pairs only in the far kernel; match on the pair there
+    const uint32_t mask = __activemask();
+    const uint32_t peers = __match_any_sync(mask, active ? pair : 0xffffffffu);
+    const uint32_t m = __reduce_max_sync(peers, d);
+    if (active && m && (threadIdx.x & 31) == (uint32_t)(__ffs(peers) - 1)) {
+        if (m > *(volatile uint32_t *)(s.max_out + pair)) atomicMax(s.max_out + pair, m);
+    }
+}
+
+// appends the still open queries of a warp to the work list (one atomic per warp)
+__device__ __forceinline__ void export_open(const HierArgs &a, bool open, uint32_t pair, uint32_t qi, uint32_t best) {
+    const uint32_t mask = __activemask();
+    const uint32_t bal = __ballot_sync(mask, open);
+    if (!bal) return;
+    const int lane = threadIdx.x & 31;
+    uint32_t base = 0;
+    if (lane == __ffs(bal) - 1) base = atomicAdd(a.wl_out_count, (uint32_t)__popc(bal));
+    base = __shfl_sync(mask, base, __ffs(bal) - 1);
+    if (open) {
+        const uint32_t slot = base + __popc(bal & ((1u << lane) - 1u));
+        if (slot < a.wl_cap)
+            a.wl_out[slot] = make_uint2(qi, (pair << 21) | (best == KEY_NONE ? KEY21_NONE : best));
+    }
+}
+
+// NEAR kernel: ring 0 (one pixel compare) and coarse rings [0, S1) for every query.
+// Dense mode: a warp owns an 8x4 patch of main pixels (= 4x2 origins: neighbouring queries share almost all loads), a
+// CTA 32x8 pixels.  Block mode: one thread per DiscretePixel, list order.
+template <bool BLOCKS>
+__global__ void __launch_bounds__(256) search_near_kernel(HierArgs a) {
+    __shared__ unsigned long long s_le[DIAG_N], s_ge[DIAG_N];
+    load_diag_tables(s_le, s_ge);
+    const SearchArgs &s = a.s;
+    const uint32_t pair = BLOCKS ? 0u : blockIdx.z;
+    const int tid = threadIdx.x;
+    bool valid;
+    uint32_t qi = 0;
+    if (BLOCKS) {
+        qi = blockIdx.x * 256u + tid;
+        valid = qi < s.n_queries;
+    } else {
+        const int lane = tid & 31, warp = tid >> 5;
+        const uint32_t X = blockIdx.x * 32u + (warp & 3) * 8u + (lane & 7);
+        const uint32_t Y = blockIdx.y * 8u + (warp >> 2) * 4u + (lane >> 3);
+        valid = X < s.w && Y < s.h;
+        qi = Y * s.w + X;
+    }
+    uint32_t key = KEY_NONE;
+    bool open = false;
+    if (valid) {
+        int ox, oyg;
+        uint32_t col;
+        query_of<BLOCKS>(s, pair, qi, ox, oyg, col);
+        const int src_wa = (int)s.wa, src_ha = (int)s.ha;
+        // ring 0 out of bounds => `still_in_bounds` stays false => break => None   (helpers.rs:49-51)
+        if (ox < src_wa && oyg < (int)s.add_img_h) {
+            const int oyl = oyg - (int)s.add_y0;  // origin row inside the sub-image held on this device
+            bool hit0 = false;
+            if (oyl >= 0 && oyl < src_ha) {
+                const uint8_t *px = s.add_rgb + (size_t)pair * src_ha * src_wa * 3 + ((size_t)oyl * src_wa + ox) * 3;
+                const ColourBox box = make_box(col & 0xff, (col >> 8) & 0xff, (col >> 16) & 0xff, s.pr, s.pg, s.pb, s.sat != 0);
+                hit0 = box_contains(box, px[0], px[1], px[2]);
+            }
+            if (hit0) {
+                key = 0;
+            } else if (s.max_rings > 1) {
+                const HierView v = make_view(a.planes, a.g, pair);
+                const HierQuery q = make_query(ox, oyl, col);
+                open = !hier_rings(v, q, (int)s.max_rings, 0, a.S1, s_le, s_ge, key);
+            }
+        }
+    }
+    export_open(a, open, pair, qi, key);
+    publish_result(s, pair, qi, key, valid && !open);
+}
+
+// FAR kernel: resumes the listed queries at coarse ring S0; a warp pulls 32 consecutive entries at a time.
+template <bool BLOCKS>
+__global__ void __launch_bounds__(128) search_far_kernel(HierArgs a) {
+    __shared__ unsigned long long s_le[DIAG_N], s_ge[DIAG_N];
+    load_diag_tables(s_le, s_ge);
+    const SearchArgs &s = a.s;
+    const int lane = threadIdx.x & 31;
+    const uint32_t n_entries = min(*a.wl_in_count, a.wl_cap);
+    for (;;) {
+        uint32_t e0 = 0;
+        if (lane == 0) e0 = atomicAdd(a.wl_in_cursor, 32u);
+        e0 = __shfl_sync(0xffffffffu, e0, 0);
+        if (e0 >= n_entries) break;
+        const uint32_t e = e0 + lane;
+        const bool valid = e < n_entries;
+        uint32_t pair = 0, qi = 0, key = KEY_NONE;
+        bool open = false;
+        if (valid) {
+            const uint2 ent = a.wl_in[e];
+            qi = ent.x;
+            pair = ent.y >> 21;
+            const uint32_t k21 = ent.y & KEY21_NONE;
+            key = k21 == KEY21_NONE ? KEY_NONE : k21;
+            int ox, oyg;
+            uint32_t col;
+            query_of<BLOCKS>(s, pair, qi, ox, oyg, col);
+            const HierView v = make_view(a.planes, a.g, pair);
+            const HierQuery q = make_query(ox, oyg - (int)s.add_y0, col);
+            open = !hier_rings(v, q, (int)s.max_rings, a.S0, a.S1, s_le, s_ge, key);
+        }
+        if (a.wl_out) export_open(a, open, pair, qi, key);
+        publish_result(s, pair, qi, key, valid && !open);
+    }
+}
+
+// planes (K0) + search (K1) for n_pairs dense pairs, or for one block list (a.blocks != nullptr)
+inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const SearchArgs &a, uint32_t n_pairs) {
+    if (a.wa > 0xffffu || a.add_img_h > 0xffffu)
+        return set_err(ctx, STEPTH_ERR_INVALID_ARG, "additional image larger than 65535 in one dimension");
+    if (n_pairs > WL_MAX_PAIRS)
+        return set_err(ctx, STEPTH_ERR_INVALID_ARG, "more than 2048 pairs in one launch");
+    HierArgs h;
+    memset(&h, 0, sizeof h);
+    h.s = a;
+    // planes only cover what a query can reach: dense origins are half-coordinates (depth_image.rs:114-117), so columns
+    // [0, w/2 + max_rings) and local rows [0, (y0+h)/2 + max_rings - add_y0) -- the rest of the image is never probed
+    uint32_t cover_w = a.wa, cover_h = a.ha;
+    if (!a.blocks) {
+        cover_w = (uint32_t)std::min<uint64_t>(a.wa, (uint64_t)a.w / 2 + a.max_rings);
+        const int64_t last_row = (int64_t)(a.y0 + a.h) / 2 + a.max_rings - 1 - (int64_t)a.add_y0;  // local, inclusive
+        cover_h = (uint32_t)std::max<int64_t>(1, std::min<int64_t>(a.ha, last_row + 1));
+    }
+    h.g = make_tile_geom(cover_w, cover_h, a.wa);
+    int32_t rc = ensure(ctx, ctx->planes, h.g.pair_bytes * n_pairs);
+    if (rc != STEPTH_OK) return rc;
+    h.planes = (const uint8_t *)ctx->planes.p;
+    if (h.g.nty > 65535u) return set_err(ctx, STEPTH_ERR_INVALID_ARG, "too many tile rows for one launch");
+    TileBuildArgs p{a.add_rgb, (size_t)a.ha * a.wa * 3, (uint8_t *)ctx->planes.p, h.g, a.pr, a.pg, a.pb, a.sat};
+    tile_planes_kernel<<<dim3(h.g.nxw, h.g.nty, n_pairs), 256, 0, st>>>(p);
+    ctx->launches++;
+    STEPTH_CUDA_TRY(ctx, cudaGetLastError());
+    coarse_transpose_kernel<<<dim3(h.g.nxw, h.g.nyw, n_pairs), 256, 0, st>>>(p);
+    ctx->launches++;
+    STEPTH_CUDA_TRY(ctx, cudaGetLastError());
+
+    // work lists: [count, cursor, pad ..][entries]; at most one entry per query
+    const size_t cap = (size_t)a.n_queries * n_pairs;
+    if (cap > 0xfffffff0ull) return set_err(ctx, STEPTH_ERR_INVALID_ARG, "more than 2^32 queries in one launch");
+    const size_t wl_bytes = 64 + cap * sizeof(uint2);
+    rc = ensure(ctx, ctx->worklist, 2 * wl_bytes);
+    if (rc != STEPTH_OK) return rc;
+    uint8_t *wl0 = (uint8_t *)ctx->worklist.p, *wl1 = wl0 + wl_bytes;
+    STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(wl0, 0, 64, st));
+    STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(wl1, 0, 64, st));
+    h.wl_cap = (uint32_t)cap;
+
+    // NEAR: ring 0 + coarse rings 0..1
+    h.S0 = 0;
+    h.S1 = ctx->near_rings;
+    h.wl_out = (uint2 *)(wl0 + 64);
+    h.wl_out_count = (uint32_t *)wl0;
+    if (a.blocks) {
+        search_near_kernel<true><<<dim3((a.n_queries + 255) / 256, 1, 1), 256, 0, st>>>(h);
+    } else {
+        const uint32_t gy = (a.h + 7) / 8;
+        if (gy > 65535u) return set_err(ctx, STEPTH_ERR_INVALID_ARG, "band taller than 524280 rows");
+        search_near_kernel<false><<<dim3((a.w + 31) / 32, gy, n_pairs), 256, 0, st>>>(h);
+    }
+    ctx->launches++;
+    STEPTH_CUDA_TRY(ctx, cudaGetLastError());
+
+    // FAR: one or two resumptions; the last one walks to the end
+    const int mid = ctx->mid_rings;
+    const uint32_t far_grid = (uint32_t)ctx->sm_count * 16;
+    uint8_t *in = wl0, *out = wl1;
+    if (mid > h.S1) {
+        h.S0 = h.S1;
+        h.S1 = mid;
+        h.wl_in = (const uint2 *)(in + 64);
+        h.wl_in_count = (const uint32_t *)in;
+        h.wl_in_cursor = (uint32_t *)in + 1;
+        h.wl_out = (uint2 *)(out + 64);
+        h.wl_out_count = (uint32_t *)out;
+        if (a.blocks) search_far_kernel<true><<<far_grid, 128, 0, st>>>(h);
+        else search_far_kernel<false><<<far_grid, 128, 0, st>>>(h);
+        ctx->launches++;
+        STEPTH_CUDA_TRY(ctx, cudaGetLastError());
+        std::swap(in, out);
+    }
+    h.S0 = h.S1;
+    h.S1 = 1 << 20;
+    h.wl_in = (const uint2 *)(in + 64);
+    h.wl_in_count = (const uint32_t *)in;
+    h.wl_in_cursor = (uint32_t *)in + 1;
+    h.wl_out = nullptr;
+    h.wl_out_count = nullptr;
+    if (a.blocks) search_far_kernel<true><<<far_grid, 128, 0, st>>>(h);
+    else search_far_kernel<false><<<far_grid, 128, 0, st>>>(h);
+    ctx->launches++;
+    STEPTH_CUDA_TRY(ctx, cudaGetLastError());
+    return STEPTH_OK;
+}
+
+#endif  // __CUDACC__
+
+}  // namespace stepth

@@ -8,9 +8,7 @@
 // There is no CPU fallback anywhere: without a usable sm_100 device every entry point returns STEPTH_ERR_CUDA.
 #include "ctx.cuh"
 #include "search_literal.cuh"
-#include "search_tiles.cuh"
-#include "search_origins.cuh"
-#include "search_tail.cuh"
+#include "search_hier.cuh"
 #include "tail.cuh"
 #include "brightness.cuh"
 
@@ -74,7 +72,8 @@ extern "C" int32_t stepth_cuda_ctx_create(int32_t device, stepth_ctx **ctx_out) 
     stepth_ctx *ctx = new stepth_ctx();
     ctx->device = device;
     ctx->sm_count = prop.multiProcessorCount;
-    if (const char *ev = getenv("STEPTH_EXPORT_BELOW")) ctx->export_below = (uint32_t)atoi(ev);  // tuning knob
+    if (const char *ev = getenv("STEPTH_NEAR_RINGS")) ctx->near_rings = std::max(1, atoi(ev));  // tuning knobs
+    if (const char *ev = getenv("STEPTH_MID_RINGS")) ctx->mid_rings = atoi(ev);
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
         g_create_err = std::string("cudaStreamCreate failed: ") + cudaGetErrorString(e);
         delete ctx;
@@ -113,7 +112,7 @@ extern "C" uint64_t stepth_cuda_launch_count(const stepth_ctx *ctx) { return ctx
 // ============================================================================================================
 static bool params_ok(const stepth_params *p) {
     if (!p) return false;
-    if (p->max_rings == 0 || p->max_rings > 512) return false;  // ring keys hold s <= 511 (common.cuh)
+    if (p->max_rings == 0 || p->max_rings > 511) return false;  // ring keys hold s <= 510 in 21 bits (common.cuh)
     if ((p->flags & STEPTH_RESAMPLE_MASK) == 3u) return false;
     return true;
 }
@@ -160,7 +159,7 @@ extern "C" int32_t stepth_cuda_dev_search_dense(stepth_ctx *ctx, void *stream, c
         LAUNCH_CHECK(ctx);
         return STEPTH_OK;
     }
-    return launch_search_tiles(ctx, st, a, s->n_pairs);
+    return launch_search_hier(ctx, st, a, s->n_pairs);
 }
 
 extern "C" int32_t stepth_cuda_dev_search_blocks(stepth_ctx *ctx, void *stream, const stepth_params *params,
@@ -191,7 +190,7 @@ extern "C" int32_t stepth_cuda_dev_search_blocks(stepth_ctx *ctx, void *stream, 
         LAUNCH_CHECK(ctx);
         return STEPTH_OK;
     }
-    return launch_search_tiles(ctx, st, a, 1);
+    return launch_search_hier(ctx, st, a, 1);
 }
 
 extern "C" int32_t stepth_cuda_dev_paint_blocks(stepth_ctx *ctx, void *stream, const stepth_block *blocks,

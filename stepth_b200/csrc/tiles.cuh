@@ -1,0 +1,200 @@
+// tiles.cuh -- K0: two-level match bit-planes of the additional image (8x8-pixel tiles + a tile-occupancy level).
+//
+// The match predicate of the reference, `v.substract(what).lt(precision)` (helpers.rs:35), is a per-channel interval
+// test  T(q) = [q - p + 1, q + p - 1]  (abs/all; sat/all: [0, q + p - 1]) on the pixel value v, q = the query's channel
+// value, p = `precision` -- the same p for every query of a call.  K0 turns the additional image into bit-planes from
+// which the search evaluates the predicate for 64 probes (one 8x8 tile) with a few 8-byte loads and ANDs.  Per channel,
+// with the query value split as q = 8 j + r:
+//
+//   U[j]    v in the UNION of T(q) over the bin q in [8j, 8j+7]:  max(0, 8j-p+1) <= v <= min(255, 8j+p+6)   j = -1 .. 32
+//   NTA[r]  ((v + p - 1) & 7) >= r        (all ones in sat mode)                                          r = 0 .. 7
+//   NTB[r]  ((v - p + 1) & 7) <= r                                                                        r = 0 .. 7
+//
+//   candidate(q) = U[j]                                    a superset of the matches: 3 loads + 2 ANDs per 64 probes
+//   exact(q)     = U[j] & (U[j+1] | NTA[r]) & (U[j-1] | NTB[r])
+//
+// Why exact: inside U[j] the pixels below T(q) are exactly those not in U[j+1] whose offset (v+p-1)&7 is < r, and the
+// pixels above T(q) are exactly those not in U[j-1] whose offset (v-p+1)&7 is > r (derivation in DESIGN.md).  Out-of-image
+// bits are 0 in every plane: the reference skips out-of-bounds probes (helpers.rs:19-25,44).
+//
+// FINE level (u64 words).  One record per 8x8 tile, 3 channels x 64 slots:
+//   slot 0..31 U[0..31] | 32 U[-1] | 33 U[32] | 34..41 NTA[0..7] | 42..49 NTB[0..7] | 50..63 unused (never written)
+//   F[((TY * ntx + TX) * 3 + c) * 64 + slot]      bit (ly * 8 + lx) <-> pixel (8 TX + lx, 8 TY + ly)
+// The 32 U words of one channel of one tile are 256 contiguous bytes: lanes that look at the same tile with different
+// query colours hit two 128-byte lines.
+//
+// COARSE level (u32 words): bit = "U[j] of channel c has at least one pixel in this tile", 32 tiles per word,
+//   row-major   CR[((TY * nxw + xw) * 3 + c) * 32 + j]   bit b <-> tile (32 xw + b, TY)      (row sides of a coarse ring)
+//   transposed  CC[((TX * nyw + yw) * 3 + c) * 32 + j]   bit b <-> tile (TX, 32 yw + b)      (column sides)
+// A tile whose three coarse bits are set for a query MAY hold a match; a tile with a clear bit cannot (superset).
+//
+// Algorithmic bytes per additional pixel: 3 read; 3 * 50 * 8 / 64 = 18.75 written (fine) + 0.4 (coarse).
+#pragma once
+#include "common.cuh"
+
+namespace stepth {
+
+constexpr int NB = 32;               // query-value bins per channel
+constexpr int QSHIFT = 3;            // log2(QSTEP)
+constexpr int QSTEP = 1 << QSHIFT;   // 8 levels per bin
+constexpr int T_SLOTS = 64;          // u64 slots per channel of a tile record
+constexpr int T_REC = 3 * T_SLOTS;   // u64 words per tile record (192 = 1536 bytes)
+constexpr int C_CELL = 3 * NB;       // u32 words per coarse cell (96 = 384 bytes)
+constexpr int W_UM1 = 32, W_UP32 = 33, W_NTA = 34, W_NTB = 42, W_USED = 50;
+static_assert(NB * QSTEP == 256 && NB == 32, "the layouts assume 32 bins of 8 levels");
+
+struct TileGeom {
+    uint32_t wa, ha;      // the part of the additional (sub-)image the planes cover: columns [0, wa), rows [0, ha)
+    uint32_t src_wa;      // row pitch (pixels) of the source image
+    uint32_t ntx, nty;    // tiles: ceil(wa/8), ceil(ha/8)
+    uint32_t nxw, nyw;    // coarse words per tile row / tile column: ceil(ntx/32), ceil(nty/32)
+    size_t fine_words;    // u64: ntx * nty * T_REC
+    size_t crp_words;     // u32: nty * nxw * C_CELL
+    size_t ccp_words;     // u32: ntx * nyw * C_CELL
+    size_t off_crp, off_ccp;  // byte offsets of the coarse sections inside one pair's block
+    size_t pair_bytes;    // bytes per pair (sections 256-byte aligned)
+};
+
+inline TileGeom make_tile_geom(uint32_t wa, uint32_t ha, uint32_t src_wa) {
+    TileGeom g;
+    g.wa = wa; g.ha = ha; g.src_wa = src_wa;
+    g.ntx = (wa + 7) / 8;
+    g.nty = (ha + 7) / 8;
+    g.nxw = (g.ntx + 31) / 32;
+    g.nyw = (g.nty + 31) / 32;
+    g.fine_words = (size_t)g.ntx * g.nty * T_REC;
+    g.crp_words = (size_t)g.nty * g.nxw * C_CELL;
+    g.ccp_words = (size_t)g.ntx * g.nyw * C_CELL;
+    auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    g.off_crp = up(g.fine_words * 8);
+    g.off_ccp = g.off_crp + up(g.crp_words * 4);
+    g.pair_bytes = g.off_ccp + up(g.ccp_words * 4);
+    return g;
+}
+
+// slot offsets (inside one channel of a tile record) a query value q needs
+STEPTH_HD uint32_t w_u(uint32_t q) { return q >> QSHIFT; }
+STEPTH_HD uint32_t w_um1(uint32_t q) { uint32_t j = q >> QSHIFT; return j ? j - 1 : (uint32_t)W_UM1; }
+STEPTH_HD uint32_t w_up1(uint32_t q) { uint32_t j = q >> QSHIFT; return j < NB - 1 ? j + 1 : (uint32_t)W_UP32; }
+STEPTH_HD uint32_t w_nta(uint32_t q) { return W_NTA + (q & (QSTEP - 1)); }
+STEPTH_HD uint32_t w_ntb(uint32_t q) { return W_NTB + (q & (QSTEP - 1)); }
+
+// membership of one pixel value in the 50 planes of its channel: lo = U[0..31], hi = bits 0..17 <-> slots 32..49
+STEPTH_HD void plane_bits(int v, int p, bool sat, bool valid, uint32_t &lo, uint32_t &hi) {
+    if (!valid) { lo = 0; hi = 0; return; }
+    // U[j] contains v  <=>  8j - p + 1 <= v (abs only)  and  v <= 8j + p + 6
+    int jb = sat ? NB : (v + p - 1) >> 3;            // largest j with 8j <= v + p - 1
+    const int ja = (v - p - 6 + 7) >> 3;              // smallest j with 8j >= v - p - 6 (arithmetic shift = floor)
+    // bits for j = 0 .. 31
+    uint32_t m_hi_side = jb >= 31 ? 0xffffffffu : (jb < 0 ? 0u : (0xffffffffu >> (31 - jb)));   // j <= jb
+    uint32_t m_lo_side = ja <= 0 ? 0xffffffffu : (ja > 31 ? 0u : (0xffffffffu << ja));          // j >= ja
+    lo = m_hi_side & m_lo_side;
+    uint32_t h = 0;
+    if (ja <= -1 && jb >= -1) h |= 1u;                // U[-1]:  v <= p - 2 (and, abs, -p - 7 <= v: always)
+    if (ja <= 32 && jb >= 32) h |= 2u;                // U[32]:  v >= 257 - p (abs) / always (sat); v <= 262 + p always
+    const uint32_t a = sat ? 7u : (uint32_t)((v + p - 1) & 7), b = (uint32_t)((v - p + 1) & 7);
+    h |= ((1u << (a + 1)) - 1u) << 2;                 // NTA[r]: r <= a
+    h |= ((0xffu << b) & 0xffu) << 10;                // NTB[r]: r >= b
+    hi = h;
+}
+
+#if defined(__CUDACC__)
+
+struct TileBuildArgs {
+    const uint8_t *add_rgb;   // [n_pairs, src_ha, src_wa, 3]
+    size_t src_pair_bytes;    // src_ha * src_wa * 3
+    uint8_t *planes;          // [n_pairs, pair_bytes]
+    TileGeom g;
+    uint32_t pr, pg, pb, sat;
+};
+
+// 32x32 bit-matrix transpose across the lanes of a warp: in: lane i holds row i; out: lane i holds column i
+__device__ __forceinline__ uint32_t warp_bit_transpose(uint32_t x, int lane) {
+#pragma unroll
+    for (int s = 0; s < 5; ++s) {
+        const int d = 16 >> s;
+        const uint32_t m = d == 16 ? 0x0000ffffu : d == 8 ? 0x00ff00ffu : d == 4 ? 0x0f0f0f0fu : d == 2 ? 0x33333333u : 0x55555555u;
+        const uint32_t y = __shfl_xor_sync(0xffffffffu, x, d);
+        x = (lane & d) ? (((y >> d) & m) | (x & ~m)) : ((x & m) | ((y << d) & ~m));
+    }
+    return x;
+}
+
+// One CTA per coarse row-major cell = 32 tiles along x of one tile row = a 256x8 pixel strip.  The strip is staged in
+// shared memory; every warp takes 4 tiles x 3 channels: each lane computes the plane membership of its pixel (rows 0-3,
+// then rows 4-7 of the tile), two warp bit transposes per half make lane j the owner of plane word j, and the stores are
+// 256 contiguous bytes (U) + 144 bytes (the 18 extra planes).  The coarse bits fall out as "word != 0".
+__global__ void __launch_bounds__(256) tile_planes_kernel(TileBuildArgs a) {
+    __shared__ uint8_t s_px[3][8][256 + 4];
+    __shared__ uint32_t s_coarse[C_CELL];
+    const uint32_t pair = blockIdx.z, xw = blockIdx.x, TY = blockIdx.y;
+    const uint32_t wa = a.g.wa, ha = a.g.ha;
+    const uint8_t *add = a.add_rgb + (size_t)pair * a.src_pair_bytes;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t x_base = xw * 256u, y_base = TY * 8u;
+    for (int i = tid; i < 8 * 768; i += 256) {
+        const int r = i / 768, k = i - r * 768;
+        const uint32_t x = x_base + k / 3, y = y_base + r;
+        uint8_t v = 0;
+        if (x < wa && y < ha) v = add[((size_t)y * a.g.src_wa + x_base) * 3 + k];
+        s_px[k % 3][r][k / 3] = v;
+    }
+    if (tid < C_CELL) s_coarse[tid] = 0;
+    __syncthreads();
+    uint8_t *pair_base = a.planes + (size_t)pair * a.g.pair_bytes;
+    unsigned long long *fine = reinterpret_cast<unsigned long long *>(pair_base);
+    const int prec[3] = {(int)a.pr, (int)a.pg, (int)a.pb};
+    const bool sat = a.sat != 0;
+    uint32_t cbits[3] = {0, 0, 0};  // lane j: coarse bits of U[j] for the warp's 4 tiles
+#pragma unroll 1
+    for (int t = 0; t < 4; ++t) {
+        const int tl = warp * 4 + t;                 // tile inside the cell
+        const uint32_t TX = xw * 32u + tl;
+        if (TX >= a.g.ntx) break;                    // warp-uniform
+        const int lx = lane & 7, ly = lane >> 3;
+        const bool col_ok = TX * 8u + lx < wa;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            uint32_t lo0, hi0, lo1, hi1;
+            plane_bits(s_px[c][ly][tl * 8 + lx], prec[c], sat, col_ok && y_base + ly < ha, lo0, hi0);
+            plane_bits(s_px[c][ly + 4][tl * 8 + lx], prec[c], sat, col_ok && y_base + ly + 4 < ha, lo1, hi1);
+            lo0 = warp_bit_transpose(lo0, lane);
+            lo1 = warp_bit_transpose(lo1, lane);
+            hi0 = warp_bit_transpose(hi0, lane);
+            hi1 = warp_bit_transpose(hi1, lane);
+            unsigned long long *rec = fine + (((size_t)TY * a.g.ntx + TX) * 3 + c) * T_SLOTS;
+            rec[lane] = (unsigned long long)lo0 | ((unsigned long long)lo1 << 32);
+            if (lane < W_USED - 32) rec[32 + lane] = (unsigned long long)hi0 | ((unsigned long long)hi1 << 32);
+            if (lo0 | lo1) cbits[c] |= 1u << tl;
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+        if (cbits[c]) atomicOr(&s_coarse[c * NB + lane], cbits[c]);
+    __syncthreads();
+    if (tid < C_CELL) {
+        uint32_t *crp = reinterpret_cast<uint32_t *>(pair_base + a.g.off_crp);
+        crp[((size_t)TY * a.g.nxw + xw) * C_CELL + tid] = s_coarse[tid];
+    }
+}
+
+// coarse row-major -> coarse transposed: one warp per (32x32 tile block, channel*32 + bin); lane r reads the word of tile
+// row 32 by + r, the warp transposes the 32x32 bit block, lane k writes the word of tile column 32 bx + k.
+__global__ void __launch_bounds__(256) coarse_transpose_kernel(TileBuildArgs a) {
+    const uint32_t pair = blockIdx.z, bx = blockIdx.x, by = blockIdx.y;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint8_t *pair_base = a.planes + (size_t)pair * a.g.pair_bytes;
+    const uint32_t *crp = reinterpret_cast<const uint32_t *>(pair_base + a.g.off_crp);
+    uint32_t *ccp = reinterpret_cast<uint32_t *>(pair_base + a.g.off_ccp);
+    for (int cj = warp; cj < C_CELL; cj += 8) {
+        const uint32_t TY = by * 32u + lane;
+        uint32_t x = TY < a.g.nty ? crp[((size_t)TY * a.g.nxw + bx) * C_CELL + cj] : 0u;
+        x = warp_bit_transpose(x, lane);
+        const uint32_t TX = bx * 32u + lane;
+        if (TX < a.g.ntx) ccp[((size_t)TX * a.g.nyw + by) * C_CELL + cj] = x;
+    }
+}
+
+#endif  // __CUDACC__
+
+}  // namespace stepth
