@@ -6,7 +6,7 @@
 // skipped.  This kernel walks COARSE rings of 8x8-pixel tiles around the origin's tile (tiles.cuh):
 //
 //   * coarse ring S = the tiles at Chebyshev tile distance S.  Its four sides are read from the tile-occupancy planes,
-//     32 tiles per word (3 loads + 2 ANDs): a clear bit proves that the tile holds no match for this query's colour bins;
+//     32 tiles per word (3 loads + 2 ANDs): a clear bit proves that the tile holds no match for this query's colour;
 //   * a flagged tile is tested on the fine planes: candidate word (3 x 8-byte loads, 64 probes), then the exact word
 //     (12 more loads) -- bit-exact without touching the pixels;
 //   * the first match inside a tile in reference order is found by bit tricks: the tile is cut by the two diagonals
@@ -138,7 +138,8 @@ STEPTH_HD uint32_t tile_min_key(unsigned long long m, int bx, int by, const unsi
 struct HierQuery {
     int ox, oy;            // origin in the coordinates of the plane coverage (oy may lie outside it in a row band)
     uint32_t col;          // r | g << 8 | b << 16
-    uint32_t jr, jg, jb;   // slot / bin of each channel
+    uint32_t jr, jg, jb;   // fine level: slot / bin of each channel
+    uint32_t cr, cg, cb;   // coarse level: word offset of each channel's exact-value plane inside a cell
 };
 
 STEPTH_HD HierQuery make_query(int ox, int oy, uint32_t col) {
@@ -147,6 +148,9 @@ STEPTH_HD HierQuery make_query(int ox, int oy, uint32_t col) {
     q.jr = w_u(col & 0xffu);
     q.jg = w_u((col >> 8) & 0xffu);
     q.jb = w_u((col >> 16) & 0xffu);
+    q.cr = col & 0xffu;
+    q.cg = C_Q + ((col >> 8) & 0xffu);
+    q.cb = 2 * C_Q + ((col >> 16) & 0xffu);
     return q;
 }
 
@@ -197,7 +201,7 @@ STEPTH_HD bool hier_rings(const HierView &v, const HierQuery &q, int D, int S0, 
                 const int w0 = lo >> 5, w1 = hi >> 5;
                 const uint32_t *cell = (is_col ? v.ccp : v.crp) + ((size_t)line * (is_col ? v.nyw : v.nxw) + w0) * C_CELL;
                 for (int w = w0; w <= w1; ++w, cell += C_CELL) {
-                    uint32_t m = ldg(cell + q.jr) & ldg(cell + NB + q.jg) & ldg(cell + 2 * NB + q.jb);
+                    uint32_t m = ldg(cell + q.cr) & ldg(cell + q.cg) & ldg(cell + q.cb);
                     if (w == w0) m &= 0xffffffffu << (lo & 31);
                     if (w == w1) m &= 0xffffffffu >> (31 - (hi & 31));
                     while (m) {

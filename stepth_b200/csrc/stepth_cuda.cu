@@ -112,7 +112,7 @@ extern "C" uint64_t stepth_cuda_launch_count(const stepth_ctx *ctx) { return ctx
 // ============================================================================================================
 static bool params_ok(const stepth_params *p) {
     if (!p) return false;
-    if (p->max_rings == 0 || p->max_rings > 511) return false;  // ring keys hold s <= 510 in 21 bits (common.cuh)
+    if (p->max_rings == 0 || p->max_rings > 512) return false;  // ring keys hold s <= 511 (common.cuh)
     if ((p->flags & STEPTH_RESAMPLE_MASK) == 3u) return false;
     return true;
 }

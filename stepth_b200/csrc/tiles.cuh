@@ -23,12 +23,15 @@
 // The 32 U words of one channel of one tile are 256 contiguous bytes: lanes that look at the same tile with different
 // query colours hit two 128-byte lines.
 //
-// COARSE level (u32 words): bit = "U[j] of channel c has at least one pixel in this tile", 32 tiles per word,
-//   row-major   CR[((TY * nxw + xw) * 3 + c) * 32 + j]   bit b <-> tile (32 xw + b, TY)      (row sides of a coarse ring)
-//   transposed  CC[((TX * nyw + yw) * 3 + c) * 32 + j]   bit b <-> tile (TX, 32 yw + b)      (column sides)
-// A tile whose three coarse bits are set for a query MAY hold a match; a tile with a clear bit cannot (superset).
+// COARSE level (u32 words): E_c[q] bit = "some pixel of this tile has channel c inside T(q)", one plane per exact query
+// value q = 0..255, 32 tiles per word,
+//   row-major   CR[((TY * nxw + xw) * 3 + c) * 256 + q]   bit b <-> tile (32 xw + b, TY)     (row sides of a coarse ring)
+//   transposed  CC[((TX * nyw + yw) * 3 + c) * 256 + q]   bit b <-> tile (TX, 32 yw + b)     (column sides)
+// A tile whose three coarse bits are set for a query MAY hold a match (the three channels may be satisfied by different
+// pixels); a tile with a clear bit cannot.  Per tile and channel E is the set of values present in the tile, dilated by
+// p - 1 on both sides (abs) / smeared upwards from min - (p - 1) (sat).
 //
-// Algorithmic bytes per additional pixel: 3 read; 3 * 50 * 8 / 64 = 18.75 written (fine) + 0.4 (coarse).
+// Algorithmic bytes per additional pixel: 3 read; 3 * 50 * 8 / 64 = 18.75 written (fine) + 2 * 3 * 256 / (8 * 64) = 3 (coarse).
 #pragma once
 #include "common.cuh"
 
@@ -39,7 +42,8 @@ constexpr int QSHIFT = 3;            // log2(QSTEP)
 constexpr int QSTEP = 1 << QSHIFT;   // 8 levels per bin
 constexpr int T_SLOTS = 64;          // u64 slots per channel of a tile record
 constexpr int T_REC = 3 * T_SLOTS;   // u64 words per tile record (192 = 1536 bytes)
-constexpr int C_CELL = 3 * NB;       // u32 words per coarse cell (96 = 384 bytes)
+constexpr int C_Q = 256;             // coarse planes per channel: one per exact query value
+constexpr int C_CELL = 3 * C_Q;      // u32 words per coarse cell (768 = 3072 bytes)
 constexpr int W_UM1 = 32, W_UP32 = 33, W_NTA = 34, W_NTB = 42, W_USED = 50;
 static_assert(NB * QSTEP == 256 && NB == 32, "the layouts assume 32 bins of 8 levels");
 
@@ -120,17 +124,51 @@ __device__ __forceinline__ uint32_t warp_bit_transpose(uint32_t x, int lane) {
     return x;
 }
 
+// ---- 512-bit shifts spread over the 16 lanes of a half warp (lane16 = word index, word 0 = bits 0..31) ------------------
+__device__ __forceinline__ uint32_t shl512(uint32_t x, int lane16, int nbits) {  // nbits warp-uniform, 0 <= nbits < 512
+    const int wsh = nbits >> 5, bsh = nbits & 31;
+    uint32_t hi = __shfl_up_sync(0xffffffffu, x, wsh, 16);
+    uint32_t lo = __shfl_up_sync(0xffffffffu, x, (wsh + 1) & 15, 16);
+    if (lane16 < wsh) hi = 0;
+    if (lane16 < wsh + 1) lo = 0;
+    return __funnelshift_l(lo, hi, bsh);
+}
+__device__ __forceinline__ uint32_t shr512(uint32_t x, int lane16, int nbits) {
+    const int wsh = nbits >> 5, bsh = nbits & 31;
+    uint32_t lo = __shfl_down_sync(0xffffffffu, x, wsh, 16);
+    uint32_t hi = __shfl_down_sync(0xffffffffu, x, (wsh + 1) & 15, 16);
+    if (lane16 + wsh > 15) lo = 0;
+    if (lane16 + wsh + 1 > 15) hi = 0;
+    return __funnelshift_r(lo, hi, bsh);
+}
+
+// E = { q : some value v of the set P satisfies v in T(q) }, P and E as 256-bit sets in words 0..7 of a half warp.
+//   abs: T(q) = [q - R, q + R]  ->  E[q] = OR_{s = 0..2R} P[q + R - s]   (window-OR by doubling, then a right shift by R)
+//   sat: T(q) = [0, q + R]      ->  the same with an unbounded window
+__device__ __forceinline__ uint32_t dilate_values(uint32_t x, int lane16, int R, bool sat) {
+    const int W = sat ? 512 : 2 * R + 1;  // window width, 1 <= W <= 512
+    int span = 1;                         // x covers the window [0, span)
+    while (2 * span <= W) {
+        x |= shl512(x, lane16, span);
+        span *= 2;
+    }
+    if (W > span) x |= shl512(x, lane16, W - span);
+    return shr512(x, lane16, R);
+}
+
 // One CTA per coarse row-major cell = 32 tiles along x of one tile row = a 256x8 pixel strip.  The strip is staged in
 // shared memory; every warp takes 4 tiles x 3 channels: each lane computes the plane membership of its pixel (rows 0-3,
 // then rows 4-7 of the tile), two warp bit transposes per half make lane j the owner of plane word j, and the stores are
-// 256 contiguous bytes (U) + 144 bytes (the 18 extra planes).  The coarse bits fall out as "word != 0".
+// 256 contiguous bytes (U) + 144 bytes (the 18 extra planes).  The coarse level: the set of values present in the tile
+// (warp OR-reductions) is dilated into E, 256 bits per (tile, channel); the CTA transposes the 32 tiles x 256 values of
+// a channel into 256 words of 32 tile bits and stores the cell with coalesced lines.
 __global__ void __launch_bounds__(256) tile_planes_kernel(TileBuildArgs a) {
     __shared__ uint8_t s_px[3][8][256 + 4];
-    __shared__ uint32_t s_coarse[C_CELL];
+    __shared__ uint32_t s_E[3][8][32];  // [channel][value word g][tile]: bit b <-> q = 32 g + b
     const uint32_t pair = blockIdx.z, xw = blockIdx.x, TY = blockIdx.y;
     const uint32_t wa = a.g.wa, ha = a.g.ha;
     const uint8_t *add = a.add_rgb + (size_t)pair * a.src_pair_bytes;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, lane16 = lane & 15;
     const uint32_t x_base = xw * 256u, y_base = TY * 8u;
     for (int i = tid; i < 8 * 768; i += 256) {
         const int r = i / 768, k = i - r * 768;
@@ -139,25 +177,26 @@ __global__ void __launch_bounds__(256) tile_planes_kernel(TileBuildArgs a) {
         if (x < wa && y < ha) v = add[((size_t)y * a.g.src_wa + x_base) * 3 + k];
         s_px[k % 3][r][k / 3] = v;
     }
-    if (tid < C_CELL) s_coarse[tid] = 0;
+    for (int i = tid; i < 3 * 8 * 32; i += 256) (&s_E[0][0][0])[i] = 0;
     __syncthreads();
     uint8_t *pair_base = a.planes + (size_t)pair * a.g.pair_bytes;
     unsigned long long *fine = reinterpret_cast<unsigned long long *>(pair_base);
     const int prec[3] = {(int)a.pr, (int)a.pg, (int)a.pb};
     const bool sat = a.sat != 0;
-    uint32_t cbits[3] = {0, 0, 0};  // lane j: coarse bits of U[j] for the warp's 4 tiles
 #pragma unroll 1
     for (int t = 0; t < 4; ++t) {
         const int tl = warp * 4 + t;                 // tile inside the cell
         const uint32_t TX = xw * 32u + tl;
         if (TX >= a.g.ntx) break;                    // warp-uniform
         const int lx = lane & 7, ly = lane >> 3;
-        const bool col_ok = TX * 8u + lx < wa;
+        const bool ok0 = TX * 8u + lx < wa && y_base + ly < ha, ok1 = TX * 8u + lx < wa && y_base + ly + 4 < ha;
+        uint32_t pw01 = 0, pw2 = 0;  // value-presence words: lanes 0-15 channel 0 | lanes 16-31 channel 1;  channel 2
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
+            const int v0 = s_px[c][ly][tl * 8 + lx], v1 = s_px[c][ly + 4][tl * 8 + lx];
             uint32_t lo0, hi0, lo1, hi1;
-            plane_bits(s_px[c][ly][tl * 8 + lx], prec[c], sat, col_ok && y_base + ly < ha, lo0, hi0);
-            plane_bits(s_px[c][ly + 4][tl * 8 + lx], prec[c], sat, col_ok && y_base + ly + 4 < ha, lo1, hi1);
+            plane_bits(v0, prec[c], sat, ok0, lo0, hi0);
+            plane_bits(v1, prec[c], sat, ok1, lo1, hi1);
             lo0 = warp_bit_transpose(lo0, lane);
             lo1 = warp_bit_transpose(lo1, lane);
             hi0 = warp_bit_transpose(hi0, lane);
@@ -165,20 +204,39 @@ __global__ void __launch_bounds__(256) tile_planes_kernel(TileBuildArgs a) {
             unsigned long long *rec = fine + (((size_t)TY * a.g.ntx + TX) * 3 + c) * T_SLOTS;
             rec[lane] = (unsigned long long)lo0 | ((unsigned long long)lo1 << 32);
             if (lane < W_USED - 32) rec[32 + lane] = (unsigned long long)hi0 | ((unsigned long long)hi1 << 32);
-            if (lo0 | lo1) cbits[c] |= 1u << tl;
+#pragma unroll
+            for (int g = 0; g < 8; ++g) {
+                uint32_t contrib = 0;
+                if (ok0 && (v0 >> 5) == g) contrib |= 1u << (v0 & 31);
+                if (ok1 && (v1 >> 5) == g) contrib |= 1u << (v1 & 31);
+                const uint32_t pg = __reduce_or_sync(0xffffffffu, contrib);
+                if (lane16 == g) {
+                    if (c == 0 && lane < 16) pw01 = pg;
+                    if (c == 1 && lane >= 16) pw01 = pg;
+                    if (c == 2) pw2 = pg;
+                }
+            }
+        }
+        // the precision differs per channel, so the three dilations are separate calls (warp-uniform shift counts)
+        const uint32_t e0 = dilate_values(pw01, lane16, prec[0] - 1, sat);   // lanes 0-15 carry channel 0
+        const uint32_t e1 = dilate_values(pw01, lane16, prec[1] - 1, sat);   // lanes 16-31 carry channel 1
+        const uint32_t e2 = dilate_values(pw2, lane16, prec[2] - 1, sat);    // both halves carry channel 2
+        if (lane16 < 8) {
+            if (lane < 16) { s_E[0][lane16][tl] = e0; s_E[2][lane16][tl] = e2; }
+            else s_E[1][lane16][tl] = e1;
         }
     }
-#pragma unroll
-    for (int c = 0; c < 3; ++c)
-        if (cbits[c]) atomicOr(&s_coarse[c * NB + lane], cbits[c]);
     __syncthreads();
-    if (tid < C_CELL) {
-        uint32_t *crp = reinterpret_cast<uint32_t *>(pair_base + a.g.off_crp);
-        crp[((size_t)TY * a.g.nxw + xw) * C_CELL + tid] = s_coarse[tid];
+    // 24 (channel, value word) blocks of 32 tiles x 32 values -> 32 values x 32 tiles
+    uint32_t *crp = reinterpret_cast<uint32_t *>(pair_base + a.g.off_crp) + ((size_t)TY * a.g.nxw + xw) * C_CELL;
+    for (int cg = warp; cg < 24; cg += 8) {
+        const int c = cg >> 3, g = cg & 7;
+        const uint32_t x = warp_bit_transpose(s_E[c][g][lane], lane);  // lane b: tile bits of q = 32 g + b
+        crp[c * C_Q + g * 32 + lane] = x;
     }
 }
 
-// coarse row-major -> coarse transposed: one warp per (32x32 tile block, channel*32 + bin); lane r reads the word of tile
+// coarse row-major -> coarse transposed: one warp per (32x32 tile block, channel*256 + value); lane r reads the word of tile
 // row 32 by + r, the warp transposes the 32x32 bit block, lane k writes the word of tile column 32 bx + k.
 __global__ void __launch_bounds__(256) coarse_transpose_kernel(TileBuildArgs a) {
     const uint32_t pair = blockIdx.z, bx = blockIdx.x, by = blockIdx.y;
