@@ -1,0 +1,204 @@
+"""Multi-GPU orchestration of the hot path: one process per GPU (`torch.distributed`), SURVEY.md 8(e).
+
+Two ways the path shards:
+
+* **pair batches** (BASELINE.json configs[3]): pairs are independent -> `shard_pairs` deals pair i to rank i % world;
+  no data-path collective at all.
+* **row bands of one giant pair** (configs[4]): rank r owns main rows [y0, y1).  Origins are half-coordinates
+  (depth_image.rs:114-117), so it needs additional rows [(y0+1)/2 - max, y1/2 + max] -- `band_plan`.  The path has
+  three real exchange steps, all tiny except the last:
+    1. all-reduce MAX of the normaliser (depth_image.rs:124): 1 u32 per pair;
+    2. the unit-scale Gaussian (:133) reads 3 rows across each seam: neighbours exchange 3-row halos of the raw
+       distance plane (all-gather of 6 edge rows per rank);
+    3. select_foreground (:220-223): all-reduce SUM of the 256-bin histogram; every rank then runs the same k-means;
+    4. optional all-gather of the depth bands when the assembled map must live on every GPU (NCCL over NVLink);
+       otherwise each band goes straight back to its rank's pinned host memory.
+
+`BandRunner` holds the exchange logic and is compute-agnostic: the product passes `DeviceStages` (the CUDA stage API,
+stepth_b200.device); the CPU test-suite passes a stand-in with the same four methods and runs the very same exchange
+code over `gloo` with world_size 2 (tests/test_bands_gloo.py).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import torch
+import torch.distributed as dist
+
+from . import _ffi
+
+HALO = 3  # rows of the Gaussian's support on each side (image 0.23.14: support 3.0 at unit scale)
+
+
+def shard_pairs(n_pairs: int, rank: int, world: int) -> list[int]:
+    """pair i -> rank i % world (config 4); every rank gets floor or ceil of n/world pairs"""
+    return list(range(rank, n_pairs, world))
+
+
+@dataclass(frozen=True)
+class Band:
+    rank: int
+    y0: int      # first main row of the band
+    y1: int      # one past the last main row
+    ay0: int     # first additional row the band can probe
+    ay1: int     # one past the last
+
+
+def band_plan(h: int, add_h: int, max_rings: int, world: int, align: int = 2) -> list[Band]:
+    """Cuts main rows [0, h) into `world` contiguous bands (multiples of `align` rows so that the two main rows that
+    share an origin row stay together where possible) and gives each the additional rows it can reach:
+    origin rows (y+1)/2 for y in [y0, y1) -> [(y0+1)/2, y1/2], widened by max_rings - 1 on both sides."""
+    if world < 1 or h < 1:
+        raise ValueError("need at least one rank and one row")
+    units = (h + align - 1) // align
+    bands = []
+    for r in range(world):
+        u0, u1 = units * r // world, units * (r + 1) // world
+        y0, y1 = min(h, u0 * align), min(h, u1 * align)
+        if y1 <= y0:
+            bands.append(Band(r, y0, y0, 0, 0))
+            continue
+        o0, o1 = (y0 + 1) // 2, y1 // 2          # first / last origin row (inclusive)
+        ay0 = max(0, o0 - (max_rings - 1))
+        ay1 = min(add_h, o1 + (max_rings - 1) + 1)
+        bands.append(Band(r, y0, y1, ay0, max(ay0, ay1)))
+    return bands
+
+
+class DeviceStages:
+    """The CUDA stage API (stepth_cuda_dev_*) behind the four calls BandRunner makes."""
+
+    def __init__(self, ctx):
+        self.ctx = ctx
+
+    def search(self, main_band, add_band, precision, max_rings, flags, y0, add_y0, add_img_h, img_h):
+        from . import device
+
+        return device.search_dense(self.ctx, main_band, add_band, precision, max_rings, flags & _ffi.FLAG_PIXELOPPS_SAT,
+                                   y0=y0, add_y0=add_y0, add_img_h=add_img_h, img_h=img_h)
+
+    def finish(self, src, mx, img_h, flags, src_y0, out_y0, out_rows, hist):
+        from . import device
+
+        return device.finish(self.ctx, src, mx, img_h, flags, src_y0=src_y0, out_y0=out_y0, out_rows=out_rows, hist=hist)
+
+    def depth_split(self, hist):
+        from . import device
+
+        return device.depth_split(self.ctx, hist, 2)
+
+    def mask_apply(self, depth, from_to, rgba):
+        from . import device
+
+        return device.mask_apply(self.ctx, depth, from_to, rgba, want_mask=True)
+
+
+class BandRunner:
+    """depth_image.rs:110-134 (+ fused tail) for ONE pair whose main rows are banded over the ranks of `group`."""
+
+    def __init__(self, stages, w: int, h: int, add_h: int, precision, max_rings: int, flags: int, group=None):
+        self.st = stages
+        self.w, self.h, self.add_h = int(w), int(h), int(add_h)
+        self.precision, self.max_rings, self.flags = list(precision), int(max_rings), int(flags)
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.plan = band_plan(self.h, self.add_h, self.max_rings, self.world)
+        self.band = self.plan[self.rank]
+
+    # ---- exchange steps ------------------------------------------------------------------------------------------
+    def _allreduce(self, t: torch.Tensor, op) -> torch.Tensor:
+        if self.world > 1:
+            dist.all_reduce(t, op=op, group=self.group)
+        return t
+
+    def exchange_halos(self, d8_band: torch.Tensor) -> tuple[torch.Tensor, int]:
+        """-> (raw distance rows [src_y0, src_y0 + rows) = own band plus up to 3 rows of each neighbour, src_y0)."""
+        b = self.band
+        n, rows, w = d8_band.shape
+        if self.world == 1:
+            return d8_band, b.y0
+        # every rank contributes its first and last HALO rows (zero-padded when the band is shorter)
+        edge = torch.zeros((2, n, HALO, w), dtype=torch.uint8, device=d8_band.device)
+        k = min(HALO, rows)
+        if k:
+            edge[0, :, :k] = d8_band[:, :k]
+            edge[1, :, HALO - k:] = d8_band[:, rows - k:]
+        edges = [torch.empty_like(edge) for _ in range(self.world)]
+        dist.all_gather(edges, edge, group=self.group)
+        # rows above: walk up through the previous ranks' LAST rows until HALO rows are collected (bands may be short)
+        above, below = [], []
+        need = min(HALO, b.y0)
+        r = self.rank - 1
+        while need > 0 and r >= 0:
+            have = min(HALO, self.plan[r].y1 - self.plan[r].y0, need)
+            if have:
+                above.insert(0, edges[r][1][:, HALO - have:])
+                need -= have
+            r -= 1
+        need = min(HALO, self.h - b.y1)
+        r = self.rank + 1
+        while need > 0 and r < self.world:
+            have = min(HALO, self.plan[r].y1 - self.plan[r].y0, need)
+            if have:
+                below.append(edges[r][0][:, :have])
+                need -= have
+            r += 1
+        parts = above + [d8_band] + below
+        src = torch.cat(parts, dim=1).contiguous() if len(parts) > 1 else d8_band
+        src_y0 = b.y0 - sum(p.shape[1] for p in above)
+        return src, src_y0
+
+    # ---- the path ---------------------------------------------------------------------------------------------------
+    def run(self, main_band: torch.Tensor, add_band: torch.Tensor, gather_depth: bool = False) -> dict:
+        """main_band [1, y1-y0, w, 4], add_band [1, ay1-ay0, wa, 3] of THIS rank (see `band_plan`).
+        Returns depth_band [1, rows, w] (+ mask_band, rgba_band, from_to when the tail is fused; + depth [1, h, w]
+        on every rank when gather_depth)."""
+        b, f = self.band, self.flags
+        dev = main_band.device
+        rows = b.y1 - b.y0
+        if rows > 0:
+            d8, mx = self.st.search(main_band, add_band, self.precision, self.max_rings, f, b.y0, b.ay0, self.add_h, self.h)
+            mx = mx.to(torch.int32)
+        else:
+            d8 = torch.empty((1, 0, self.w), dtype=torch.uint8, device=dev)
+            mx = torch.zeros(1, dtype=torch.int32, device=dev)
+        mx = self._allreduce(mx, dist.ReduceOp.MAX)                      # exchange 1: the normaliser
+        src, src_y0 = self.exchange_halos(d8)                            # exchange 2: 3-row halos
+        want_fg = bool(f & _ffi.FLAG_FOREGROUND)
+        hist = torch.zeros((1, 256), dtype=torch.int32, device=dev) if want_fg else None
+        out = {}
+        if rows > 0:
+            depth, status = self.st.finish(src, mx, self.h, f & (_ffi.RESAMPLE_U8 | _ffi.RESAMPLE_F32 | _ffi.FLAG_INVERT),
+                                           src_y0, b.y0, rows, hist)
+        else:
+            depth = torch.empty((1, 0, self.w), dtype=torch.uint8, device=dev)
+            status = torch.zeros(1, dtype=torch.int32, device=dev)
+        # max == 0 is a property of the whole image: every rank sees the same all-reduced value
+        out["status"] = _ffi.ERR_DIV_BY_ZERO_MAX if int(mx[0]) == 0 else int(status[0]) if rows > 0 else 0
+        out["depth_band"] = depth
+        if want_fg and out["status"] == 0:
+            hist = self._allreduce(hist, dist.ReduceOp.SUM)              # exchange 3: the histogram
+            ranges, n_out, st2 = self.st.depth_split(hist)
+            out["status"] = int(st2[0])
+            if out["status"] == 0:
+                out["from_to"] = (int(ranges[0, 0]), int(ranges[0, 1]))
+                if rows > 0:
+                    rgba = main_band if f & _ffi.FLAG_APPLY else None
+                    mask, rgba_out = self.st.mask_apply(depth, ranges, rgba)
+                    out["mask_band"], out["rgba_band"] = mask, rgba_out
+        if gather_depth:                                                 # exchange 4: assemble the map everywhere
+            out["depth"] = self.gather_bands(depth)
+        return out
+
+    def gather_bands(self, band: torch.Tensor) -> torch.Tensor:
+        """all-gather of (possibly unequal) row bands -> [n, h, w] on every rank"""
+        if self.world == 1:
+            return band
+        n, _, w = band.shape
+        max_rows = max(p.y1 - p.y0 for p in self.plan)
+        padded = torch.zeros((n, max_rows, w), dtype=band.dtype, device=band.device)
+        padded[:, : band.shape[1]] = band
+        parts = [torch.empty_like(padded) for _ in range(self.world)]
+        dist.all_gather(parts, padded, group=self.group)
+        return torch.cat([parts[p.rank][:, : p.y1 - p.y0] for p in self.plan], dim=1).contiguous()
