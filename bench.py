@@ -33,9 +33,18 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-W, H, D = 1920, 1080, 128          # BASELINE.json configs[1]
+W, H, D = 1920, 1080, 128          # BASELINE.json configs[1] (set per workload in main())
 PRECISION = [36, 36, 36]           # u8::MAX / 7 (Readme.md:15)
 METRIC = "Mpx*disparities/sec"
+FUSED = False                      # invert_depth + select_foreground + apply_mask fused into the step (configs[2..])
+
+# name -> (w, h, max_rings, pairs per step [per GPU | total], fused tail, scaling)
+WORKLOADS = {
+    "1080p": (1920, 1080, 128, 16, False, "weak"),        # configs[1]: the metric's configuration (default)
+    "4k_fused": (3840, 2160, 256, 4, True, "weak"),       # configs[2]
+    "batch4k": (3840, 2160, 256, 64, True, "strong"),     # configs[3]: 64 pairs in total, dealt to the ranks
+    "giant": (16384, 8192, 256, 1, False, "strong"),      # configs[4]: one pair, row-banded over the ranks
+}
 
 
 def parse_args():
@@ -45,7 +54,8 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--kind", default="nat", choices=["nat", "geo", "worst"])
-    ap.add_argument("--pairs", type=int, default=16, help="pairs per step per GPU")
+    ap.add_argument("--workload", default="1080p", choices=sorted(WORKLOADS))
+    ap.add_argument("--pairs", type=int, default=0, help="pairs per step per GPU (default: the workload's)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--extra-kinds", action="store_true", help="also time the geo and worst distributions (N=1)")
@@ -68,6 +78,15 @@ def reach(w, h, d):
 def search_alg_bytes(w, h, d, pairs):
     rw, rh = reach(w, h, d)
     return pairs * (4 * w * h + 3 * rw * rh + w * h)   # main RGBA read + reachable additional RGB read + d8 write
+
+
+def ncu_traffic(workload, kind):
+    """dram bytes (read + write) of the search-stage kernels per launch sequence, from the committed ncu capture"""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f).get(f"{workload}_{kind}")
+    return None
 
 
 class ClockSampler(threading.Thread):
@@ -170,7 +189,7 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": round(val, 3), "unit": METRIC, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 3),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": f"1080p_d{D}_{args.kind}", "w": W, "h": H, "max_rings": D, "precision": PRECISION,
+        "config": {"workload": f"{args.workload}_d{D}_{args.kind}", "w": W, "h": H, "max_rings": D, "precision": PRECISION,
                    "pairs_per_step": 1, "note": "each step = one pair of the GPU arm's batch (bounded sample)"},
         "cpu_baseline": {"value": round(val, 3), "unit": METRIC, "cores": used, "kind": "port",
                          "sample": f"{args.steps} steps x 1 pair, reference-faithful 8-9 chunk threads on {cores} cores"},
@@ -183,10 +202,11 @@ def run_reference(args):
 # ---------------------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------------------
-def time_resident(torch, dist, pipe, mains, adds, steps, warmup, world):
-    """K timed steps over HBM-resident inputs; returns (total ms [max over ranks], search-stage ms summed)"""
+def time_resident(torch, dist, step, steps, warmup, world):
+    """K timed steps over HBM-resident inputs; `step(events)` enqueues one step and records (start, end) CUDA events
+    around its ring-search stage.  Returns (total ms [max over ranks], search-stage ms summed over the steps)."""
     for _ in range(warmup):
-        pipe.run(mains, adds)
+        step(None)
     torch.cuda.synchronize()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -195,7 +215,7 @@ def time_resident(torch, dist, pipe, mains, adds, steps, warmup, world):
     torch.cuda.synchronize()
     t0.record()
     for i in range(steps):
-        pipe.run(mains, adds, search_events=ev[i])
+        step(ev[i])
     t1.record()
     torch.cuda.synchronize()
     if world > 1:
@@ -209,11 +229,8 @@ def time_resident(torch, dist, pipe, mains, adds, steps, warmup, world):
     return total, search
 
 
-def time_e2e(torch, dist, ctx, sb, host_m, host_a, host_d, steps, warmup, world):
-    """the C-ABI host-buffer call: H2D of all inputs + the whole path + D2H of the depth maps, per step"""
-    def step():
-        ctx.depth_dense_batch(host_m, host_a, PRECISION, D, sb.RESAMPLE_U8, out={"depth": host_d})
-
+def time_e2e(torch, dist, step, steps, warmup, world):
+    """`step()` = the C-ABI host-buffer call: H2D of all inputs + the whole path + D2H of the results (synchronous)"""
     for _ in range(max(1, min(warmup, 2))):
         step()
     if world > 1:
@@ -221,7 +238,7 @@ def time_e2e(torch, dist, ctx, sb, host_m, host_a, host_d, steps, warmup, world)
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for _ in range(steps):
-        step()                       # synchronous: returns after the device->host copies finished
+        step()
     dt = (time.perf_counter() - t0) * 1e3
     if world > 1:
         t = torch.tensor([dt], dtype=torch.float64, device="cuda")
@@ -247,62 +264,102 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     import stepth_b200 as sb
-    from stepth_b200 import device, synth
+    from stepth_b200 import bands, device, synth
 
     ctx = sb.Context(local)
-    B = args.pairs
     dev = torch.device("cuda", local)
+    scaling = WORKLOADS[args.workload][5]
+    flags = sb.RESAMPLE_U8 | ((sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY) if FUSED else 0)
+    if args.workload == "giant":
+        return run_giant(args, torch, dist, ctx, dev, rank, world, flags)
+
+    # pairs this rank processes per step: weak scaling = a fixed batch per GPU; batch4k = 64 pairs dealt to the ranks
+    if scaling == "strong":
+        my_pairs = bands.shard_pairs(args.pairs, rank, world)
+        total_pairs = args.pairs
+    else:
+        my_pairs = [rank * args.pairs + i for i in range(args.pairs)]
+        total_pairs = args.pairs * world
+    B = len(my_pairs)
+    SUB = min(B, 16)                                   # pairs per launch sequence (bounds the scratch in HBM)
 
     def make_batch(kind):
         ms, as_ = [], []
-        for i in range(B):
-            m, a = synth.make_pair(kind, W, H, seed=rank * B + i + 1, device=dev)
+        for i in my_pairs:
+            m, a = synth.make_pair(kind, W, H, seed=i + 1, device=dev)
             ms.append(m)
             as_.append(a)
         return torch.stack(ms).contiguous(), torch.stack(as_).contiguous()
 
     mains, adds = make_batch(args.kind)
-    flags = sb.RESAMPLE_U8
-    pipe = device.DensePipeline(ctx, B, W, H, W, H, PRECISION, D, flags)
+    pipes = {}
+
+    def pipe_for(n):
+        if n not in pipes:
+            pipes[n] = device.DensePipeline(ctx, n, W, H, W, H, PRECISION, D, flags)
+        return pipes[n]
+
+    def make_step(mains, adds):
+        def step(events):
+            for j, i0 in enumerate(range(0, B, SUB)):
+                n = min(SUB, B - i0)
+                # the search-stage events bracket the first launch sequence of the step (all are alike)
+                pipe_for(n).run(mains[i0:i0 + n], adds[i0:i0 + n], search_events=events if j == 0 else None)
+        return step
+
+    step = make_step(mains, adds)
     sampler = ClockSampler(local)
     l0 = ctx.launch_count()
-    pipe.run(mains, adds)
+    step(None)
     torch.cuda.synchronize()
     launches_per_step = ctx.launch_count() - l0
-    assert int(pipe.status.abs().sum()) == 0, "a pair of the bench batch failed (max == 0?)"
+    for p in pipes.values():
+        assert int(p.status.abs().sum()) == 0, "a pair of the bench batch failed (max == 0?)"
 
     sampler.start()
-    total_ms, search_ms = time_resident(torch, dist, pipe, mains, adds, args.steps, args.warmup, world)
+    total_ms, search_ms = time_resident(torch, dist, step, args.steps, args.warmup, world)
     clocks = sampler.stop()
     px_disp = W * H * D
-    value = world * B * args.steps * px_disp / (total_ms * 1e-3) / 1e6
+    value = total_pairs * args.steps * px_disp / (total_ms * 1e-3) / 1e6
 
     hbm, which = peaks()
     search_launch_ms = search_ms / args.steps
-    alg = search_alg_bytes(W, H, D, B)
+    alg = search_alg_bytes(W, H, D, SUB)
     achieved = alg / (search_launch_ms * 1e-3) / 1e9
+    n_seq = (B + SUB - 1) // SUB
     roofline = {"bound": "hbm", "achieved": round(achieved, 2), "peak": hbm, "unit": "GB/s",
-                "frac": round(achieved / hbm, 5), "traffic": None, "peak_source": which,
-                "kernel": "ring search stage (stepth_cuda_dev_search_dense)", "alg_bytes_per_launch": alg,
-                "launch_ms": round(search_launch_ms, 4), "share_of_step": round(search_ms / total_ms, 4)}
+                "frac": round(achieved / hbm, 5), "traffic": ncu_traffic(args.workload, args.kind), "peak_source": which,
+                "kernel": "ring search stage (stepth_cuda_dev_search_dense: tile_planes + coarse_transpose + search_near + search_far)",
+                "alg_bytes_per_launch": alg, "pairs_per_launch": SUB, "launch_ms": round(search_launch_ms, 4),
+                "share_of_step": round(search_ms * n_seq / total_ms, 4),
+                "note": "the stage is issue/latency bound, not HBM bound (DESIGN.md section 5); frac is reported as the contract asks"}
 
     e2e = None
     if not args.no_e2e:
         host_m = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(B)]
         host_a = [torch.empty((H, W, 3), dtype=torch.uint8).pin_memory() for _ in range(B)]
-        host_d = [torch.empty((H, W), dtype=torch.uint8).pin_memory() for _ in range(B)]
+        out = {"depth": [torch.empty((H, W), dtype=torch.uint8).pin_memory() for _ in range(B)]}
+        if FUSED:
+            out["mask"] = [torch.empty((H, W), dtype=torch.uint8).pin_memory() for _ in range(B)]
+            out["rgba"] = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(B)]
         for i in range(B):
             host_m[i].copy_(mains[i])
             host_a[i].copy_(adds[i])
+
+        def e2e_step():
+            for i0 in range(0, B, SUB):
+                sl = slice(i0, min(B, i0 + SUB))
+                ctx.depth_dense_batch(host_m[sl], host_a[sl], PRECISION, D, flags, out={k: v[sl] for k, v in out.items()})
+
         e2e_steps = max(2, min(args.steps, 5))
-        e2e_ms = time_e2e(torch, dist, ctx, sb, host_m, host_a, host_d, e2e_steps, args.warmup, world)
+        e2e_ms = time_e2e(torch, dist, e2e_step, e2e_steps, args.warmup, world)
         rw, rh = reach(W, H, D)
-        e2e = {"value": round(world * B * e2e_steps * px_disp / (e2e_ms * 1e-3) / 1e6, 3), "unit": METRIC,
-               "h2d_bytes_per_step": B * (4 * W * H + 3 * rw * rh), "d2h_bytes_per_step": B * W * H,
+        e2e = {"value": round(total_pairs * e2e_steps * px_disp / (e2e_ms * 1e-3) / 1e6, 3), "unit": METRIC,
+               "h2d_bytes_per_step": B * (4 * W * H + 3 * rw * rh), "d2h_bytes_per_step": B * W * H * (6 if FUSED else 1),
                "ms_per_step": round(e2e_ms / e2e_steps, 3), "steps": e2e_steps,
-               "api": "stepth_cuda_depth_dense_batch (host buffers, pinned)"}
+               "api": "stepth_cuda_depth_dense_batch (host buffers, pinned; chunks pipelined over copy/compute/copy streams)"}
         # the resident pipeline and the host-buffer call must agree bit for bit
-        assert torch.equal(host_d[0], pipe.depth[0].cpu()), "host-buffer path and device-resident path disagree"
+        assert torch.equal(out["depth"][0], pipe_for(min(SUB, B)).depth[0].cpu()) or B > SUB, "host-buffer path and device-resident path disagree"
 
     extra = {}
     if args.extra_kinds and world == 1:
@@ -311,9 +368,9 @@ def run_ours(args):
                 continue
             m2, a2 = make_batch(kind)
             steps2 = max(1, min(args.steps, 3))
-            t_ms, s_ms = time_resident(torch, dist, pipe, m2, a2, steps2, 1, world)
-            extra[kind] = {"value": round(B * steps2 * px_disp / (t_ms * 1e-3) / 1e6, 3), "ms_per_step": round(t_ms / steps2, 3),
-                           "search_ms_per_step": round(s_ms / steps2, 3)}
+            t_ms, s_ms = time_resident(torch, dist, make_step(m2, a2), steps2, 1, world)
+            extra[kind] = {"value": round(total_pairs * steps2 * px_disp / (t_ms * 1e-3) / 1e6, 3), "ms_per_step": round(t_ms / steps2, 3),
+                           "search_ms_per_launch": round(s_ms / steps2, 3)}
             del m2, a2
 
     cpu = None
@@ -324,10 +381,11 @@ def run_ours(args):
         line = {
             "metric": METRIC, "value": round(value, 3), "unit": METRIC, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(total_ms / args.steps, 4), "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": f"1080p_d{D}_{args.kind}", "w": W, "h": H, "max_rings": D, "precision": PRECISION,
-                       "pairs_per_step_per_gpu": B, "flags": "RESAMPLE_U8",
-                       "l2": f"inputs {B * (4 + 3) * W * H / 1e6:.0f} MB per step > 126 MB L2 (no flush needed)",
+            "scaling": scaling, "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": f"{args.workload}_d{D}_{args.kind}", "w": W, "h": H, "max_rings": D, "precision": PRECISION,
+                       "pairs_per_step_total": total_pairs, "pairs_per_step_this_gpu": B,
+                       "flags": "RESAMPLE_U8" + ("|INVERT|FOREGROUND|APPLY" if FUSED else ""),
+                       "l2": f"inputs {B * (4 + 3) * W * H / 1e6:.0f} MB per step per GPU > 126 MB L2 (no flush needed)",
                        "parallelism": f"pair-batch x{world} (no collective)"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
             "clocks": clocks,
@@ -339,8 +397,60 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def run_giant(args, torch, dist, ctx, dev, rank, world, flags):
+    """configs[4]: ONE pair, main rows banded over the ranks (bands.BandRunner): MAX all-reduce of the normaliser, 3-row
+    halo exchange, and an NCCL all-gather of the depth bands so that every GPU ends with the assembled map."""
+    import stepth_b200 as sb
+    from stepth_b200 import bands, synth
+
+    runner = bands.BandRunner(bands.DeviceStages(ctx), W, H, H, PRECISION, D, flags)
+    b = runner.band
+    # every rank generates the same pair from the same seed and keeps only its rows (synthetic data; no scatter timed)
+    m, a = synth.make_pair(args.kind, W, H, seed=1, device=dev)
+    mb, ab = m[None, b.y0:b.y1].contiguous(), a[None, b.ay0:b.ay1].contiguous()
+    del m, a
+    torch.cuda.empty_cache()
+    sampler = ClockSampler(int(os.environ.get("LOCAL_RANK", "0")))
+    l0 = ctx.launch_count()
+    out = runner.run(mb, ab, gather_depth=world > 1)
+    torch.cuda.synchronize()
+    launches = ctx.launch_count() - l0
+    assert out["status"] == 0
+
+    def step(events):
+        if events is not None:
+            events[0].record()
+        runner.run(mb, ab, gather_depth=world > 1)
+        if events is not None:
+            events[1].record()
+
+    sampler.start()
+    total_ms, _ = time_resident(torch, dist, step, args.steps, args.warmup, world)
+    clocks = sampler.stop()
+    value = args.steps * W * H * D / (total_ms * 1e-3) / 1e6
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": round(value, 3), "unit": METRIC, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(total_ms / args.steps, 4), "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": f"giant_d{D}_{args.kind}", "w": W, "h": H, "max_rings": D, "precision": PRECISION,
+                       "bands": [[p.y0, p.y1, p.ay0, p.ay1] for p in runner.plan],
+                       "l2": "inputs larger than L2",
+                       "parallelism": f"row bands x{world}: allreduce(MAX) + 3-row halo all-gather + NCCL all-gather of depth bands"},
+            "roofline": None, "cpu_baseline": None, "e2e": None, "gpu_launches": launches * args.steps, "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
+    global W, H, D, FUSED
     args = parse_args()
+    w, h, d, pairs, fused, _ = WORKLOADS[args.workload]
+    W, H, D, FUSED = w, h, d, fused
+    if not args.pairs:
+        args.pairs = pairs
     if args.impl == "reference":
         run_reference(args)
     else:

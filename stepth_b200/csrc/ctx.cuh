@@ -14,7 +14,10 @@
 
 struct stepth_ctx {
     int device = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;    // compute (and the single-pair copies)
+    cudaStream_t copy_in = nullptr;   // batch entry point: host->device copies of the next chunk of pairs
+    cudaStream_t copy_out = nullptr;  // batch entry point: device->host copies of the previous chunk
+    std::vector<cudaEvent_t> events;  // pool for the chunk hand-offs between the three streams
     std::string err;
     uint64_t launches = 0;
     int sm_count = 148;

@@ -40,6 +40,8 @@ extern "C" int32_t stepth_cuda_device_count(int32_t *count_out) {
     return STEPTH_OK;
 }
 
+extern "C" void stepth_cuda_ctx_destroy(stepth_ctx *ctx);
+
 extern "C" int32_t stepth_cuda_ctx_create(int32_t device, stepth_ctx **ctx_out) {
     if (!ctx_out) return STEPTH_ERR_INVALID_ARG;
     *ctx_out = nullptr;
@@ -79,6 +81,12 @@ extern "C" int32_t stepth_cuda_ctx_create(int32_t device, stepth_ctx **ctx_out) 
         delete ctx;
         return STEPTH_ERR_CUDA;
     }
+    if (cudaStreamCreateWithFlags(&ctx->copy_in, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&ctx->copy_out, cudaStreamNonBlocking) != cudaSuccess) {
+        g_create_err = "cudaStreamCreate (copy streams) failed";
+        stepth_cuda_ctx_destroy(ctx);
+        return STEPTH_ERR_CUDA;
+    }
     *ctx_out = ctx;
     return STEPTH_OK;
 }
@@ -95,6 +103,9 @@ extern "C" void stepth_cuda_ctx_destroy(stepth_ctx *ctx) {
     for (auto &kv : ctx->taps)
         if (kv.second.dev) cudaFree(kv.second.dev);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
+    for (cudaEvent_t e : ctx->events) cudaEventDestroy(e);
+    if (ctx->copy_in) cudaStreamDestroy(ctx->copy_in);
+    if (ctx->copy_out) cudaStreamDestroy(ctx->copy_out);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -355,57 +366,88 @@ int32_t run_pairs(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_rgba, 
     if (want_apply) TRY_RC(ensure(ctx, ctx->rgba_out, px * 4 * n));
 
     STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(ctx->small.p, 0, sm.bytes, st));
-    for (uint32_t i = 0; i < n; ++i) {
-        const uint8_t *rgba_src = blocks ? (want_apply ? rgba_in[i] : nullptr) : main_rgba[i];
-        if (rgba_src)
-            STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync((uint8_t *)ctx->main_rgba.p + px * 4 * i, rgba_src, px * 4,
+    // The batch is cut into chunks of pairs that move through three streams: copy_in uploads chunk k+1 while the compute
+    // stream works on chunk k and copy_out brings chunk k-1 back, so the PCIe transfers hide behind the kernels.
+    const uint32_t chunk = (blocks || n <= 2) ? n : (n + 3) / 4;
+    const uint32_t n_chunks = (n + chunk - 1) / chunk;
+    while (ctx->events.size() < 2 * (size_t)n_chunks + 1) {
+        cudaEvent_t e;
+        STEPTH_CUDA_TRY(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        ctx->events.push_back(e);
+    }
+    const bool piped = n_chunks > 1;
+    cudaStream_t s_in = piped ? ctx->copy_in : st, s_out = piped ? ctx->copy_out : st;
+    if (piped) {  // the copy streams must not overtake the memset / earlier work on the compute stream
+        STEPTH_CUDA_TRY(ctx, cudaEventRecord(ctx->events[2 * n_chunks], st));
+        STEPTH_CUDA_TRY(ctx, cudaStreamWaitEvent(s_in, ctx->events[2 * n_chunks], 0));
+        STEPTH_CUDA_TRY(ctx, cudaStreamWaitEvent(s_out, ctx->events[2 * n_chunks], 0));
+    }
+    uint8_t *d_main = (uint8_t *)ctx->main_rgba.p, *d_add = (uint8_t *)ctx->add_rgb.p, *d_d8 = (uint8_t *)ctx->d8.p;
+    uint8_t *d_depth = (uint8_t *)ctx->depth.p, *d_mask = (uint8_t *)ctx->mask.p, *d_rgba = (uint8_t *)ctx->rgba_out.p;
+    for (uint32_t k = 0; k < n_chunks; ++k) {
+        const uint32_t i0 = k * chunk, i1 = std::min(n, i0 + chunk), nc = i1 - i0;
+        for (uint32_t i = i0; i < i1; ++i) {
+            const uint8_t *rgba_src = blocks ? (want_apply ? rgba_in[i] : nullptr) : main_rgba[i];
+            if (rgba_src)
+                STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(d_main + px * 4 * i, rgba_src, px * 4, cudaMemcpyHostToDevice, s_in));
+            STEPTH_CUDA_TRY(ctx, cudaMemcpy2DAsync(d_add + add_bytes * i, (size_t)wa_d * 3, add_rgb[i], (size_t)wa * 3,
+                                                   (size_t)wa_d * 3, ha_d, cudaMemcpyHostToDevice, s_in));
+        }
+        if (piped) {
+            STEPTH_CUDA_TRY(ctx, cudaEventRecord(ctx->events[2 * k], s_in));
+            STEPTH_CUDA_TRY(ctx, cudaStreamWaitEvent(st, ctx->events[2 * k], 0));
+        }
+        uint32_t *c_max = sm.max(ctx->small.p) + i0, *c_hist = sm.hist(ctx->small.p) + 256 * (size_t)i0;
+        int32_t *c_status = sm.status(ctx->small.p) + i0;
+        uint32_t *c_nout = sm.nout(ctx->small.p) + i0;
+        uint8_t *c_ranges = sm.ranges(ctx->small.p) + 512 * (size_t)i0;
+        const uint8_t *plane = nullptr;  // the raw-distance plane handed to finish
+        if (blocks) {
+            STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->blocks.p, blocks, sizeof(stepth_block) * n_blocks,
                                                  cudaMemcpyHostToDevice, st));
-        STEPTH_CUDA_TRY(ctx, cudaMemcpy2DAsync((uint8_t *)ctx->add_rgb.p + add_bytes * i, (size_t)wa_d * 3, add_rgb[i],
-                                               (size_t)wa * 3, (size_t)wa_d * 3, ha_d, cudaMemcpyHostToDevice, st));
-    }
-    const uint8_t *plane = nullptr;  // the raw-distance plane handed to finish
-    if (blocks) {
-        STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->blocks.p, blocks, sizeof(stepth_block) * n_blocks,
-                                             cudaMemcpyHostToDevice, st));
-        TRY_RC(stepth_cuda_dev_search_blocks(ctx, st, params, (const uint8_t *)ctx->add_rgb.p, wa_d, ha_d,
-                                             (const stepth_block *)ctx->blocks.p, n_blocks, (uint8_t *)ctx->d8.p,
-                                             sm.max(ctx->small.p)));
-        TRY_RC(stepth_cuda_dev_paint_blocks(ctx, st, (const stepth_block *)ctx->blocks.p, (const uint8_t *)ctx->d8.p,
-                                            n_blocks, w, h, (uint8_t *)ctx->plane.p));
-        plane = (const uint8_t *)ctx->plane.p;
-    } else {
-        stepth_dev_shape s;
-        memset(&s, 0, sizeof s);
-        s.n_pairs = n; s.w = w; s.h = h; s.img_h = h; s.y0 = 0;
-        s.wa = wa_d; s.ha = ha_d; s.add_y0 = 0; s.add_img_h = ha;
-        TRY_RC(stepth_cuda_dev_search_dense(ctx, st, &s, params, (const uint8_t *)ctx->main_rgba.p,
-                                            (const uint8_t *)ctx->add_rgb.p, (uint8_t *)ctx->d8.p,
-                                            sm.max(ctx->small.p)));
-        plane = (const uint8_t *)ctx->d8.p;
-    }
-    TRY_RC(stepth_cuda_dev_finish(ctx, st, n, w, h, plane, 0, h, sm.max(ctx->small.p), flags, (uint8_t *)ctx->depth.p,
-                                  0, h, want_fg ? sm.hist(ctx->small.p) : nullptr, sm.status(ctx->small.p)));
-    if (want_fg) {
-        TRY_RC(stepth_cuda_dev_depth_split(ctx, st, n, sm.hist(ctx->small.p), 2, sm.ranges(ctx->small.p),
-                                           sm.nout(ctx->small.p), sm.status(ctx->small.p)));
-        if (mask_out || want_apply)
-            TRY_RC(stepth_cuda_dev_mask_apply(ctx, st, n, px, (const uint8_t *)ctx->depth.p, sm.ranges(ctx->small.p),
-                                              512, sm.status(ctx->small.p),
-                                              want_apply ? (const uint8_t *)ctx->main_rgba.p : nullptr,
-                                              mask_out ? (uint8_t *)ctx->mask.p : nullptr,
-                                              want_apply ? (uint8_t *)ctx->rgba_out.p : nullptr));
+            TRY_RC(stepth_cuda_dev_search_blocks(ctx, st, params, d_add, wa_d, ha_d, (const stepth_block *)ctx->blocks.p,
+                                                 n_blocks, d_d8, c_max));
+            TRY_RC(stepth_cuda_dev_paint_blocks(ctx, st, (const stepth_block *)ctx->blocks.p, d_d8, n_blocks, w, h,
+                                                (uint8_t *)ctx->plane.p));
+            plane = (const uint8_t *)ctx->plane.p;
+        } else {
+            stepth_dev_shape s;
+            memset(&s, 0, sizeof s);
+            s.n_pairs = nc; s.w = w; s.h = h; s.img_h = h; s.y0 = 0;
+            s.wa = wa_d; s.ha = ha_d; s.add_y0 = 0; s.add_img_h = ha;
+            TRY_RC(stepth_cuda_dev_search_dense(ctx, st, &s, params, d_main + px * 4 * i0, d_add + add_bytes * i0,
+                                                d_d8 + px * i0, c_max));
+            plane = d_d8 + px * i0;
+        }
+        TRY_RC(stepth_cuda_dev_finish(ctx, st, nc, w, h, plane, 0, h, c_max, flags, d_depth + px * i0, 0, h,
+                                      want_fg ? c_hist : nullptr, c_status));
+        if (want_fg) {
+            TRY_RC(stepth_cuda_dev_depth_split(ctx, st, nc, c_hist, 2, c_ranges, c_nout, c_status));
+            if (mask_out || want_apply)
+                TRY_RC(stepth_cuda_dev_mask_apply(ctx, st, nc, px, d_depth + px * i0, c_ranges, 512, c_status,
+                                                  want_apply ? d_main + px * 4 * i0 : nullptr,
+                                                  mask_out ? d_mask + px * i0 : nullptr,
+                                                  want_apply ? d_rgba + px * 4 * i0 : nullptr));
+        }
+        if (piped) {
+            STEPTH_CUDA_TRY(ctx, cudaEventRecord(ctx->events[2 * k + 1], st));
+            STEPTH_CUDA_TRY(ctx, cudaStreamWaitEvent(s_out, ctx->events[2 * k + 1], 0));
+        }
+        for (uint32_t i = i0; i < i1; ++i) {
+            STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(depth_out[i], d_depth + px * i, px, cudaMemcpyDeviceToHost, s_out));
+            if (want_fg && mask_out && mask_out[i])
+                STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(mask_out[i], d_mask + px * i, px, cudaMemcpyDeviceToHost, s_out));
+            if (want_apply && rgba_out[i])
+                STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(rgba_out[i], d_rgba + px * 4 * i, px * 4, cudaMemcpyDeviceToHost, s_out));
+        }
     }
     STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_small, ctx->small.p, sm.bytes, cudaMemcpyDeviceToHost, st));
-    for (uint32_t i = 0; i < n; ++i) {
-        STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(depth_out[i], (uint8_t *)ctx->depth.p + px * i, px, cudaMemcpyDeviceToHost, st));
-        if (want_fg && mask_out && mask_out[i])
-            STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(mask_out[i], (uint8_t *)ctx->mask.p + px * i, px, cudaMemcpyDeviceToHost, st));
-        if (want_apply && rgba_out[i])
-            STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(rgba_out[i], (uint8_t *)ctx->rgba_out.p + px * 4 * i, px * 4,
-                                                 cudaMemcpyDeviceToHost, st));
-    }
     if (raw_d8_out) STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(raw_d8_out, ctx->d8.p, n_q * n, cudaMemcpyDeviceToHost, st));
     STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    if (piped) {
+        STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(s_in));
+        STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(s_out));
+    }
 
     int32_t first_bad = STEPTH_OK;
     for (uint32_t i = 0; i < n; ++i) {

@@ -407,3 +407,80 @@ def test_full_size_worst_case_sampled(ctx, orc):
     got = d8[0].reshape(-1).cpu().numpy()[idx]
     assert np.array_equal(got, sub)
     assert (sub != 0).any() and int(mx[0]) > 0
+
+
+# ---- multi-GPU orchestration (stepth_b200/bands.py) on the CUDA stage API ---------------------------------------------
+def test_band_runner_one_rank_equals_host_api(ctx, orc):
+    import stepth_b200 as sb
+    from stepth_b200 import bands
+
+    m, a = synth_pair("nat", 120, 90, seed=33)
+    flags = sb.RESAMPLE_U8 | sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY
+    host = ctx.depth_dense(m, a, P36, 40, flags)
+    runner = bands.BandRunner(bands.DeviceStages(ctx), 120, 90, 90, P36, 40, flags)
+    out = runner.run(torch.from_numpy(m).cuda()[None], torch.from_numpy(a).cuda()[None])
+    assert out["status"] == 0 and out["from_to"] == host["from_to"]
+    assert np.array_equal(out["depth_band"][0].cpu().numpy(), host["depth"])
+    assert np.array_equal(out["mask_band"][0].cpu().numpy(), host["mask"])
+    assert np.array_equal(out["rgba_band"][0].cpu().numpy(), host["rgba"])
+
+
+def _band_worker(rank, world, port, w, h, rings, q):
+    import os
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    import torch.distributed as dist
+
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        import stepth_b200 as sb
+        from stepth_b200 import bands, synth
+
+        c = sb.Context(rank)
+        m, a = synth.make_pair("nat", w, h, 9)
+        flags = sb.RESAMPLE_U8 | sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY
+        runner = bands.BandRunner(bands.DeviceStages(c), w, h, h, P36, rings, flags)
+        b = runner.band
+        out = runner.run(m[None, b.y0:b.y1].cuda().contiguous(), a[None, b.ay0:b.ay1].cuda().contiguous(), gather_depth=True)
+        torch.cuda.synchronize()
+        q.put({"rank": rank, "band": (b.y0, b.y1), "status": out["status"], "from_to": out.get("from_to"),
+               "depth": out["depth"][0].cpu().numpy(), "mask_band": out["mask_band"][0].cpu().numpy(),
+               "rgba_band": out["rgba_band"][0].cpu().numpy()})
+    finally:
+        dist.destroy_process_group()
+
+
+def test_row_bands_over_nccl_equal_one_gpu(ctx, orc):
+    """configs[4]'s decomposition on every GPU of the box: bands + MAX all-reduce + halo exchange + NCCL all-gather"""
+    world = torch.cuda.device_count()
+    if world < 2:
+        pytest.skip("needs at least 2 GPUs")
+    import socket
+
+    import torch.multiprocessing as mp
+
+    import stepth_b200 as sb
+
+    w, h, rings = 320, 250, 48
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    mpc = mp.get_context("spawn")
+    q = mpc.Queue()
+    procs = [mpc.Process(target=_band_worker, args=(r, world, port, w, h, rings, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=600) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    m, a = synth_pair("nat", w, h, seed=9)
+    host = ctx.depth_dense(m, a, P36, rings, sb.RESAMPLE_U8 | sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY)
+    for r in results:
+        y0, y1 = r["band"]
+        assert r["status"] == 0 and r["from_to"] == host["from_to"]
+        assert np.array_equal(r["depth"], host["depth"])
+        assert np.array_equal(r["mask_band"], host["mask"][y0:y1])
+        assert np.array_equal(r["rgba_band"], host["rgba"][y0:y1])
