@@ -1,0 +1,89 @@
+//! Raw bindings to `libstepth_cuda.so` -- one declaration per symbol of `include/stepth_cuda.h` that the patched
+//! `stepth` crate calls.  (The `stepth_cuda_dev_*` stage API is for in-process GPU pipelines and is not bound here.)
+#![allow(non_camel_case_types)]
+use std::os::raw::{c_char, c_double};
+
+pub const STEPTH_OK: i32 = 0;
+pub const STEPTH_ERR_INVALID_ARG: i32 = 1;
+pub const STEPTH_ERR_SIZE_MISMATCH: i32 = 2;
+pub const STEPTH_ERR_DIV_BY_ZERO_MAX: i32 = 3;
+pub const STEPTH_ERR_TOO_FEW_BLOCKS: i32 = 4;
+pub const STEPTH_ERR_DEGENERATE_DEPTH: i32 = 5;
+pub const STEPTH_ERR_NO_CONVERGENCE: i32 = 6;
+pub const STEPTH_ERR_CUDA: i32 = 100;
+
+pub const STEPTH_RESAMPLE_OFF: u32 = 0;
+pub const STEPTH_RESAMPLE_U8: u32 = 1;
+pub const STEPTH_RESAMPLE_F32: u32 = 2;
+pub const STEPTH_FLAG_INVERT: u32 = 1 << 2;
+pub const STEPTH_FLAG_FOREGROUND: u32 = 1 << 3;
+pub const STEPTH_FLAG_APPLY: u32 = 1 << 4;
+pub const STEPTH_FLAG_PIXELOPPS_SAT: u32 = 1 << 5;
+
+#[repr(C)]
+pub struct stepth_ctx {
+    _private: [u8; 0],
+}
+
+/// `disage::DiscretePixel<[u8;3]>` as it crosses the boundary (20 bytes)
+#[repr(C)]
+#[derive(Clone, Copy, Default)]
+pub struct stepth_block {
+    pub x: u32,
+    pub y: u32,
+    pub w: u32,
+    pub h: u32,
+    pub value: [u8; 3],
+    pub pad: u8,
+}
+
+#[repr(C)]
+#[derive(Clone, Copy, Default)]
+pub struct stepth_params {
+    pub precision: [u8; 3],
+    pub pad: u8,
+    pub max_rings: u32,
+    pub flags: u32,
+}
+
+extern "C" {
+    pub fn stepth_cuda_device_count(count_out: *mut i32) -> i32;
+    pub fn stepth_cuda_ctx_create(device: i32, ctx_out: *mut *mut stepth_ctx) -> i32;
+    pub fn stepth_cuda_ctx_destroy(ctx: *mut stepth_ctx);
+    pub fn stepth_cuda_last_error(ctx: *const stepth_ctx) -> *const c_char;
+    pub fn stepth_cuda_version() -> *const c_char;
+
+    pub fn stepth_cuda_depth_from_blocks(
+        ctx: *mut stepth_ctx, add_rgb: *const u8, wa: u32, ha: u32, blocks: *const stepth_block, n_blocks: usize,
+        w: u32, h: u32, params: *const stepth_params, depth_out: *mut u8, raw_d8_out: *mut u8, rgba_in: *const u8,
+        rgba_out: *mut u8, mask_out: *mut u8, from_to_out: *mut u8,
+    ) -> i32;
+    pub fn stepth_cuda_depth_dense(
+        ctx: *mut stepth_ctx, main_rgba: *const u8, w: u32, h: u32, add_rgb: *const u8, wa: u32, ha: u32,
+        params: *const stepth_params, depth_out: *mut u8, raw_d8_out: *mut u8, rgba_out: *mut u8, mask_out: *mut u8,
+        from_to_out: *mut u8,
+    ) -> i32;
+    pub fn stepth_cuda_depth_dense_batch(
+        ctx: *mut stepth_ctx, n_pairs: u32, main_rgba: *const *const u8, w: u32, h: u32, add_rgb: *const *const u8,
+        wa: u32, ha: u32, params: *const stepth_params, depth_out: *const *mut u8, rgba_out: *const *mut u8,
+        mask_out: *const *mut u8, from_to_out: *mut u8, status_out: *mut i32,
+    ) -> i32;
+
+    pub fn stepth_cuda_invert_depth(ctx: *mut stepth_ctx, depth_inout: *mut u8, n: usize) -> i32;
+    pub fn stepth_cuda_depth_split(
+        ctx: *mut stepth_ctx, depth: *const u8, n: usize, zones: u8, ranges_out: *mut u8, n_out: *mut u32,
+        has_values_out: *mut i32,
+    ) -> i32;
+    pub fn stepth_cuda_slice(ctx: *mut stepth_ctx, depth: *const u8, n: usize, from: i32, to: i32, mask_out: *mut u8) -> i32;
+    pub fn stepth_cuda_select_foreground(
+        ctx: *mut stepth_ctx, depth: *const u8, n: usize, mask_out: *mut u8, from_to_out: *mut u8,
+    ) -> i32;
+    pub fn stepth_cuda_apply_mask(ctx: *mut stepth_ctx, rgba_inout: *mut u8, mask: *const u8, n: usize) -> i32;
+
+    pub fn stepth_cuda_normalize_brightness_luma16(
+        ctx: *mut stepth_ctx, img1: *const u16, n1: usize, img2: *const u16, n2: usize, percent: c_double, out: *mut u16,
+    ) -> i32;
+    pub fn stepth_cuda_normalize_brightness_rgb16(
+        ctx: *mut stepth_ctx, img1: *const u16, n1: usize, img2: *const u16, n2: usize, percent: c_double, out: *mut u16,
+    ) -> i32;
+}

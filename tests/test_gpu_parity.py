@@ -484,3 +484,22 @@ def test_row_bands_over_nccl_equal_one_gpu(ctx, orc):
         assert np.array_equal(r["depth"], host["depth"])
         assert np.array_equal(r["mask_band"], host["mask"][y0:y1])
         assert np.array_equal(r["rgba_band"], host["rgba"][y0:y1])
+
+
+def test_cpp_host_mirror(ctx, orc, tmp_path):
+    """include/stepth.hpp (the C++ host side over the C ABI) against the oracle: tests/cpp/test_host.cpp"""
+    import os
+    import subprocess
+
+    from stepth_b200 import _build
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "test_host")
+    lib_dir, orc_dir = os.path.dirname(_build.LIB_PATH), os.path.join(root, "oracle")
+    subprocess.run(["g++", "-std=c++17", "-O1", "-o", exe, os.path.join(root, "tests", "cpp", "test_host.cpp"),
+                    f"-L{lib_dir}", "-lstepth_cuda", f"-L{orc_dir}", "-lstepth_oracle",
+                    f"-Wl,-rpath,{lib_dir}", f"-Wl,-rpath,{orc_dir}", "-L/usr/local/cuda/lib64", "-lcudart"],
+                   check=True, capture_output=True)
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "cpp host mirror ok" in r.stdout
