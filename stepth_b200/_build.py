@@ -38,10 +38,12 @@ def is_stale() -> bool:
     return any(os.path.exists(s) and os.path.getmtime(s) > t for s in sources())
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not is_stale():
+def build(force: bool = False, verbose: bool = False, out: str | None = None, defs=()) -> str:
+    """`out` / `defs` build a tuning variant next to the product library (scratch/ sweeps; see _ffi.lib)."""
+    if out is None and not force and not is_stale():
         return LIB_PATH
-    cmd = [_nvcc(), *NVCC_FLAGS, "-o", LIB_PATH, os.path.join(CSRC, "stepth_cuda.cu")]
+    out = out or LIB_PATH
+    cmd = [_nvcc(), *NVCC_FLAGS, *[f"-D{d}" for d in defs], "-o", out, os.path.join(CSRC, "stepth_cuda.cu")]
     if verbose:
         cmd += ["-Xptxas", "-v"]
     r = subprocess.run(cmd, capture_output=True, text=True)
@@ -49,7 +51,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
     if verbose:
         print(r.stdout + r.stderr)
-    return LIB_PATH
+    return out
 
 
 if __name__ == "__main__":

@@ -95,7 +95,8 @@ def lib() -> C.CDLL:
     if _lib is None:
         if not os.path.exists(_build.LIB_PATH) or os.environ.get("STEPTH_REBUILD") == "1":
             _build.build(force=True)
-        L = C.CDLL(_build.LIB_PATH)
+        # STEPTH_LIB: a tuning variant of the SAME library built by _build.build(out=..., defs=...) (kernel sweeps only)
+        L = C.CDLL(os.environ.get("STEPTH_LIB") or _build.LIB_PATH)
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(L, name)  # AttributeError here = header and library disagree: fail loudly
             fn.restype = res

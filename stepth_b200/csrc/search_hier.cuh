@@ -34,7 +34,7 @@ constexpr uint32_t WL_MAX_PAIRS = 2048;     // pair index travels in the upper 1
 
 struct HierView {
     const unsigned long long *fine;  // this pair's fine records
-    const uint32_t *crp, *ccp;       // this pair's coarse planes
+    const unsigned long long *crp, *ccp;  // this pair's coarse planes (64-tile windows)
     int ntx, nty, nxw, nyw;
 };
 
@@ -42,8 +42,8 @@ STEPTH_HD HierView make_view(const uint8_t *planes, const TileGeom &g, uint32_t 
     const uint8_t *base = planes + (size_t)pair * g.pair_bytes;
     HierView v;
     v.fine = reinterpret_cast<const unsigned long long *>(base);
-    v.crp = reinterpret_cast<const uint32_t *>(base + g.off_crp);
-    v.ccp = reinterpret_cast<const uint32_t *>(base + g.off_ccp);
+    v.crp = reinterpret_cast<const unsigned long long *>(base + g.off_crp);
+    v.ccp = reinterpret_cast<const unsigned long long *>(base + g.off_ccp);
     v.ntx = (int)g.ntx; v.nty = (int)g.nty; v.nxw = (int)g.nxw; v.nyw = (int)g.nyw;
     return v;
 }
@@ -154,6 +154,8 @@ STEPTH_HD HierQuery make_query(int ox, int oy, uint32_t col) {
     return q;
 }
 
+// Tests tile (TX, TY) for query q and lowers `best` to the tile's first match if that precedes it.  All 15 plane words
+// (3 candidate + 12 for the exact word) are requested at once: the walk is latency bound, one round trip beats two.
 STEPTH_HD void fine_test(const HierView &v, const HierQuery &q, int TX, int TY, int D, const unsigned long long *tab_le,
                          const unsigned long long *tab_ge, uint32_t &best) {
     const int bx = TX * 8 - q.ox, by = TY * 8 - q.oy;
@@ -162,52 +164,88 @@ STEPTH_HD void fine_test(const HierView &v, const HierQuery &q, int TX, int TY, 
     const int smin = dxm > dym ? dxm : dym;              // ring of the tile's nearest pixel
     if (smin >= D || smin > (int)(best >> 12)) return;   // KEY_NONE >> 12 is larger than any ring
     const unsigned long long *rec = v.fine + ((size_t)TY * v.ntx + TX) * T_REC;
-    unsigned long long m = ldg(rec + q.jr) & ldg(rec + T_SLOTS + q.jg) & ldg(rec + 2 * T_SLOTS + q.jb);
-    if (!m) return;
+    unsigned long long m = ~0ull;
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
         const uint32_t qc = (q.col >> (8 * c)) & 0xffu;
         const unsigned long long *ch = rec + c * T_SLOTS;
-        m &= (ldg(ch + w_up1(qc)) | ldg(ch + w_nta(qc))) & (ldg(ch + w_um1(qc)) | ldg(ch + w_ntb(qc)));
+        m &= ldg(ch + w_u(qc)) & (ldg(ch + w_up1(qc)) | ldg(ch + w_nta(qc))) & (ldg(ch + w_um1(qc)) | ldg(ch + w_ntb(qc)));
     }
     if (!m) return;
     const uint32_t k = tile_min_key(m, bx, by, tab_le, tab_ge);
     if ((int)(k >> 12) < D && k < best) best = k;
 }
 
+// occupancy window `cell` (= line * windows_per_line + w) of a coarse plane for query q: bit i <-> tile 32 w + i
+STEPTH_HD unsigned long long coarse_window(const unsigned long long *plane, uint32_t cell, const HierQuery &q) {
+    const unsigned long long *p = plane + (size_t)cell * C_CELL;
+    return ldg(p + q.cr) & ldg(p + q.cg) & ldg(p + q.cb);
+}
+
+// flags of the tile run [lo, hi] of plane line `line` as one word (bit i <-> tile lo + i); needs (lo & 31) + hi - lo < 64
+STEPTH_HD unsigned long long side_flags(const unsigned long long *plane, int wpl, int line, int n_lines, int lo, int hi,
+                                        const HierQuery &q) {
+    if ((unsigned)line >= (unsigned)n_lines || lo > hi) return 0ull;
+    unsigned long long m = coarse_window(plane, (uint32_t)(line * wpl + (lo >> 5)), q) >> (lo & 31);
+    const int len = hi - lo + 1;
+    if (len < 64) m &= (1ull << len) - 1ull;
+    return m;
+}
+
+// coarse rings [S0, S1): true when the answer is final, false when rings >= S1 still have to be walked.
+// Ring S: side 0 = tile row T0y+S, 1 = row T0y-S (tiles T0x-S .. T0x+S), 2 = tile column T0x+S, 3 = column T0x-S
+// (tiles T0y-S+1 .. T0y+S-1), all clipped to the grid.
 STEPTH_HD bool hier_rings(const HierView &v, const HierQuery &q, int D, int S0, int S1, const unsigned long long *tab_le,
                           const unsigned long long *tab_ge, uint32_t &best) {
     const int T0x = q.ox >> 3, T0y = q.oy >> 3;  // arithmetic shift: floor for a negative oy
     const int Smax = (D + 6) >> 3;               // tiles of coarse ring S start at ring >= 8S - 7
     const int S_end = S1 < Smax + 1 ? S1 : Smax + 1;
+    const int xmax = v.ntx - 1, ymax = v.nty - 1;
     for (int S = S0; S < S_end; ++S) {
         // the coarse square has left the tile grid on all four sides: nothing further out exists
-        if (T0x - S < 0 && T0x + S >= v.ntx && T0y - S < 0 && T0y + S >= v.nty) return true;
+        if (T0x - S < 0 && T0x + S > xmax && T0y - S < 0 && T0y + S > ymax) return true;
         if (S == 0) {
             if ((unsigned)T0x < (unsigned)v.ntx && (unsigned)T0y < (unsigned)v.nty)
                 fine_test(v, q, T0x, T0y, D, tab_le, tab_ge, best);
         } else {
+            const int rlo = T0x - S < 0 ? 0 : T0x - S, rhi = T0x + S > xmax ? xmax : T0x + S;               // row sides
+            const int clo = T0y - S + 1 < 0 ? 0 : T0y - S + 1, chi = T0y + S - 1 > ymax ? ymax : T0y + S - 1;  // column sides
+            if (S <= 16) {
+                // a side is at most 33 tiles: one window each; all four are requested before any is used
+                const unsigned long long f0 = side_flags(v.crp, v.nxw, T0y + S, v.nty, rlo, rhi, q);
+                const unsigned long long f1 = side_flags(v.crp, v.nxw, T0y - S, v.nty, rlo, rhi, q);
+                const unsigned long long f2 = side_flags(v.ccp, v.nyw, T0x + S, v.ntx, clo, chi, q);
+                const unsigned long long f3 = side_flags(v.ccp, v.nyw, T0x - S, v.ntx, clo, chi, q);
+                if (f0 | f1 | f2 | f3) {
 #pragma unroll 1
-            for (int side = 0; side < 4; ++side) {
-                const bool is_col = side >= 2;
-                const int line = (is_col ? T0x : T0y) + ((side & 1) ? -S : S);
-                const int n_lines = is_col ? v.ntx : v.nty, n = is_col ? v.nty : v.ntx;
-                if ((unsigned)line >= (unsigned)n_lines) continue;
-                const int c0 = is_col ? T0y : T0x;
-                int lo = is_col ? c0 - S + 1 : c0 - S, hi = is_col ? c0 + S - 1 : c0 + S;
-                lo = lo < 0 ? 0 : lo;
-                hi = hi > n - 1 ? n - 1 : hi;
-                if (lo > hi) continue;
-                const int w0 = lo >> 5, w1 = hi >> 5;
-                const uint32_t *cell = (is_col ? v.ccp : v.crp) + ((size_t)line * (is_col ? v.nyw : v.nxw) + w0) * C_CELL;
-                for (int w = w0; w <= w1; ++w, cell += C_CELL) {
-                    uint32_t m = ldg(cell + q.cr) & ldg(cell + q.cg) & ldg(cell + q.cb);
-                    if (w == w0) m &= 0xffffffffu << (lo & 31);
-                    if (w == w1) m &= 0xffffffffu >> (31 - (hi & 31));
-                    while (m) {
-                        const int p = (w << 5) + ffs32(m) - 1;
-                        m &= m - 1;
-                        fine_test(v, q, is_col ? line : p, is_col ? p : line, D, tab_le, tab_ge, best);
+                    for (int side = 0; side < 4; ++side) {
+                        unsigned long long m = side == 0 ? f0 : side == 1 ? f1 : side == 2 ? f2 : f3;
+                        const int line = (side >= 2 ? T0x : T0y) + ((side & 1) ? -S : S);
+                        const int lo = side >= 2 ? clo : rlo;
+                        while (m) {
+                            const int p = lo + ffs64(m) - 1;
+                            m &= m - 1;
+                            fine_test(v, q, side >= 2 ? line : p, side >= 2 ? p : line, D, tab_le, tab_ge, best);
+                        }
+                    }
+                }
+            } else {
+                // longer sides (max_rings > 134): window by window
+#pragma unroll 1
+                for (int side = 0; side < 4; ++side) {
+                    const bool is_col = side >= 2;
+                    const int line = (is_col ? T0x : T0y) + ((side & 1) ? -S : S);
+                    if ((unsigned)line >= (unsigned)(is_col ? v.ntx : v.nty)) continue;
+                    const int lo = is_col ? clo : rlo, hi = is_col ? chi : rhi;
+                    for (int w = lo >> 5; 32 * w <= hi; w += 2) {
+                        unsigned long long m = coarse_window(is_col ? v.ccp : v.crp, (uint32_t)(line * (is_col ? v.nyw : v.nxw) + w), q);
+                        if (32 * w < lo) m &= ~0ull << (lo - 32 * w);
+                        if (32 * w + 63 > hi) m &= ~0ull >> (32 * w + 63 - hi);
+                        while (m) {
+                            const int p = 32 * w + ffs64(m) - 1;
+                            m &= m - 1;
+                            fine_test(v, q, is_col ? line : p, is_col ? p : line, D, tab_le, tab_ge, best);
+                        }
                     }
                 }
             }
@@ -291,7 +329,13 @@ __device__ __forceinline__ void export_open(const HierArgs &a, bool open, uint32
 // Dense mode: a warp owns an 8x4 patch of main pixels (= 4x2 origins: neighbouring queries share almost all loads), a
 // CTA 32x8 pixels.  Block mode: one thread per DiscretePixel, list order.
 template <bool BLOCKS>
-__global__ void __launch_bounds__(256) search_near_kernel(HierArgs a) {
+#ifndef STEPTH_NEAR_MINB
+#define STEPTH_NEAR_MINB 5
+#endif
+#ifndef STEPTH_FAR_MINB
+#define STEPTH_FAR_MINB 10
+#endif
+__global__ void __launch_bounds__(256, STEPTH_NEAR_MINB) search_near_kernel(HierArgs a) {
     __shared__ unsigned long long s_le[DIAG_N], s_ge[DIAG_N];
     load_diag_tables(s_le, s_ge);
     const SearchArgs &s = a.s;
@@ -340,7 +384,7 @@ __global__ void __launch_bounds__(256) search_near_kernel(HierArgs a) {
 
 // FAR kernel: resumes the listed queries at coarse ring S0; a warp pulls 32 consecutive entries at a time.
 template <bool BLOCKS>
-__global__ void __launch_bounds__(128) search_far_kernel(HierArgs a) {
+__global__ void __launch_bounds__(128, STEPTH_FAR_MINB) search_far_kernel(HierArgs a) {
     __shared__ unsigned long long s_le[DIAG_N], s_ge[DIAG_N];
     load_diag_tables(s_le, s_ge);
     const SearchArgs &s = a.s;

@@ -23,15 +23,16 @@
 // The 32 U words of one channel of one tile are 256 contiguous bytes: lanes that look at the same tile with different
 // query colours hit two 128-byte lines.
 //
-// COARSE level (u32 words): E_c[q] bit = "some pixel of this tile has channel c inside T(q)", one plane per exact query
-// value q = 0..255, 32 tiles per word,
+// COARSE level: E_c[q] bit = "some pixel of this tile has channel c inside T(q)", one plane per exact query value
+// q = 0..255.  A cell is a 64-tile WINDOW that starts every 32 tiles (u64 = {tiles 32w .. 32w+31, tiles 32w+32 .. 32w+63}),
+// so one 8-byte load holds any run of up to 33 tiles -- a whole side of a coarse ring up to ring 16 -- wherever it starts:
 //   row-major   CR[((TY * nxw + xw) * 3 + c) * 256 + q]   bit b <-> tile (32 xw + b, TY)     (row sides of a coarse ring)
 //   transposed  CC[((TX * nyw + yw) * 3 + c) * 256 + q]   bit b <-> tile (TX, 32 yw + b)     (column sides)
 // A tile whose three coarse bits are set for a query MAY hold a match (the three channels may be satisfied by different
 // pixels); a tile with a clear bit cannot.  Per tile and channel E is the set of values present in the tile, dilated by
 // p - 1 on both sides (abs) / smeared upwards from min - (p - 1) (sat).
 //
-// Algorithmic bytes per additional pixel: 3 read; 3 * 50 * 8 / 64 = 18.75 written (fine) + 2 * 3 * 256 / (8 * 64) = 3 (coarse).
+// Algorithmic bytes per additional pixel: 3 read; 3 * 50 * 8 / 64 = 18.75 written (fine) + 2 * 2 * 3 * 256 / (8 * 64) = 6 (coarse).
 #pragma once
 #include "common.cuh"
 
@@ -43,7 +44,7 @@ constexpr int QSTEP = 1 << QSHIFT;   // 8 levels per bin
 constexpr int T_SLOTS = 64;          // u64 slots per channel of a tile record
 constexpr int T_REC = 3 * T_SLOTS;   // u64 words per tile record (192 = 1536 bytes)
 constexpr int C_Q = 256;             // coarse planes per channel: one per exact query value
-constexpr int C_CELL = 3 * C_Q;      // u32 words per coarse cell (768 = 3072 bytes)
+constexpr int C_CELL = 3 * C_Q;      // u64 windows per coarse cell (768 = 6144 bytes)
 constexpr int W_UM1 = 32, W_UP32 = 33, W_NTA = 34, W_NTB = 42, W_USED = 50;
 static_assert(NB * QSTEP == 256 && NB == 32, "the layouts assume 32 bins of 8 levels");
 
@@ -53,8 +54,8 @@ struct TileGeom {
     uint32_t ntx, nty;    // tiles: ceil(wa/8), ceil(ha/8)
     uint32_t nxw, nyw;    // coarse words per tile row / tile column: ceil(ntx/32), ceil(nty/32)
     size_t fine_words;    // u64: ntx * nty * T_REC
-    size_t crp_words;     // u32: nty * nxw * C_CELL
-    size_t ccp_words;     // u32: ntx * nyw * C_CELL
+    size_t crp_words;     // u64: nty * nxw * C_CELL
+    size_t ccp_words;     // u64: ntx * nyw * C_CELL
     size_t off_crp, off_ccp;  // byte offsets of the coarse sections inside one pair's block
     size_t pair_bytes;    // bytes per pair (sections 256-byte aligned)
 };
@@ -71,8 +72,8 @@ inline TileGeom make_tile_geom(uint32_t wa, uint32_t ha, uint32_t src_wa) {
     g.ccp_words = (size_t)g.ntx * g.nyw * C_CELL;
     auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
     g.off_crp = up(g.fine_words * 8);
-    g.off_ccp = g.off_crp + up(g.crp_words * 4);
-    g.pair_bytes = g.off_ccp + up(g.ccp_words * 4);
+    g.off_ccp = g.off_crp + up(g.crp_words * 8);
+    g.pair_bytes = g.off_ccp + up(g.ccp_words * 8);
     return g;
 }
 
@@ -228,11 +229,15 @@ __global__ void __launch_bounds__(256) tile_planes_kernel(TileBuildArgs a) {
     }
     __syncthreads();
     // 24 (channel, value word) blocks of 32 tiles x 32 values -> 32 values x 32 tiles
-    uint32_t *crp = reinterpret_cast<uint32_t *>(pair_base + a.g.off_crp) + ((size_t)TY * a.g.nxw + xw) * C_CELL;
+    // window xw gets these 32 tiles as its low half, window xw - 1 as its high half; the last window's high half is empty
+    uint32_t *crp = reinterpret_cast<uint32_t *>(pair_base + a.g.off_crp) + ((size_t)TY * a.g.nxw + xw) * C_CELL * 2;
     for (int cg = warp; cg < 24; cg += 8) {
         const int c = cg >> 3, g = cg & 7;
         const uint32_t x = warp_bit_transpose(s_E[c][g][lane], lane);  // lane b: tile bits of q = 32 g + b
-        crp[c * C_Q + g * 32 + lane] = x;
+        const int slot = (c * C_Q + g * 32 + lane) * 2;
+        crp[slot] = x;
+        if (xw > 0) crp[slot + 1 - C_CELL * 2] = x;
+        if (xw + 1 == a.g.nxw) crp[slot + 1] = 0u;
     }
 }
 
@@ -246,10 +251,15 @@ __global__ void __launch_bounds__(256) coarse_transpose_kernel(TileBuildArgs a) 
     uint32_t *ccp = reinterpret_cast<uint32_t *>(pair_base + a.g.off_ccp);
     for (int cj = warp; cj < C_CELL; cj += 8) {
         const uint32_t TY = by * 32u + lane;
-        uint32_t x = TY < a.g.nty ? crp[((size_t)TY * a.g.nxw + bx) * C_CELL + cj] : 0u;
+        uint32_t x = TY < a.g.nty ? crp[(((size_t)TY * a.g.nxw + bx) * C_CELL + cj) * 2] : 0u;
         x = warp_bit_transpose(x, lane);
         const uint32_t TX = bx * 32u + lane;
-        if (TX < a.g.ntx) ccp[((size_t)TX * a.g.nyw + by) * C_CELL + cj] = x;
+        if (TX < a.g.ntx) {
+            uint32_t *dst = ccp + (((size_t)TX * a.g.nyw + by) * C_CELL + cj) * 2;
+            dst[0] = x;
+            if (by > 0) dst[1 - C_CELL * 2] = x;
+            if (by + 1 == a.g.nyw) dst[1] = 0u;
+        }
     }
 }
 

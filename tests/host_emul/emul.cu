@@ -33,9 +33,12 @@ void build_planes_host(const uint8_t *add, const TileGeom &g, int pr, int pg, in
                 const int v = add[((size_t)y * g.src_wa + x) * 3 + c], p = prec[c];
                 for (int q = 0; q < 256; ++q) {
                     const bool in = sat ? (v <= q + p - 1) : (v >= q - p + 1 && v <= q + p - 1);
-                    if (in) {
-                        crp[((size_t)TY * g.nxw + (TX >> 5)) * C_CELL + c * C_Q + q] |= 1u << (TX & 31);
-                        ccp[((size_t)TX * g.nyw + (TY >> 5)) * C_CELL + c * C_Q + q] |= 1u << (TY & 31);
+                    if (in) {  // window w holds tiles 32w .. 32w+63: a tile sits in the low half of its own window and in
+                               // the high half of the previous one
+                        crp[(((size_t)TY * g.nxw + (TX >> 5)) * C_CELL + c * C_Q + q) * 2] |= 1u << (TX & 31);
+                        if (TX >= 32) crp[(((size_t)TY * g.nxw + (TX >> 5) - 1) * C_CELL + c * C_Q + q) * 2 + 1] |= 1u << (TX & 31);
+                        ccp[(((size_t)TX * g.nyw + (TY >> 5)) * C_CELL + c * C_Q + q) * 2] |= 1u << (TY & 31);
+                        if (TY >= 32) ccp[(((size_t)TX * g.nyw + (TY >> 5) - 1) * C_CELL + c * C_Q + q) * 2 + 1] |= 1u << (TY & 31);
                     }
                 }
                 for (int j = 0; j < W_USED - 32; ++j)
