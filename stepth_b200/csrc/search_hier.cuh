@@ -325,6 +325,164 @@ __device__ __forceinline__ void export_open(const HierArgs &a, bool open, uint32
     }
 }
 
+// ---- warp-cooperative walk ---------------------------------------------------------------------------------------------
+// Reading the occupancy windows of a ring is cheap and every lane does it for its own query.  The expensive part -- the
+// tile tests -- is rare per lane (a few percent of the tiles are flagged), so lane-private tile tests would run with one
+// or two active lanes at a time.  Instead the warp pools them: every lane lists the flagged tiles of its query as tasks
+// (owner lane, tile) in shared memory, the 32 lanes take 32 tasks at a time -- fetching the owner's query with shuffles --
+// and post the key they find with an atomicMin on the owner's slot.  Pruning (`smin > best ring`) uses the best key
+// known when the task is listed; the arg-min does not depend on the order in which tiles are tested.
+constexpr int WTASKS = 96;  // tasks per pass
+
+struct WarpScratch {
+    uint32_t task[WTASKS];  // owner << 26 | TX << 13 | TY
+    uint32_t best[32];      // per owner lane: best key so far
+};
+
+__device__ __forceinline__ int list_tasks(unsigned long long m, int lo, int line, bool is_col, uint32_t lane, int k,
+                                          int pass_base, uint32_t *task) {
+    while (m) {
+        const int p = lo + __ffsll((long long)m) - 1;
+        m &= m - 1;
+        const uint32_t idx = (uint32_t)(k - pass_base);
+        if (idx < (uint32_t)WTASKS) task[idx] = lane << 26 | (uint32_t)(is_col ? line : p) << 13 | (uint32_t)(is_col ? p : line);
+        ++k;
+    }
+    return k;
+}
+
+// ring of the nearest pixel of tile (TX, TY) as seen from the origin of q
+STEPTH_HD int tile_smin(const HierQuery &q, int TX, int TY) {
+    const int bx = TX * 8 - q.ox, by = TY * 8 - q.oy;
+    const int dxm = bx > 0 ? bx : (bx + 7 < 0 ? -(bx + 7) : 0);
+    const int dym = by > 0 ? by : (by + 7 < 0 ? -(by + 7) : 0);
+    return dxm > dym ? dxm : dym;
+}
+
+// drops the flagged tiles of one side that cannot hold the answer: nearest pixel beyond the best ring so far or >= D
+__device__ __forceinline__ unsigned long long prune_side(unsigned long long m, int lo, int line, bool is_col, const HierQuery &q,
+                                                         int limit) {
+    unsigned long long keep = 0, rest = m;
+    while (rest) {
+        const int i = __ffsll((long long)rest) - 1;
+        rest &= rest - 1;
+        const int p = lo + i;
+        if (tile_smin(q, is_col ? line : p, is_col ? p : line) <= limit) keep |= 1ull << i;
+    }
+    return keep;
+}
+
+// All 32 lanes call this together.  `walking` lanes carry a query (v, q, best); the others only help with tile tests.
+// Walks coarse rings [S0, S1); returns true when this lane's answer is final.
+__device__ __forceinline__ bool hier_rings_warp(bool walking, const uint8_t *planes, const TileGeom &g, uint32_t pair,
+                                                const HierQuery &q, int D, int S0, int S1, const unsigned long long *tab_le,
+                                                const unsigned long long *tab_ge, uint32_t &best, WarpScratch *ws) {
+    const uint32_t lane = threadIdx.x & 31;
+    const HierView v = make_view(planes, g, pair);
+    const int T0x = q.ox >> 3, T0y = q.oy >> 3;
+    const int Smax = (D + 6) >> 3;
+    const int S_end = S1 < Smax + 1 ? S1 : Smax + 1;
+    const int xmax = v.ntx - 1, ymax = v.nty - 1;
+    bool final_ = !walking;
+    for (int S = S0; S < S_end; ++S) {
+        unsigned long long f0 = 0, f1 = 0, f2 = 0, f3 = 0;
+        int rlo = 0, clo = 0;
+        const bool go = walking && !final_;
+        if (go) {
+            if (T0x - S < 0 && T0x + S > xmax && T0y - S < 0 && T0y + S > ymax) {
+                final_ = true;  // the coarse square has left the tile grid on all four sides
+            } else if (S == 0) {
+                // the origin's own tile: every walking lane has exactly this one test, nothing to pool
+                if ((unsigned)T0x < (unsigned)v.ntx && (unsigned)T0y < (unsigned)v.nty)
+                    fine_test(v, q, T0x, T0y, D, tab_le, tab_ge, best);
+            } else {
+                rlo = T0x - S < 0 ? 0 : T0x - S;
+                clo = T0y - S + 1 < 0 ? 0 : T0y - S + 1;
+                const int rhi = T0x + S > xmax ? xmax : T0x + S, chi = T0y + S - 1 > ymax ? ymax : T0y + S - 1;
+                if (S <= 16) {
+                    f0 = side_flags(v.crp, v.nxw, T0y + S, v.nty, rlo, rhi, q);
+                    f1 = side_flags(v.crp, v.nxw, T0y - S, v.nty, rlo, rhi, q);
+                    f2 = side_flags(v.ccp, v.nyw, T0x + S, v.ntx, clo, chi, q);
+                    f3 = side_flags(v.ccp, v.nyw, T0x - S, v.ntx, clo, chi, q);
+                    // with a match in hand (or at the last rings) most flagged tiles are out of reach: do not list them
+                    const int limit = min(D - 1, (int)(best >> 12));
+                    if (limit < 8 * S + 7) {
+                        f0 = prune_side(f0, rlo, T0y + S, false, q, limit);
+                        f1 = prune_side(f1, rlo, T0y - S, false, q, limit);
+                        f2 = prune_side(f2, clo, T0x + S, true, q, limit);
+                        f3 = prune_side(f3, clo, T0x - S, true, q, limit);
+                    }
+                } else {
+                    // sides longer than one window (max_rings > 134): this lane tests its tiles itself, window by window
+#pragma unroll 1
+                    for (int side = 0; side < 4; ++side) {
+                        const bool is_col = side >= 2;
+                        const int line = (is_col ? T0x : T0y) + ((side & 1) ? -S : S);
+                        if ((unsigned)line >= (unsigned)(is_col ? v.ntx : v.nty)) continue;
+                        const int lo = is_col ? clo : rlo, hi = is_col ? chi : rhi;
+                        for (int w = lo >> 5; 32 * w <= hi; w += 2) {
+                            unsigned long long m = coarse_window(is_col ? v.ccp : v.crp, (uint32_t)(line * (is_col ? v.nyw : v.nxw) + w), q);
+                            if (32 * w < lo) m &= ~0ull << (lo - 32 * w);
+                            if (32 * w + 63 > hi) m &= ~0ull >> (32 * w + 63 - hi);
+                            while (m) {
+                                const int p = 32 * w + __ffsll((long long)m) - 1;
+                                m &= m - 1;
+                                fine_test(v, q, is_col ? line : p, is_col ? p : line, D, tab_le, tab_ge, best);
+                            }
+                        }
+                    }
+                }
+            }
+        }
+        // ---- pool the tile tests of the warp -----------------------------------------------------------------------------
+        const int cnt = __popcll(f0) + __popcll(f1) + __popcll(f2) + __popcll(f3);
+        const int total = __reduce_add_sync(0xffffffffu, cnt);
+        if (total) {
+            int prefix = cnt;  // inclusive scan
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, prefix, d);
+                if ((int)lane >= d) prefix += t;
+            }
+            prefix -= cnt;
+            ws->best[lane] = best;
+            for (int pass_base = 0; pass_base < total; pass_base += WTASKS) {
+                __syncwarp();
+                if (cnt) {
+                    int k = prefix;
+                    k = list_tasks(f0, rlo, T0y + S, false, lane, k, pass_base, ws->task);
+                    k = list_tasks(f1, rlo, T0y - S, false, lane, k, pass_base, ws->task);
+                    k = list_tasks(f2, clo, T0x + S, true, lane, k, pass_base, ws->task);
+                    k = list_tasks(f3, clo, T0x - S, true, lane, k, pass_base, ws->task);
+                }
+                __syncwarp();
+                const int n_pass = min(WTASKS, total - pass_base);
+                for (int b = 0; b < n_pass; b += 32) {
+                    const bool has = b + (int)lane < n_pass;
+                    const uint32_t task = has ? ws->task[b + lane] : 0u;
+                    const int owner = (int)(task >> 26);
+                    const int o_ox = __shfl_sync(0xffffffffu, q.ox, owner), o_oy = __shfl_sync(0xffffffffu, q.oy, owner);
+                    const uint32_t o_col = __shfl_sync(0xffffffffu, q.col, owner);
+                    const uint32_t o_pair = __shfl_sync(0xffffffffu, pair, owner);
+                    if (has) {
+                        const HierView ov = make_view(planes, g, o_pair);
+                        const HierQuery oq = make_query(o_ox, o_oy, o_col);
+                        uint32_t kb = ws->best[owner];
+                        const uint32_t before = kb;
+                        fine_test(ov, oq, (int)((task >> 13) & 0x1fffu), (int)(task & 0x1fffu), D, tab_le, tab_ge, kb);
+                        if (kb < before) atomicMin(&ws->best[owner], kb);
+                    }
+                }
+            }
+            __syncwarp();
+            best = ws->best[lane];
+        }
+        if (go && best != KEY_NONE && (int)(best >> 12) <= 8 * S) final_ = true;
+        if (__all_sync(0xffffffffu, final_)) return true;
+    }
+    return final_ || S1 > Smax;
+}
+
 // NEAR kernel: ring 0 (one pixel compare) and coarse rings [0, S1) for every query.
 // Dense mode: a warp owns an 8x4 patch of main pixels (= 4x2 origins: neighbouring queries share almost all loads), a
 // CTA 32x8 pixels.  Block mode: one thread per DiscretePixel, list order.
@@ -337,6 +495,7 @@ template <bool BLOCKS>
 #endif
 __global__ void __launch_bounds__(256, STEPTH_NEAR_MINB) search_near_kernel(HierArgs a) {
     __shared__ unsigned long long s_le[DIAG_N], s_ge[DIAG_N];
+    __shared__ WarpScratch s_ws[8];
     load_diag_tables(s_le, s_ge);
     const SearchArgs &s = a.s;
     const uint32_t pair = BLOCKS ? 0u : blockIdx.z;
@@ -355,28 +514,28 @@ __global__ void __launch_bounds__(256, STEPTH_NEAR_MINB) search_near_kernel(Hier
     }
     uint32_t key = KEY_NONE;
     bool open = false;
+    int ox = 0, oyl = 0;
+    uint32_t col = 0;
     if (valid) {
-        int ox, oyg;
-        uint32_t col;
+        int oyg;
         query_of<BLOCKS>(s, pair, qi, ox, oyg, col);
         const int src_wa = (int)s.wa, src_ha = (int)s.ha;
         // ring 0 out of bounds => `still_in_bounds` stays false => break => None   (helpers.rs:49-51)
         if (ox < src_wa && oyg < (int)s.add_img_h) {
-            const int oyl = oyg - (int)s.add_y0;  // origin row inside the sub-image held on this device
+            oyl = oyg - (int)s.add_y0;  // origin row inside the sub-image held on this device
             bool hit0 = false;
             if (oyl >= 0 && oyl < src_ha) {
                 const uint8_t *px = s.add_rgb + (size_t)pair * src_ha * src_wa * 3 + ((size_t)oyl * src_wa + ox) * 3;
                 const ColourBox box = make_box(col & 0xff, (col >> 8) & 0xff, (col >> 16) & 0xff, s.pr, s.pg, s.pb, s.sat != 0);
                 hit0 = box_contains(box, px[0], px[1], px[2]);
             }
-            if (hit0) {
-                key = 0;
-            } else if (s.max_rings > 1) {
-                const HierView v = make_view(a.planes, a.g, pair);
-                const HierQuery q = make_query(ox, oyl, col);
-                open = !hier_rings(v, q, (int)s.max_rings, 0, a.S1, s_le, s_ge, key);
-            }
+            if (hit0) key = 0;
+            else open = s.max_rings > 1;
         }
+    }
+    if (__any_sync(0xffffffffu, open)) {
+        const HierQuery q = make_query(ox, oyl, col);
+        open = !hier_rings_warp(open, a.planes, a.g, pair, q, (int)s.max_rings, 0, a.S1, s_le, s_ge, key, &s_ws[tid >> 5]);
     }
     export_open(a, open, pair, qi, key);
     publish_result(s, pair, qi, key, valid && !open);
@@ -386,6 +545,7 @@ __global__ void __launch_bounds__(256, STEPTH_NEAR_MINB) search_near_kernel(Hier
 template <bool BLOCKS>
 __global__ void __launch_bounds__(128, STEPTH_FAR_MINB) search_far_kernel(HierArgs a) {
     __shared__ unsigned long long s_le[DIAG_N], s_ge[DIAG_N];
+    __shared__ WarpScratch s_ws[4];
     load_diag_tables(s_le, s_ge);
     const SearchArgs &s = a.s;
     const int lane = threadIdx.x & 31;
@@ -397,21 +557,21 @@ __global__ void __launch_bounds__(128, STEPTH_FAR_MINB) search_far_kernel(HierAr
         if (e0 >= n_entries) break;
         const uint32_t e = e0 + lane;
         const bool valid = e < n_entries;
-        uint32_t pair = 0, qi = 0, key = KEY_NONE;
-        bool open = false;
+        uint32_t pair = 0, qi = 0, key = KEY_NONE, col = 0;
+        int ox = 0, oyl = 0;
         if (valid) {
             const uint2 ent = a.wl_in[e];
             qi = ent.x;
             pair = ent.y >> 21;
             const uint32_t k21 = ent.y & KEY21_NONE;
             key = k21 == KEY21_NONE ? KEY_NONE : k21;
-            int ox, oyg;
-            uint32_t col;
+            int oyg;
             query_of<BLOCKS>(s, pair, qi, ox, oyg, col);
-            const HierView v = make_view(a.planes, a.g, pair);
-            const HierQuery q = make_query(ox, oyg - (int)s.add_y0, col);
-            open = !hier_rings(v, q, (int)s.max_rings, a.S0, a.S1, s_le, s_ge, key);
+            oyl = oyg - (int)s.add_y0;
         }
+        const HierQuery q = make_query(ox, oyl, col);
+        const bool open = !hier_rings_warp(valid, a.planes, a.g, pair, q, (int)s.max_rings, a.S0, a.S1, s_le, s_ge, key,
+                                           &s_ws[threadIdx.x >> 5]);
         if (a.wl_out) export_open(a, open, pair, qi, key);
         publish_result(s, pair, qi, key, valid && !open);
     }
