@@ -27,7 +27,6 @@ constexpr int FIN_TILE_H = 32;
 constexpr int FIN_HALO = 3;
 constexpr int FIN_SW = FIN_TILE_W + 2 * FIN_HALO;  // 134 staged columns
 constexpr int FIN_SH = FIN_TILE_H + 2 * FIN_HALO;  // 38 staged rows
-constexpr int FIN_SWP = FIN_SW + 2;                // padded row pitch
 
 struct FinishArgs {
     const uint8_t *src;      // [n, src_rows, w] raw `d as u8` plane, global rows [src_y0, src_y0 + src_rows)
@@ -48,10 +47,26 @@ __device__ __forceinline__ uint8_t to_u8_nearest(float t) {
     return (uint8_t)roundf(t);         // NumCast::from(FloatNearest(t)) -> t.round()
 }
 
+// one output sample along an axis: the 7-tap interior case uses the constant weights (all interior indices share them:
+// at unit scale the tap offsets i - c are the integers -3 .. 3), the border case walks the host-built table
+__device__ __forceinline__ float taps7(const float *v, const float (&w)[7]) {
+    float t = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 7; ++k) t = __fadd_rn(t, __fmul_rn(v[k], w[k]));
+    return t;
+}
+
+constexpr int FIN_VSEG = 8;    // outputs per thread in the vertical pass (one column, 8 rows)
+constexpr int FIN_HSEG = 16;   // outputs per thread in the horizontal pass (one row, 16 columns)
+constexpr int FIN_PITCH = 137; // odd row pitch (floats): column walks and row walks are both bank-conflict free
+static_assert(FIN_SW <= FIN_PITCH && FIN_TILE_H % FIN_VSEG == 0 && FIN_TILE_W % FIN_HSEG == 0, "tile geometry");
+static_assert((FIN_TILE_W / FIN_HSEG) * FIN_TILE_H == 256, "horizontal pass: one item per thread");
+
 __global__ void __launch_bounds__(256) finish_kernel(FinishArgs a) {
-    __shared__ uint8_t lut[256];
-    __shared__ uint8_t s_src[FIN_SH][FIN_SWP];
-    __shared__ float s_v[FIN_TILE_H][FIN_SWP];
+    __shared__ float lut[256];
+    __shared__ float s_src[FIN_SH][FIN_PITCH];       // normalised input tile + halo, as f32
+    __shared__ float s_v[FIN_TILE_H][FIN_PITCH];     // after the vertical pass
+    __shared__ __align__(16) uint8_t s_out[FIN_TILE_H][FIN_TILE_W];
     __shared__ uint32_t s_hist[256];
 
     const uint32_t pair = blockIdx.z;
@@ -61,7 +76,7 @@ __global__ void __launch_bounds__(256) finish_kernel(FinishArgs a) {
         if (a.status && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.status[pair] = STEPTH_ERR_DIV_BY_ZERO_MAX;
         return;
     }
-    lut[tid] = (uint8_t)(((uint32_t)tid * 255u) / mx);  // (v as u64 * 255 / max as u64) as u8; v <= max
+    lut[tid] = (float)(uint8_t)(((uint32_t)tid * 255u) / mx);  // (v as u64 * 255 / max as u64) as u8; v <= max
     s_hist[tid] = 0;
 
     const int tx0 = blockIdx.x * FIN_TILE_W;                    // first output column of the tile
@@ -74,71 +89,111 @@ __global__ void __launch_bounds__(256) finish_kernel(FinishArgs a) {
 
     // stage + normalise; out-of-image cells are never referenced by a tap table, fill with 0
     for (int i = tid; i < FIN_SH * FIN_SW; i += 256) {
-        int r = i / FIN_SW, c = i - r * FIN_SW;
-        int gy = ty0 - FIN_HALO + r, gx = tx0 - FIN_HALO + c;
-        uint8_t v = 0;
-        int ly = gy - (int)a.src_y0;
+        const int r = i / FIN_SW, c = i - r * FIN_SW;
+        const int gy = ty0 - FIN_HALO + r, gx = tx0 - FIN_HALO + c;
+        float v = 0.0f;
+        const int ly = gy - (int)a.src_y0;
         if (gx >= 0 && gx < w && gy >= 0 && gy < img_h && ly >= 0 && ly < (int)a.src_rows)
             v = lut[src[(size_t)ly * w + gx]];
         s_src[r][c] = v;
     }
     __syncthreads();
 
-    // a thread walks down one column (i += 256 advances two rows): neighbouring outputs are mostly equal, so
-    // the shared-memory histogram is fed run-length encoded to keep same-address atomics rare
-    uint32_t run_val = 0, run_len = 0;
-    auto count = [&](uint8_t o) {
-        if (run_len && o != run_val) { atomicAdd(&s_hist[run_val], run_len); run_len = 0; }
-        run_val = o;
-        ++run_len;
-    };
     if (a.mode == STEPTH_RESAMPLE_OFF) {
         for (int i = tid; i < FIN_TILE_H * FIN_TILE_W; i += 256) {
-            int r = i / FIN_TILE_W, c = i - r * FIN_TILE_W;
-            int gy = ty0 + r, gx = tx0 + c;
-            if (gy < y_end && gx < w) {
-                uint8_t o = s_src[r + FIN_HALO][c + FIN_HALO];
-                if (a.invert) o = (uint8_t)(255 - o);
-                dst[(size_t)(gy - (int)a.out_y0) * w + gx] = o;
-                if (a.hist) count(o);
-            }
+            const int r = i / FIN_TILE_W, c = i - r * FIN_TILE_W;
+            s_out[r][c] = (uint8_t)s_src[r + FIN_HALO][c + FIN_HALO];
         }
     } else {
-        // vertical_sample: t = sum_k px(x, left + k) * w_k
-        for (int i = tid; i < FIN_TILE_H * FIN_SW; i += 256) {
-            int r = i / FIN_SW, c = i - r * FIN_SW;
-            int gy = ty0 + r;
-            float t = 0.0f;
-            if (gy < y_end) {
-                const TapRow &tp = a.taps_y[gy];
-                int base = tp.left - (ty0 - FIN_HALO);
-                for (int k = 0; k < tp.cnt; ++k)
-                    t = __fadd_rn(t, __fmul_rn((float)s_src[base + k][c], tp.w[k]));
-                if (a.mode == STEPTH_RESAMPLE_U8) t = (float)to_u8_nearest(t);
+        // ---- vertical_sample: t = sum_k px(x, left + k) * w_k; item = (column, 8-row segment), columns fastest ----------
+        float wy[7], wx[7];
+        {
+            // weights of an interior index (any will do); tiny images have none and never take the interior path
+            const int iy = min(max(3, 0), img_h - 1), ix = min(3, w - 1);
+#pragma unroll
+            for (int k = 0; k < 7; ++k) { wy[k] = a.taps_y[iy].w[k]; wx[k] = a.taps_x[ix].w[k]; }
+        }
+        for (int it = tid; it < FIN_SW * (FIN_TILE_H / FIN_VSEG); it += 256) {
+            const int seg = it / FIN_SW, c = it - seg * FIN_SW;
+            float v[FIN_VSEG + 6];
+#pragma unroll
+            for (int k = 0; k < FIN_VSEG + 6; ++k) v[k] = s_src[seg * FIN_VSEG + k][c];
+#pragma unroll
+            for (int j = 0; j < FIN_VSEG; ++j) {
+                const int r = seg * FIN_VSEG + j, gy = ty0 + r;
+                float t = 0.0f;
+                if (gy < y_end) {
+                    if (gy >= 3 && gy + 4 <= img_h) {
+                        t = taps7(v + j, wy);
+                    } else {
+                        const TapRow &tp = a.taps_y[gy];
+                        const int base = tp.left - (ty0 - FIN_HALO);
+                        for (int k = 0; k < tp.cnt; ++k) t = __fadd_rn(t, __fmul_rn(s_src[base + k][c], tp.w[k]));
+                    }
+                    if (a.mode == STEPTH_RESAMPLE_U8) t = (float)to_u8_nearest(t);
+                }
+                s_v[r][c] = t;
             }
-            s_v[r][c] = t;
         }
         __syncthreads();
-        // horizontal_sample
-        for (int i = tid; i < FIN_TILE_H * FIN_TILE_W; i += 256) {
-            int r = i / FIN_TILE_W, c = i - r * FIN_TILE_W;
-            int gy = ty0 + r, gx = tx0 + c;
-            if (gy < y_end && gx < w) {
-                const TapRow &tp = a.taps_x[gx];
-                int base = tp.left - (tx0 - FIN_HALO);
-                float t = 0.0f;
-                for (int k = 0; k < tp.cnt; ++k) t = __fadd_rn(t, __fmul_rn(s_v[r][base + k], tp.w[k]));
-                uint8_t o = to_u8_nearest(t);
-                if (a.invert) o = (uint8_t)(255 - o);
-                dst[(size_t)(gy - (int)a.out_y0) * w + gx] = o;
-                if (a.hist) count(o);
+        // ---- horizontal_sample: item = (row, 16-column segment), rows fastest -------------------------------------------
+        {
+            const int r = tid & (FIN_TILE_H - 1), seg = tid / FIN_TILE_H;
+            const int gy = ty0 + r;
+            float v[FIN_HSEG + 6];
+#pragma unroll
+            for (int k = 0; k < FIN_HSEG + 6; ++k) v[k] = s_v[r][seg * FIN_HSEG + k];
+#pragma unroll
+            for (int j = 0; j < FIN_HSEG; ++j) {
+                const int c = seg * FIN_HSEG + j, gx = tx0 + c;
+                uint8_t o = 0;
+                if (gy < y_end && gx < w) {
+                    float t = 0.0f;
+                    if (gx >= 3 && gx + 4 <= w) {
+                        t = taps7(v + j, wx);
+                    } else {
+                        const TapRow &tp = a.taps_x[gx];
+                        const int base = tp.left - (tx0 - FIN_HALO);
+                        for (int k = 0; k < tp.cnt; ++k) t = __fadd_rn(t, __fmul_rn(s_v[r][base + k], tp.w[k]));
+                    }
+                    o = to_u8_nearest(t);
+                }
+                s_out[r][c] = o;
+            }
+        }
+    }
+    __syncthreads();
+    // ---- invert, store (coalesced: a warp writes 4 rows x 128 bytes), histogram ------------------------------------------
+    {
+        const int r = tid >> 3, c0 = (tid & 7) * 16;
+        const int gy = ty0 + r;
+        if (gy < y_end && tx0 + c0 < w) {
+            uint4 q = *reinterpret_cast<const uint4 *>(&s_out[r][c0]);
+            if (a.invert) { q.x = ~q.x; q.y = ~q.y; q.z = ~q.z; q.w = ~q.w; }
+            uint8_t *drow = dst + (size_t)(gy - (int)a.out_y0) * w + tx0 + c0;
+            const int n = min(16, w - (tx0 + c0));
+            if (n == 16 && ((uintptr_t)drow & 15) == 0) {
+                *reinterpret_cast<uint4 *>(drow) = q;
+            } else {
+                const uint32_t qq[4] = {q.x, q.y, q.z, q.w};
+                for (int k = 0; k < n; ++k) drow[k] = (uint8_t)(qq[k >> 2] >> (8 * (k & 3)));
+            }
+            if (a.hist) {
+                // neighbouring outputs are mostly equal: feed the shared-memory histogram run-length encoded
+                const uint32_t qq[4] = {q.x, q.y, q.z, q.w};
+                uint32_t run_val = qq[0] & 0xffu, run_len = 0;
+                for (int k = 0; k < n; ++k) {
+                    const uint32_t o = (qq[k >> 2] >> (8 * (k & 3))) & 0xffu;
+                    if (o != run_val) { atomicAdd(&s_hist[run_val], run_len); run_val = o; run_len = 0; }
+                    ++run_len;
+                }
+                atomicAdd(&s_hist[run_val], run_len);
             }
         }
     }
     if (a.hist) {
-        if (run_len) atomicAdd(&s_hist[run_val], run_len);
         __syncthreads();
-        uint32_t c = s_hist[tid];
+        const uint32_t c = s_hist[tid];
         if (c) atomicAdd(&a.hist[(size_t)pair * 256 + tid], c);
     }
 }

@@ -581,6 +581,7 @@ __global__ void __launch_bounds__(128, STEPTH_FAR_MINB) search_far_kernel(HierAr
 inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const SearchArgs &a, uint32_t n_pairs) {
     if (a.wa > 0xffffu || a.add_img_h > 0xffffu)
         return set_err(ctx, STEPTH_ERR_INVALID_ARG, "additional image larger than 65535 in one dimension");
+    static_assert(WL_MAX_PAIRS * CT_PARTS <= 65535, "grid.z of the transpose kernel");
     if (n_pairs > WL_MAX_PAIRS)
         return set_err(ctx, STEPTH_ERR_INVALID_ARG, "more than 2048 pairs in one launch");
     HierArgs h;
@@ -603,7 +604,7 @@ inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const Search
     tile_planes_kernel<<<dim3(h.g.nxw, h.g.nty, n_pairs), 256, 0, st>>>(p);
     ctx->launches++;
     STEPTH_CUDA_TRY(ctx, cudaGetLastError());
-    coarse_transpose_kernel<<<dim3(h.g.nxw, h.g.nyw, n_pairs), 256, 0, st>>>(p);
+    coarse_transpose_kernel<<<dim3(h.g.nxw, h.g.nyw, n_pairs * CT_PARTS), 256, 0, st>>>(p);
     ctx->launches++;
     STEPTH_CUDA_TRY(ctx, cudaGetLastError());
 

@@ -243,22 +243,33 @@ __global__ void __launch_bounds__(256) tile_planes_kernel(TileBuildArgs a) {
 
 // coarse row-major -> coarse transposed: one warp per (32x32 tile block, channel*256 + value); lane r reads the word of tile
 // row 32 by + r, the warp transposes the 32x32 bit block, lane k writes the word of tile column 32 bx + k.
+constexpr int CT_PARTS = 8;  // CTAs per (32x32 tile block, pair): each transposes C_CELL / CT_PARTS planes
+
 __global__ void __launch_bounds__(256) coarse_transpose_kernel(TileBuildArgs a) {
-    const uint32_t pair = blockIdx.z, bx = blockIdx.x, by = blockIdx.y;
+    const uint32_t pair = blockIdx.z / CT_PARTS, part = blockIdx.z % CT_PARTS, bx = blockIdx.x, by = blockIdx.y;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     uint8_t *pair_base = a.planes + (size_t)pair * a.g.pair_bytes;
     const uint32_t *crp = reinterpret_cast<const uint32_t *>(pair_base + a.g.off_crp);
     uint32_t *ccp = reinterpret_cast<uint32_t *>(pair_base + a.g.off_ccp);
-    for (int cj = warp; cj < C_CELL; cj += 8) {
-        const uint32_t TY = by * 32u + lane;
-        uint32_t x = TY < a.g.nty ? crp[(((size_t)TY * a.g.nxw + bx) * C_CELL + cj) * 2] : 0u;
-        x = warp_bit_transpose(x, lane);
-        const uint32_t TX = bx * 32u + lane;
-        if (TX < a.g.ntx) {
-            uint32_t *dst = ccp + (((size_t)TX * a.g.nyw + by) * C_CELL + cj) * 2;
-            dst[0] = x;
-            if (by > 0) dst[1 - C_CELL * 2] = x;
-            if (by + 1 == a.g.nyw) dst[1] = 0u;
+    constexpr int PER_WARP = C_CELL / CT_PARTS / 8;  // 12 planes per warp, four loads in flight at a time
+    const uint32_t TY = by * 32u + lane, TX = bx * 32u + lane;
+    const uint32_t *src = crp + ((size_t)TY * a.g.nxw + bx) * C_CELL * 2;
+    uint32_t *dst = ccp + ((size_t)TX * a.g.nyw + by) * C_CELL * 2;
+    const int cj0 = (int)part * (C_CELL / CT_PARTS) + warp * PER_WARP;
+#pragma unroll 1
+    for (int i = 0; i < PER_WARP; i += 4) {
+        uint32_t x[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) x[u] = TY < a.g.nty ? src[(cj0 + i + u) * 2] : 0u;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const uint32_t t = warp_bit_transpose(x[u], lane);
+            if (TX < a.g.ntx) {
+                uint32_t *d = dst + (cj0 + i + u) * 2;
+                d[0] = t;
+                if (by > 0) d[1 - C_CELL * 2] = t;
+                if (by + 1 == a.g.nyw) d[1] = 0u;
+            }
         }
     }
 }
