@@ -486,16 +486,18 @@ __device__ __forceinline__ bool hier_rings_warp(bool walking, const uint8_t *pla
 // NEAR kernel: ring 0 (one pixel compare) and coarse rings [0, S1) for every query.
 // Dense mode: a warp owns an 8x4 patch of main pixels (= 4x2 origins: neighbouring queries share almost all loads), a
 // CTA 32x8 pixels.  Block mode: one thread per DiscretePixel, list order.
-template <bool BLOCKS>
 #ifndef STEPTH_NEAR_MINB
-#define STEPTH_NEAR_MINB 5
+#define STEPTH_NEAR_MINB 5   // resident CTAs per SM the register allocation must allow: 5 x 256 threads -> 48 registers
 #endif
 #ifndef STEPTH_FAR_MINB
 #define STEPTH_FAR_MINB 10
 #endif
+template <bool BLOCKS, bool COMPACT>
 __global__ void __launch_bounds__(256, STEPTH_NEAR_MINB) search_near_kernel(HierArgs a) {
     __shared__ unsigned long long s_le[DIAG_N], s_ge[DIAG_N];
     __shared__ WarpScratch s_ws[8];
+    __shared__ uint4 s_open[COMPACT ? 256 : 1];  // queries that survive ring 0: {qi, ox, oy, colour}
+    __shared__ uint32_t s_cnt[8];
     load_diag_tables(s_le, s_ge);
     const SearchArgs &s = a.s;
     const uint32_t pair = BLOCKS ? 0u : blockIdx.z;
@@ -532,6 +534,33 @@ __global__ void __launch_bounds__(256, STEPTH_NEAR_MINB) search_near_kernel(Hier
             if (hit0) key = 0;
             else open = s.max_rings > 1;
         }
+    }
+    if (COMPACT) {
+        // Ring 0 settles about half of the queries of a natural pair; the rest are packed into the first warps of the CTA
+        // so that the walk runs with full warps (and the other warps retire).
+        publish_result(s, pair, qi, key, valid && !open);
+        const int lane = tid & 31, warp = tid >> 5;
+        const uint32_t bal = __ballot_sync(0xffffffffu, open);
+        if (lane == 0) s_cnt[warp] = __popc(bal);
+        __syncthreads();
+        uint32_t pre = 0, n_open = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) {
+            const uint32_t c = s_cnt[w];
+            if (w < warp) pre += c;
+            n_open += c;
+        }
+        if (open) s_open[pre + __popc(bal & ((1u << lane) - 1u))] = make_uint4(qi, (uint32_t)ox, (uint32_t)oyl, col);
+        __syncthreads();
+        if ((uint32_t)(warp * 32) >= n_open) return;  // warp-uniform
+        const bool has = (uint32_t)tid < n_open;
+        const uint4 e = has ? s_open[tid] : make_uint4(0, 0, 0, 0);
+        const HierQuery q = make_query((int)e.y, (int)e.z, e.w);
+        key = KEY_NONE;
+        const bool still = !hier_rings_warp(has, a.planes, a.g, pair, q, (int)s.max_rings, 0, a.S1, s_le, s_ge, key, &s_ws[warp]);
+        export_open(a, has && still, pair, e.x, key);
+        publish_result(s, pair, e.x, key, has && !still);
+        return;
     }
     if (__any_sync(0xffffffffu, open)) {
         const HierQuery q = make_query(ox, oyl, col);
@@ -625,11 +654,13 @@ inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const Search
     h.wl_out = (uint2 *)(wl0 + 64);
     h.wl_out_count = (uint32_t *)wl0;
     if (a.blocks) {
-        search_near_kernel<true><<<dim3((a.n_queries + 255) / 256, 1, 1), 256, 0, st>>>(h);
+        if (ctx->near_compact) search_near_kernel<true, true><<<dim3((a.n_queries + 255) / 256, 1, 1), 256, 0, st>>>(h);
+        else search_near_kernel<true, false><<<dim3((a.n_queries + 255) / 256, 1, 1), 256, 0, st>>>(h);
     } else {
         const uint32_t gy = (a.h + 7) / 8;
         if (gy > 65535u) return set_err(ctx, STEPTH_ERR_INVALID_ARG, "band taller than 524280 rows");
-        search_near_kernel<false><<<dim3((a.w + 31) / 32, gy, n_pairs), 256, 0, st>>>(h);
+        if (ctx->near_compact) search_near_kernel<false, true><<<dim3((a.w + 31) / 32, gy, n_pairs), 256, 0, st>>>(h);
+        else search_near_kernel<false, false><<<dim3((a.w + 31) / 32, gy, n_pairs), 256, 0, st>>>(h);
     }
     ctx->launches++;
     STEPTH_CUDA_TRY(ctx, cudaGetLastError());

@@ -76,6 +76,7 @@ extern "C" int32_t stepth_cuda_ctx_create(int32_t device, stepth_ctx **ctx_out) 
     ctx->sm_count = prop.multiProcessorCount;
     if (const char *ev = getenv("STEPTH_NEAR_RINGS")) ctx->near_rings = std::max(1, atoi(ev));  // tuning knobs
     if (const char *ev = getenv("STEPTH_MID_RINGS")) ctx->mid_rings = atoi(ev);
+    if (const char *ev = getenv("STEPTH_NEAR_COMPACT")) ctx->near_compact = atoi(ev);
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
         g_create_err = std::string("cudaStreamCreate failed: ") + cudaGetErrorString(e);
         delete ctx;
