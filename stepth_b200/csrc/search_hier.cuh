@@ -332,24 +332,13 @@ __device__ __forceinline__ void export_open(const HierArgs &a, bool open, uint32
 // (owner lane, tile) in shared memory, the 32 lanes take 32 tasks at a time -- fetching the owner's query with shuffles --
 // and post the key they find with an atomicMin on the owner's slot.  Pruning (`smin > best ring`) uses the best key
 // known when the task is listed; the arg-min does not depend on the order in which tiles are tested.
-constexpr int WTASKS = 96;  // tasks per pass
+constexpr int WTASKS = 96;  // task slots of a warp
 
 struct WarpScratch {
     uint32_t task[WTASKS];  // owner << 26 | TX << 13 | TY
     uint32_t best[32];      // per owner lane: best key so far
+    uint32_t n;             // tasks listed in this pass (may run past WTASKS: the surplus is listed again next pass)
 };
-
-__device__ __forceinline__ int list_tasks(unsigned long long m, int lo, int line, bool is_col, uint32_t lane, int k,
-                                          int pass_base, uint32_t *task) {
-    while (m) {
-        const int p = lo + __ffsll((long long)m) - 1;
-        m &= m - 1;
-        const uint32_t idx = (uint32_t)(k - pass_base);
-        if (idx < (uint32_t)WTASKS) task[idx] = lane << 26 | (uint32_t)(is_col ? line : p) << 13 | (uint32_t)(is_col ? p : line);
-        ++k;
-    }
-    return k;
-}
 
 // ring of the nearest pixel of tile (TX, TY) as seen from the origin of q
 STEPTH_HD int tile_smin(const HierQuery &q, int TX, int TY) {
@@ -359,17 +348,21 @@ STEPTH_HD int tile_smin(const HierQuery &q, int TX, int TY) {
     return dxm > dym ? dxm : dym;
 }
 
-// drops the flagged tiles of one side that cannot hold the answer: nearest pixel beyond the best ring so far or >= D
-__device__ __forceinline__ unsigned long long prune_side(unsigned long long m, int lo, int line, bool is_col, const HierQuery &q,
-                                                         int limit) {
-    unsigned long long keep = 0, rest = m;
-    while (rest) {
-        const int i = __ffsll((long long)rest) - 1;
-        rest &= rest - 1;
-        const int p = lo + i;
-        if (tile_smin(q, is_col ? line : p, is_col ? p : line) <= limit) keep |= 1ull << i;
+// Lists the flagged tiles of one side of a ring as tasks of the warp, skipping tiles that cannot hold the answer (nearest
+// pixel beyond `limit` = the best ring so far, or max_rings - 1).  Returns the bits that did not fit into this pass.
+__device__ __forceinline__ unsigned long long emit_side(unsigned long long m, int lo, int line, bool is_col, const HierQuery &q,
+                                                        int limit, uint32_t lane, WarpScratch *ws) {
+    while (m) {
+        const int p = lo + __ffsll((long long)m) - 1;
+        const int TX = is_col ? line : p, TY = is_col ? p : line;
+        if (tile_smin(q, TX, TY) <= limit) {
+            const uint32_t slot = atomicAdd(&ws->n, 1u);
+            if (slot >= (uint32_t)WTASKS) return m;
+            ws->task[slot] = lane << 26 | (uint32_t)TX << 13 | (uint32_t)TY;
+        }
+        m &= m - 1;
     }
-    return keep;
+    return 0ull;
 }
 
 // All 32 lanes call this together.  `walking` lanes carry a query (v, q, best); the others only help with tile tests.
@@ -404,14 +397,6 @@ __device__ __forceinline__ bool hier_rings_warp(bool walking, const uint8_t *pla
                     f1 = side_flags(v.crp, v.nxw, T0y - S, v.nty, rlo, rhi, q);
                     f2 = side_flags(v.ccp, v.nyw, T0x + S, v.ntx, clo, chi, q);
                     f3 = side_flags(v.ccp, v.nyw, T0x - S, v.ntx, clo, chi, q);
-                    // with a match in hand (or at the last rings) most flagged tiles are out of reach: do not list them
-                    const int limit = min(D - 1, (int)(best >> 12));
-                    if (limit < 8 * S + 7) {
-                        f0 = prune_side(f0, rlo, T0y + S, false, q, limit);
-                        f1 = prune_side(f1, rlo, T0y - S, false, q, limit);
-                        f2 = prune_side(f2, clo, T0x + S, true, q, limit);
-                        f3 = prune_side(f3, clo, T0x - S, true, q, limit);
-                    }
                 } else {
                     // sides longer than one window (max_rings > 134): this lane tests its tiles itself, window by window
 #pragma unroll 1
@@ -435,43 +420,34 @@ __device__ __forceinline__ bool hier_rings_warp(bool walking, const uint8_t *pla
             }
         }
         // ---- pool the tile tests of the warp -----------------------------------------------------------------------------
-        const int cnt = __popcll(f0) + __popcll(f1) + __popcll(f2) + __popcll(f3);
-        const int total = __reduce_add_sync(0xffffffffu, cnt);
-        if (total) {
-            int prefix = cnt;  // inclusive scan
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const int t = __shfl_up_sync(0xffffffffu, prefix, d);
-                if ((int)lane >= d) prefix += t;
-            }
-            prefix -= cnt;
+        while (__any_sync(0xffffffffu, (f0 | f1 | f2 | f3) != 0ull)) {
+            if (lane == 0) ws->n = 0;
             ws->best[lane] = best;
-            for (int pass_base = 0; pass_base < total; pass_base += WTASKS) {
-                __syncwarp();
-                if (cnt) {
-                    int k = prefix;
-                    k = list_tasks(f0, rlo, T0y + S, false, lane, k, pass_base, ws->task);
-                    k = list_tasks(f1, rlo, T0y - S, false, lane, k, pass_base, ws->task);
-                    k = list_tasks(f2, clo, T0x + S, true, lane, k, pass_base, ws->task);
-                    k = list_tasks(f3, clo, T0x - S, true, lane, k, pass_base, ws->task);
-                }
-                __syncwarp();
-                const int n_pass = min(WTASKS, total - pass_base);
-                for (int b = 0; b < n_pass; b += 32) {
-                    const bool has = b + (int)lane < n_pass;
-                    const uint32_t task = has ? ws->task[b + lane] : 0u;
-                    const int owner = (int)(task >> 26);
-                    const int o_ox = __shfl_sync(0xffffffffu, q.ox, owner), o_oy = __shfl_sync(0xffffffffu, q.oy, owner);
-                    const uint32_t o_col = __shfl_sync(0xffffffffu, q.col, owner);
-                    const uint32_t o_pair = __shfl_sync(0xffffffffu, pair, owner);
-                    if (has) {
-                        const HierView ov = make_view(planes, g, o_pair);
-                        const HierQuery oq = make_query(o_ox, o_oy, o_col);
-                        uint32_t kb = ws->best[owner];
-                        const uint32_t before = kb;
-                        fine_test(ov, oq, (int)((task >> 13) & 0x1fffu), (int)(task & 0x1fffu), D, tab_le, tab_ge, kb);
-                        if (kb < before) atomicMin(&ws->best[owner], kb);
-                    }
+            __syncwarp();
+            if (f0 | f1 | f2 | f3) {
+                // with a match in hand (or at the last rings) most flagged tiles are out of reach and are not listed
+                const int limit = min(D - 1, (int)(best >> 12));
+                f0 = emit_side(f0, rlo, T0y + S, false, q, limit, lane, ws);
+                if (!f0) f1 = emit_side(f1, rlo, T0y - S, false, q, limit, lane, ws);
+                if (!(f0 | f1)) f2 = emit_side(f2, clo, T0x + S, true, q, limit, lane, ws);
+                if (!(f0 | f1 | f2)) f3 = emit_side(f3, clo, T0x - S, true, q, limit, lane, ws);
+            }
+            __syncwarp();
+            const int n_pass = (int)min(ws->n, (uint32_t)WTASKS);
+            for (int b = 0; b < n_pass; b += 32) {
+                const bool has = b + (int)lane < n_pass;
+                const uint32_t task = has ? ws->task[b + lane] : 0u;
+                const int owner = (int)(task >> 26);
+                const int o_ox = __shfl_sync(0xffffffffu, q.ox, owner), o_oy = __shfl_sync(0xffffffffu, q.oy, owner);
+                const uint32_t o_col = __shfl_sync(0xffffffffu, q.col, owner);
+                const uint32_t o_pair = __shfl_sync(0xffffffffu, pair, owner);
+                if (has) {
+                    const HierView ov = make_view(planes, g, o_pair);
+                    const HierQuery oq = make_query(o_ox, o_oy, o_col);
+                    uint32_t kb = ws->best[owner];
+                    const uint32_t before = kb;
+                    fine_test(ov, oq, (int)((task >> 13) & 0x1fffu), (int)(task & 0x1fffu), D, tab_le, tab_ge, kb);
+                    if (kb < before) atomicMin(&ws->best[owner], kb);
                 }
             }
             __syncwarp();
