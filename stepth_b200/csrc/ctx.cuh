@@ -114,7 +114,7 @@ inline void build_taps(uint32_t n, std::vector<TapRow> &out) {
     }
 }
 
-inline int32_t get_taps(stepth_ctx *ctx, cudaStream_t st, uint32_t n, const TapRow **dev_out) {
+inline int32_t get_taps(stepth_ctx *ctx, cudaStream_t st, uint32_t n, const TapRow **dev_out, float *interior_out) {
     auto it = ctx->taps.find(n);
     if (it == ctx->taps.end()) {
         stepth_ctx::Taps t;
@@ -125,6 +125,7 @@ inline int32_t get_taps(stepth_ctx *ctx, cudaStream_t st, uint32_t n, const TapR
         it = ctx->taps.emplace(n, std::move(t)).first;
     }
     (void)st;
+    for (int k = 0; k < 7; ++k) interior_out[k] = n >= 7 ? it->second.host[3].w[k] : 0.0f;
     *dev_out = it->second.dev;
     return STEPTH_OK;
 }

@@ -39,6 +39,7 @@ struct FinishArgs {
     uint32_t w, img_h, src_y0, src_rows, out_y0, out_rows;
     uint32_t mode;           // STEPTH_RESAMPLE_*
     uint32_t invert;
+    float wy_int[7], wx_int[7];  // the taps of an interior index of each axis (all interior indices share them)
 };
 
 // clamp(t, 0.0, 255.0) then f32::round (half away from zero), as NumCast::from(FloatNearest(t)) does
@@ -88,14 +89,32 @@ __global__ void __launch_bounds__(256) finish_kernel(FinishArgs a) {
     __syncthreads();
 
     // stage + normalise; out-of-image cells are never referenced by a tap table, fill with 0
-    for (int i = tid; i < FIN_SH * FIN_SW; i += 256) {
-        const int r = i / FIN_SW, c = i - r * FIN_SW;
-        const int gy = ty0 - FIN_HALO + r, gx = tx0 - FIN_HALO + c;
-        float v = 0.0f;
-        const int ly = gy - (int)a.src_y0;
-        if (gx >= 0 && gx < w && gy >= 0 && gy < img_h && ly >= 0 && ly < (int)a.src_rows)
-            v = lut[src[(size_t)ly * w + gx]];
-        s_src[r][c] = v;
+    if ((w & 3) == 0 && ((uintptr_t)src & 3) == 0) {
+        // four pixels per load: words cover columns [tx0 - 4, tx0 + 132); staged column = global column - (tx0 - 3)
+        constexpr int WORDS = (FIN_TILE_W + 8) / 4;
+        for (int i = tid; i < FIN_SH * WORDS; i += 256) {
+            const int r = i / WORDS, wd = i - r * WORDS;
+            const int gy = ty0 - FIN_HALO + r, gx0 = tx0 - 4 + 4 * wd;
+            const int ly = gy - (int)a.src_y0;
+            uint32_t px = 0;
+            const bool ok = gx0 >= 0 && gx0 < w && gy >= 0 && gy < img_h && ly >= 0 && ly < (int)a.src_rows;
+            if (ok) px = *reinterpret_cast<const uint32_t *>(src + (size_t)ly * w + gx0);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int c = 4 * wd + k - 1;
+                if (c >= 0 && c < FIN_SW) s_src[r][c] = ok ? lut[(px >> (8 * k)) & 0xffu] : 0.0f;
+            }
+        }
+    } else {
+        for (int i = tid; i < FIN_SH * FIN_SW; i += 256) {
+            const int r = i / FIN_SW, c = i - r * FIN_SW;
+            const int gy = ty0 - FIN_HALO + r, gx = tx0 - FIN_HALO + c;
+            float v = 0.0f;
+            const int ly = gy - (int)a.src_y0;
+            if (gx >= 0 && gx < w && gy >= 0 && gy < img_h && ly >= 0 && ly < (int)a.src_rows)
+                v = lut[src[(size_t)ly * w + gx]];
+            s_src[r][c] = v;
+        }
     }
     __syncthreads();
 
@@ -106,13 +125,9 @@ __global__ void __launch_bounds__(256) finish_kernel(FinishArgs a) {
         }
     } else {
         // ---- vertical_sample: t = sum_k px(x, left + k) * w_k; item = (column, 8-row segment), columns fastest ----------
-        float wy[7], wx[7];
-        {
-            // weights of an interior index (any will do); tiny images have none and never take the interior path
-            const int iy = min(max(3, 0), img_h - 1), ix = min(3, w - 1);
+        float wy[7], wx[7];  // tiny images have no interior index and never take the interior path
 #pragma unroll
-            for (int k = 0; k < 7; ++k) { wy[k] = a.taps_y[iy].w[k]; wx[k] = a.taps_x[ix].w[k]; }
-        }
+        for (int k = 0; k < 7; ++k) { wy[k] = a.wy_int[k]; wx[k] = a.wx_int[k]; }
         for (int it = tid; it < FIN_SW * (FIN_TILE_H / FIN_VSEG); it += 256) {
             const int seg = it / FIN_SW, c = it - seg * FIN_SW;
             float v[FIN_VSEG + 6];
@@ -172,18 +187,18 @@ __global__ void __launch_bounds__(256) finish_kernel(FinishArgs a) {
             if (a.invert) { q.x = ~q.x; q.y = ~q.y; q.z = ~q.z; q.w = ~q.w; }
             uint8_t *drow = dst + (size_t)(gy - (int)a.out_y0) * w + tx0 + c0;
             const int n = min(16, w - (tx0 + c0));
+            const uint8_t inv = a.invert ? 0xffu : 0u;
+            const uint8_t *orow = &s_out[r][c0];
             if (n == 16 && ((uintptr_t)drow & 15) == 0) {
                 *reinterpret_cast<uint4 *>(drow) = q;
             } else {
-                const uint32_t qq[4] = {q.x, q.y, q.z, q.w};
-                for (int k = 0; k < n; ++k) drow[k] = (uint8_t)(qq[k >> 2] >> (8 * (k & 3)));
+                for (int k = 0; k < n; ++k) drow[k] = orow[k] ^ inv;
             }
             if (a.hist) {
                 // neighbouring outputs are mostly equal: feed the shared-memory histogram run-length encoded
-                const uint32_t qq[4] = {q.x, q.y, q.z, q.w};
-                uint32_t run_val = qq[0] & 0xffu, run_len = 0;
+                uint32_t run_val = orow[0] ^ inv, run_len = 0;
                 for (int k = 0; k < n; ++k) {
-                    const uint32_t o = (qq[k >> 2] >> (8 * (k & 3))) & 0xffu;
+                    const uint32_t o = orow[k] ^ inv;
                     if (o != run_val) { atomicAdd(&s_hist[run_val], run_len); run_val = o; run_len = 0; }
                     ++run_len;
                 }

@@ -237,9 +237,9 @@ extern "C" int32_t stepth_cuda_dev_finish(stepth_ctx *ctx, void *stream, uint32_
     a.mode = flags & STEPTH_RESAMPLE_MASK;
     a.invert = (flags & STEPTH_FLAG_INVERT) ? 1u : 0u;
     if (a.mode != STEPTH_RESAMPLE_OFF) {
-        int32_t rc = get_taps(ctx, st, img_h, &a.taps_y);
+        int32_t rc = get_taps(ctx, st, img_h, &a.taps_y, a.wy_int);
         if (rc != STEPTH_OK) return rc;
-        rc = get_taps(ctx, st, w, &a.taps_x);
+        rc = get_taps(ctx, st, w, &a.taps_x, a.wx_int);
         if (rc != STEPTH_OK) return rc;
     }
     dim3 grid((w + FIN_TILE_W - 1) / FIN_TILE_W, (out_rows + FIN_TILE_H - 1) / FIN_TILE_H, n_pairs);
