@@ -1,14 +1,14 @@
-// search_hier.cuh -- K1: the production ring search (helpers.rs:9-54 + depth_image.rs:113-122), one thread per query.
+// search_hier.cuh -- K1: the production ring search (helpers.rs:9-54 + depth_image.rs:113-122).
 //
 // The reference walks ring s = 0, 1, .. around the origin as: row y+s, row y-s (x ascending), column x+s, column x-s
 // (y ascending) and returns the FIRST pixel inside the query's colour box.  That is an arg-min of the ring-order key
 // (common.cuh) over the matching pixels, so pixels may be visited in any order and whole regions without a match may be
 // skipped.  This kernel walks COARSE rings of 8x8-pixel tiles around the origin's tile (tiles.cuh):
 //
-//   * coarse ring S = the tiles at Chebyshev tile distance S.  Its four sides are read from the tile-occupancy planes,
-//     32 tiles per word (3 loads + 2 ANDs): a clear bit proves that the tile holds no match for this query's colour;
-//   * a flagged tile is tested on the fine planes: candidate word (3 x 8-byte loads, 64 probes), then the exact word
-//     (12 more loads) -- bit-exact without touching the pixels;
+//   * coarse ring S = the tiles at Chebyshev tile distance S.  Each of its four sides is one 64-tile occupancy window
+//     per channel (3 x 8-byte loads + 2 ANDs): a clear bit proves that the tile holds no match for this query's colour;
+//   * a flagged tile is tested on the fine planes: the 15 words of the exact match word in one round trip (64 probes),
+//     bit-exact without touching the pixels;
 //   * the first match inside a tile in reference order is found by bit tricks: the tile is cut by the two diagonals
 //     through the origin into the parts that belong to the bottom row / top row / right column / left column of their
 //     rings (corners go to the rows, helpers.rs:28-31); inside a part the ring-order key is monotone in (row, column) or
@@ -17,9 +17,11 @@
 //     best key so far has ring <= 8S; a tile whose nearest pixel is farther than the best ring so far (or >= max) is skipped.
 //
 // Work per query is data dependent (most queries stop at ring 0; a few percent walk to the last ring), so the walk is
-// split: the NEAR kernel (one thread per main pixel / per block) does ring 0 and coarse rings 0..1 and appends what is
-// still open to a work list; the FAR kernel(s) resume the listed queries, 32 consecutive entries per warp, pulled with an
-// atomic cursor.  `d as u8` (depth_image.rs:120-121) and the per-pair maximum (:124) leave with the result.
+// split: the NEAR kernel (one thread per main pixel / per block) does ring 0, packs the survivors into full warps and
+// walks the first coarse rings; what is still open goes to a work list; the FAR kernel runs twice over the (shrinking)
+// list, 32 consecutive entries per warp, pulled with an atomic cursor.  Inside a warp the expensive, rare tile tests are
+// pooled (hier_rings_warp).  `d as u8` (depth_image.rs:120-121) and the per-pair maximum (:124) leave with the result.
+// hier_rings() is the same walk for ONE query without the pooling: tests/host_emul compiles it for the host.
 #pragma once
 #include <algorithm>
 
