@@ -62,6 +62,7 @@ public:
             case STEPTH_ERR_TOO_FEW_BLOCKS: throw Panic(rc, "chunk_size must not be zero");
             case STEPTH_ERR_DEGENERATE_DEPTH: throw Panic(rc, "depth_split on a degenerate depth range");
             case STEPTH_ERR_NO_CONVERGENCE: throw Panic(rc, "depth_split did not converge");
+            case STEPTH_ERR_OUT_OF_BOUNDS: throw Panic(rc, "Image index out of bounds");
             default: throw CudaError(stepth_cuda_last_error(ctx_));
         }
     }
@@ -84,6 +85,34 @@ struct MaskImage {
 
     uint32_t width() const { return w; }
     uint32_t height() const { return h; }
+    // src/mask_image.rs:57-73 -> RGBA8
+    std::vector<uint8_t> highlight_mask() const {
+        auto c = ctx ? ctx : default_context();
+        std::vector<uint8_t> out(image.size());
+        c->check(stepth_cuda_highlight_mask(c->get(), image.data(), mask.data(), (size_t)w * h, out.data()));
+        return out;
+    }
+    // src/mask_image.rs:99-109
+    void image_replace(const MaskImage &other, uint32_t start_x, uint32_t start_y) {
+        auto c = ctx ? ctx : default_context();
+        c->check(stepth_cuda_image_replace(c->get(), image.data(), mask.data(), w, h, other.image.data(), other.w, other.h,
+                                           start_x, start_y));
+    }
+    // src/mask_image.rs:147-197 (equal-sized masks)
+    void mask_and(const MaskImage &other) {
+        if (other.w != w || other.h != h) throw IoError("Sizes don't match");
+        auto c = ctx ? ctx : default_context();
+        c->check(stepth_cuda_mask_and(c->get(), mask.data(), other.mask.data(), mask.size()));
+    }
+    void mask_or(const MaskImage &other) {
+        if (other.w != w || other.h != h) throw IoError("Sizes don't match");
+        auto c = ctx ? ctx : default_context();
+        c->check(stepth_cuda_mask_or(c->get(), mask.data(), other.mask.data(), mask.size()));
+    }
+    void mask_not() {
+        auto c = ctx ? ctx : default_context();
+        c->check(stepth_cuda_mask_not(c->get(), mask.data(), mask.size()));
+    }
     // src/mask_image.rs:205-213
     void apply_mask() {
         auto c = ctx ? ctx : default_context();
@@ -152,6 +181,13 @@ public:
         ctx_->check(stepth_cuda_depth_dense(ctx_->get(), image_.data(), w_, h_, add_rgb, wa, ha, &p, depth.data(), nullptr,
                                             nullptr, nullptr, nullptr));
         load_depth(std::move(depth), w_, h_);
+    }
+
+    // src/depth_image.rs:51-63 -> RGBA8
+    std::vector<uint8_t> highlight_depth() const {
+        std::vector<uint8_t> out(image_.size());
+        ctx_->check(stepth_cuda_highlight_depth(ctx_->get(), image_.data(), depth_.data(), depth_.size(), out.data()));
+        return out;
     }
 
     // src/depth_image.rs:225-227

@@ -12,6 +12,7 @@
  *   src/depth_image.rs:220-245  select_foreground / slice
  *   src/mask_image.rs:205-213   MaskImage::apply_mask
  *   src/operations.rs:3-80      normalize_brightness_{luma16,rgb16}   
+ *   src/depth_image.rs:51-63, src/mask_image.rs:57-73,99-109,147-197   highlight_*, image_replace, mask_and/or/not (8(f) row 3)
  *
  * Ownership: the caller owns every buffer; the library borrows pointers for the duration of a call and
  * never frees or retains them.  Device buffers, pinned staging and streams live in the context.
@@ -39,6 +40,7 @@ extern "C" {
 #define STEPTH_ERR_TOO_FEW_BLOCKS 4   /* -> panic (par_chunks_mut(0))                     depth_image.rs:111-112 */
 #define STEPTH_ERR_DEGENERATE_DEPTH 5 /* -> panic (step_by(0) / underflow / unwrap(None)) depth_image.rs:212-216 */
 #define STEPTH_ERR_NO_CONVERGENCE 6   /* k-means did not converge (reference: unbounded recursion)             */
+#define STEPTH_ERR_OUT_OF_BOUNDS 7    /* -> panic (ImageBuffer::get_pixel out of bounds)  mask_image.rs:106        */
 #define STEPTH_ERR_CUDA 100           /* CUDA runtime failure; text in stepth_cuda_last_error()                */
 
 /* ---- flags (stepth_params.flags) ------------------------------------------------------------------------ */
@@ -114,6 +116,20 @@ int32_t stepth_cuda_slice(stepth_ctx *ctx, const uint8_t *depth, size_t n, int32
 int32_t stepth_cuda_select_foreground(stepth_ctx *ctx, const uint8_t *depth, size_t n, uint8_t *mask_out,
                                       uint8_t *from_to_out);                                    /* :220-223 */
 int32_t stepth_cuda_apply_mask(stepth_ctx *ctx, uint8_t *rgba_inout, const uint8_t *mask, size_t n); /* mask_image.rs:205-213 */
+
+/* ---- editor operations on host buffers (n = pixel counts) -------------------------------- */
+int32_t stepth_cuda_highlight_depth(stepth_ctx *ctx, const uint8_t *rgba_in, const uint8_t *depth, size_t n,
+                                    uint8_t *rgba_out);                                  /* depth_image.rs:51-63 */
+int32_t stepth_cuda_highlight_mask(stepth_ctx *ctx, const uint8_t *rgba_in, const uint8_t *mask, size_t n,
+                                   uint8_t *rgba_out);                                   /* mask_image.rs:57-73  */
+/* equal-sized masks only (the reference resizes `other` otherwise: out of scope -> callers resize first) */
+int32_t stepth_cuda_mask_and(stepth_ctx *ctx, uint8_t *mask_inout, const uint8_t *other, size_t n); /* :147-169 */
+int32_t stepth_cuda_mask_or(stepth_ctx *ctx, uint8_t *mask_inout, const uint8_t *other, size_t n);  /* :171-193 */
+int32_t stepth_cuda_mask_not(stepth_ctx *ctx, uint8_t *mask_inout, size_t n);                        /* :195-197 */
+/* mask_image.rs:99-109; STEPTH_ERR_OUT_OF_BOUNDS when a masked pixel of the window lies outside `other` */
+int32_t stepth_cuda_image_replace(stepth_ctx *ctx, uint8_t *rgba_inout, const uint8_t *mask, uint32_t w, uint32_t h,
+                                  const uint8_t *other_rgba, uint32_t ow, uint32_t oh, uint32_t start_x,
+                                  uint32_t start_y);
 
 /* operations.rs:3-36 / 38-80 (n = pixel counts) */
 int32_t stepth_cuda_normalize_brightness_luma16(stepth_ctx *ctx, const uint16_t *img1, size_t n1,

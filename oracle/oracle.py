@@ -284,3 +284,61 @@ def normalize_brightness_rgb16(img1, img2, percent):
     lib().orc_normalize_brightness_rgb16(img1.ctypes.data_as(p), img1.size // 3, img2.ctypes.data_as(p),
                                          img2.size // 3, float(percent), out.ctypes.data_as(p))
     return out
+
+
+# ---- editor operations ---------------------------------------------------------------------------
+def _bind_edit():
+    L = lib()
+    if getattr(L, "_edit_bound", False):
+        return L
+    u8p = C.POINTER(C.c_uint8)
+    L.orc_highlight_depth.restype = None
+    L.orc_highlight_depth.argtypes = [u8p, u8p, C.c_size_t, u8p]
+    L.orc_highlight_mask.restype = None
+    L.orc_highlight_mask.argtypes = [u8p, u8p, C.c_size_t, u8p]
+    for name in ("orc_mask_and", "orc_mask_or"):
+        getattr(L, name).restype = None
+        getattr(L, name).argtypes = [u8p, u8p, C.c_size_t]
+    L.orc_mask_not.restype = None
+    L.orc_mask_not.argtypes = [u8p, C.c_size_t]
+    L.orc_image_replace.restype = C.c_int32
+    L.orc_image_replace.argtypes = [u8p, u8p, C.c_uint32, C.c_uint32, u8p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
+    L._edit_bound = True
+    return L
+
+
+def highlight_depth(rgba: np.ndarray, depth: np.ndarray) -> np.ndarray:
+    rgba = np.ascontiguousarray(rgba, dtype=np.uint8)
+    depth = np.ascontiguousarray(depth, dtype=np.uint8)
+    out = np.empty_like(rgba)
+    _bind_edit().orc_highlight_depth(_u8(rgba), _u8(depth), depth.size, _u8(out))
+    return out
+
+
+def highlight_mask(rgba: np.ndarray, mask: np.ndarray) -> np.ndarray:
+    rgba = np.ascontiguousarray(rgba, dtype=np.uint8)
+    mask = np.ascontiguousarray(mask, dtype=np.uint8)
+    out = np.empty_like(rgba)
+    _bind_edit().orc_highlight_mask(_u8(rgba), _u8(mask), mask.size, _u8(out))
+    return out
+
+
+def mask_logic(op: str, mask: np.ndarray, other: np.ndarray | None = None) -> np.ndarray:
+    out = np.ascontiguousarray(mask, dtype=np.uint8).copy()
+    L = _bind_edit()
+    if op == "not":
+        L.orc_mask_not(_u8(out), out.size)
+    else:
+        other = np.ascontiguousarray(other, dtype=np.uint8)
+        (L.orc_mask_and if op == "and" else L.orc_mask_or)(_u8(out), _u8(other), out.size)
+    return out
+
+
+def image_replace(rgba: np.ndarray, mask: np.ndarray, other_rgba: np.ndarray, start_x: int, start_y: int) -> np.ndarray:
+    out = np.ascontiguousarray(rgba, dtype=np.uint8).copy()
+    mask = np.ascontiguousarray(mask, dtype=np.uint8)
+    other_rgba = np.ascontiguousarray(other_rgba, dtype=np.uint8)
+    h, w = out.shape[:2]
+    oh, ow = other_rgba.shape[:2]
+    _check(_bind_edit().orc_image_replace(_u8(out), _u8(mask), w, h, _u8(other_rgba), ow, oh, start_x, start_y))
+    return out

@@ -545,3 +545,66 @@ void orc_normalize_brightness_rgb16(const uint16_t *img1, size_t n1_px, const ui
     for (size_t i = 0; i < n1_px; ++i)
         for (int c = 0; c < 3; ++c) out[3 * i + c] = f64_as_u16((double)img1[3 * i + c] * diff[c]);
 }
+
+/* ---- editor operations ------------------------------------------------------------------ */
+
+/* `(v as f32 * m).max(0.0).min(255.0) as u8`: f32 product, clamp, truncation */
+static uint8_t adjust_u8(uint8_t v, float m) {
+    float t = (float)v * m;
+    if (!(t > 0.0f)) t = 0.0f; /* f32::max(0.0) also maps NaN to 0.0 */
+    if (t > 255.0f) t = 255.0f;
+    return (uint8_t)t;
+}
+
+/* depth_image.rs:51-63: multiplier = d as f32 / 255.0 * 2.0, applied to r, g, b; alpha untouched */
+void orc_highlight_depth(const uint8_t *rgba_in, const uint8_t *depth, size_t n, uint8_t *rgba_out) {
+    for (size_t i = 0; i < n; ++i) {
+        volatile float q = (float)depth[i] / 255.0f; /* volatile: keep the two roundings of the reference */
+        const float m = q * 2.0f;
+        rgba_out[4 * i + 0] = adjust_u8(rgba_in[4 * i + 0], m);
+        rgba_out[4 * i + 1] = adjust_u8(rgba_in[4 * i + 1], m);
+        rgba_out[4 * i + 2] = adjust_u8(rgba_in[4 * i + 2], m);
+        rgba_out[4 * i + 3] = rgba_in[4 * i + 3];
+    }
+}
+
+/* mask_image.rs:57-73: where mask == MASK_TRUE: r * 2.0, g * (1.0 / 2.0), b * (1.0 / 2.0) */
+void orc_highlight_mask(const uint8_t *rgba_in, const uint8_t *mask, size_t n, uint8_t *rgba_out) {
+    const float multiplier = 2.0f;
+    for (size_t i = 0; i < n; ++i) {
+        uint8_t r = rgba_in[4 * i], g = rgba_in[4 * i + 1], b = rgba_in[4 * i + 2];
+        if (mask[i] == 255) {
+            r = adjust_u8(r, multiplier);
+            g = adjust_u8(g, 1.0f / multiplier);
+            b = adjust_u8(b, 1.0f / multiplier);
+        }
+        rgba_out[4 * i] = r; rgba_out[4 * i + 1] = g; rgba_out[4 * i + 2] = b; rgba_out[4 * i + 3] = rgba_in[4 * i + 3];
+    }
+}
+
+/* mask_image.rs:147-169 / 171-193, the equal-dimensions branch */
+void orc_mask_and(uint8_t *mask, const uint8_t *other, size_t n) {
+    for (size_t i = 0; i < n; ++i) mask[i] = (mask[i] == 255 && other[i] == 255) ? 255 : 0;
+}
+void orc_mask_or(uint8_t *mask, const uint8_t *other, size_t n) {
+    for (size_t i = 0; i < n; ++i) mask[i] = (mask[i] == 255 || other[i] == 255) ? 255 : 0;
+}
+/* mask_image.rs:195-197 */
+void orc_mask_not(uint8_t *mask, size_t n) {
+    for (size_t i = 0; i < n; ++i) mask[i] = (uint8_t)(255 - mask[i]);
+}
+
+/* mask_image.rs:99-109: note `other.image.get_pixel(x, y)` uses the coordinates of SELF (literal) */
+int32_t orc_image_replace(uint8_t *rgba, const uint8_t *mask, uint32_t w, uint32_t h, const uint8_t *other_rgba,
+                          uint32_t ow, uint32_t oh, uint32_t start_x, uint32_t start_y) {
+    uint64_t y1 = (uint64_t)start_y + oh, x1 = (uint64_t)start_x + ow;
+    if (y1 > h) y1 = h;
+    if (x1 > w) x1 = w;
+    for (uint64_t y = start_y; y < y1; ++y)
+        for (uint64_t x = start_x; x < x1; ++x) {
+            if (mask[y * w + x] != 255) continue;
+            if (x >= ow || y >= oh) return ORC_OUT_OF_BOUNDS; /* get_pixel panics */
+            memcpy(rgba + (y * w + x) * 4, other_rgba + (y * ow + x) * 4, 4);
+        }
+    return ORC_OK;
+}

@@ -30,7 +30,8 @@ enum {
     ORC_DIV_BY_ZERO_MAX = 3,   /* max == 0 -> integer division panic   depth_image.rs:127 */
     ORC_TOO_FEW_BLOCKS = 4,    /* len/8 == 0 -> par_chunks_mut(0) panic depth_image.rs:111-112 */
     ORC_DEGENERATE_DEPTH = 5,  /* step_by(0) / usize underflow / unwrap(None) depth_image.rs:212-216 */
-    ORC_NO_CONVERGENCE = 6     /* k-means recursion did not terminate (reference: stack overflow) */
+    ORC_NO_CONVERGENCE = 6,    /* k-means recursion did not terminate (reference: stack overflow) */
+    ORC_OUT_OF_BOUNDS = 7      /* ImageBuffer::get_pixel out of bounds -> panic   mask_image.rs:106 */
 };
 
 /* disage::pixels::PixelOpps<[u8;3]> semantics (source absent -- SURVEY.md F6). */
@@ -118,6 +119,16 @@ int32_t orc_select_foreground(const uint8_t *depth, size_t n, uint8_t *mask_out,
 
 /* mask_image.rs:205-213 */
 void orc_apply_mask(uint8_t *rgba, const uint8_t *mask, size_t n);
+
+/* editor operations (SURVEY 8(f) "next" row 3) */
+void orc_highlight_depth(const uint8_t *rgba_in, const uint8_t *depth, size_t n, uint8_t *rgba_out); /* depth_image.rs:51-63 */
+void orc_highlight_mask(const uint8_t *rgba_in, const uint8_t *mask, size_t n, uint8_t *rgba_out);   /* mask_image.rs:57-73  */
+void orc_mask_and(uint8_t *mask, const uint8_t *other, size_t n);                                    /* mask_image.rs:147-169 (equal sizes) */
+void orc_mask_or(uint8_t *mask, const uint8_t *other, size_t n);                                     /* mask_image.rs:171-193 (equal sizes) */
+void orc_mask_not(uint8_t *mask, size_t n);                                                          /* mask_image.rs:195-197 */
+/* mask_image.rs:99-109; returns 7 (out of bounds) where ImageBuffer::get_pixel would panic */
+int32_t orc_image_replace(uint8_t *rgba, const uint8_t *mask, uint32_t w, uint32_t h, const uint8_t *other_rgba,
+                          uint32_t ow, uint32_t oh, uint32_t start_x, uint32_t start_y);
 
 /* operations.rs:3-36 / 38-80 (SURVEY 8(f) "next" row 1) */
 void orc_normalize_brightness_luma16(const uint16_t *img1, size_t n1, const uint16_t *img2, size_t n2,

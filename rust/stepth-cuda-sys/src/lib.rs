@@ -10,6 +10,7 @@ pub const STEPTH_ERR_DIV_BY_ZERO_MAX: i32 = 3;
 pub const STEPTH_ERR_TOO_FEW_BLOCKS: i32 = 4;
 pub const STEPTH_ERR_DEGENERATE_DEPTH: i32 = 5;
 pub const STEPTH_ERR_NO_CONVERGENCE: i32 = 6;
+pub const STEPTH_ERR_OUT_OF_BOUNDS: i32 = 7;
 pub const STEPTH_ERR_CUDA: i32 = 100;
 
 pub const STEPTH_RESAMPLE_OFF: u32 = 0;
@@ -79,6 +80,16 @@ extern "C" {
         ctx: *mut stepth_ctx, depth: *const u8, n: usize, mask_out: *mut u8, from_to_out: *mut u8,
     ) -> i32;
     pub fn stepth_cuda_apply_mask(ctx: *mut stepth_ctx, rgba_inout: *mut u8, mask: *const u8, n: usize) -> i32;
+
+    pub fn stepth_cuda_highlight_depth(ctx: *mut stepth_ctx, rgba_in: *const u8, depth: *const u8, n: usize, rgba_out: *mut u8) -> i32;
+    pub fn stepth_cuda_highlight_mask(ctx: *mut stepth_ctx, rgba_in: *const u8, mask: *const u8, n: usize, rgba_out: *mut u8) -> i32;
+    pub fn stepth_cuda_mask_and(ctx: *mut stepth_ctx, mask_inout: *mut u8, other: *const u8, n: usize) -> i32;
+    pub fn stepth_cuda_mask_or(ctx: *mut stepth_ctx, mask_inout: *mut u8, other: *const u8, n: usize) -> i32;
+    pub fn stepth_cuda_mask_not(ctx: *mut stepth_ctx, mask_inout: *mut u8, n: usize) -> i32;
+    pub fn stepth_cuda_image_replace(
+        ctx: *mut stepth_ctx, rgba_inout: *mut u8, mask: *const u8, w: u32, h: u32, other_rgba: *const u8, ow: u32,
+        oh: u32, start_x: u32, start_y: u32,
+    ) -> i32;
 
     pub fn stepth_cuda_normalize_brightness_luma16(
         ctx: *mut stepth_ctx, img1: *const u16, n1: usize, img2: *const u16, n2: usize, percent: c_double, out: *mut u16,

@@ -33,6 +33,7 @@ impl Ctx {
             sys::STEPTH_ERR_TOO_FEW_BLOCKS => panic!("chunk_size must not be zero"), // src/depth_image.rs:111-112
             sys::STEPTH_ERR_DEGENERATE_DEPTH => panic!("depth_split: degenerate depth range"), // src/depth_image.rs:212-216
             sys::STEPTH_ERR_NO_CONVERGENCE => panic!("depth_split: no convergence"),
+            sys::STEPTH_ERR_OUT_OF_BOUNDS => panic!("Image index out of bounds"), // src/mask_image.rs:106
             _ => Err(Error::new(ErrorKind::Other, self.last_error())),
         }
     }

@@ -20,6 +20,7 @@ ERR_DIV_BY_ZERO_MAX = 3
 ERR_TOO_FEW_BLOCKS = 4
 ERR_DEGENERATE_DEPTH = 5
 ERR_NO_CONVERGENCE = 6
+ERR_OUT_OF_BOUNDS = 7
 ERR_CUDA = 100
 
 RESAMPLE_OFF, RESAMPLE_U8, RESAMPLE_F32 = 0, 1, 2
@@ -73,6 +74,12 @@ SIGNATURES = {
     "stepth_cuda_slice": (_i32, [_vp, _u8p, _sz, _i32, _i32, _u8p]),
     "stepth_cuda_select_foreground": (_i32, [_vp, _u8p, _sz, _u8p, _u8p]),
     "stepth_cuda_apply_mask": (_i32, [_vp, _u8p, _u8p, _sz]),
+    "stepth_cuda_highlight_depth": (_i32, [_vp, _u8p, _u8p, _sz, _u8p]),
+    "stepth_cuda_highlight_mask": (_i32, [_vp, _u8p, _u8p, _sz, _u8p]),
+    "stepth_cuda_mask_and": (_i32, [_vp, _u8p, _u8p, _sz]),
+    "stepth_cuda_mask_or": (_i32, [_vp, _u8p, _u8p, _sz]),
+    "stepth_cuda_mask_not": (_i32, [_vp, _u8p, _sz]),
+    "stepth_cuda_image_replace": (_i32, [_vp, _u8p, _u8p, _u32, _u32, _u8p, _u32, _u32, _u32, _u32]),
     "stepth_cuda_normalize_brightness_luma16": (_i32, [_vp, _vp, _sz, _vp, _sz, C.c_double, _vp]),
     "stepth_cuda_normalize_brightness_rgb16": (_i32, [_vp, _vp, _sz, _vp, _sz, C.c_double, _vp]),
     "stepth_host_discretise_v0": (_sz, [_u8p, _u32, _u32, _u32, _u8p, _u32, _u32, _vp, _sz]),

@@ -38,6 +38,7 @@ _PANIC_TEXT = {
     _ffi.ERR_TOO_FEW_BLOCKS: "chunk_size must not be zero",
     _ffi.ERR_DEGENERATE_DEPTH: "depth_split on a degenerate depth range (step_by(0) / subtract with overflow / unwrap on None)",
     _ffi.ERR_NO_CONVERGENCE: "depth_split did not converge (the reference recurses without bound)",
+    _ffi.ERR_OUT_OF_BOUNDS: "Image index out of bounds",
 }
 
 
@@ -233,6 +234,50 @@ class Context:
             raise StepthIOError("Sizes don't match")
         with self._lock:
             self.check(self._lib.stepth_cuda_apply_mask(self._h, _ffi.ptr(out), _ffi.ptr(mask), mask.size))
+        return out
+
+    # ---- editor operations ---------------------------------------------------------------------
+    def highlight_depth(self, rgba, depth) -> np.ndarray:  # depth_image.rs:51-63
+        rgba, depth = _u8c(rgba, (4,)), _u8c(depth)
+        if depth.size * 4 != rgba.size:
+            raise StepthIOError("Sizes don't match")
+        out = np.empty_like(rgba)
+        with self._lock:
+            self.check(self._lib.stepth_cuda_highlight_depth(self._h, _ffi.ptr(rgba), _ffi.ptr(depth), depth.size, _ffi.ptr(out)))
+        return out
+
+    def highlight_mask(self, rgba, mask) -> np.ndarray:  # mask_image.rs:57-73
+        rgba, mask = _u8c(rgba, (4,)), _u8c(mask)
+        if mask.size * 4 != rgba.size:
+            raise StepthIOError("Sizes don't match")
+        out = np.empty_like(rgba)
+        with self._lock:
+            self.check(self._lib.stepth_cuda_highlight_mask(self._h, _ffi.ptr(rgba), _ffi.ptr(mask), mask.size, _ffi.ptr(out)))
+        return out
+
+    def mask_logic(self, op: str, mask, other=None) -> np.ndarray:  # mask_image.rs:147-197
+        out = _u8c(mask).copy()
+        with self._lock:
+            if op == "not":
+                self.check(self._lib.stepth_cuda_mask_not(self._h, _ffi.ptr(out), out.size))
+            else:
+                other = _u8c(other)
+                if other.shape != out.shape:
+                    raise StepthIOError("Sizes don't match")  # the reference would Gaussian-resize `other`: out of scope
+                fn = self._lib.stepth_cuda_mask_and if op == "and" else self._lib.stepth_cuda_mask_or
+                self.check(fn(self._h, _ffi.ptr(out), _ffi.ptr(other), out.size))
+        return out
+
+    def image_replace(self, rgba, mask, other_rgba, start_x: int, start_y: int) -> np.ndarray:  # mask_image.rs:99-109
+        out = _u8c(rgba, (4,)).copy()
+        mask, other_rgba = _u8c(mask), _u8c(other_rgba, (4,))
+        h, w = out.shape[:2]
+        oh, ow = other_rgba.shape[:2]
+        if mask.shape != (h, w):
+            raise StepthIOError("Sizes don't match")
+        with self._lock:
+            self.check(self._lib.stepth_cuda_image_replace(self._h, _ffi.ptr(out), _ffi.ptr(mask), w, h, _ffi.ptr(other_rgba),
+                                                           ow, oh, int(start_x), int(start_y)))
         return out
 
     # ---- operations.rs ------------------------------------------------------------------------------------

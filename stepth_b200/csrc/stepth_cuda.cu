@@ -11,6 +11,7 @@
 #include "search_hier.cuh"
 #include "tail.cuh"
 #include "brightness.cuh"
+#include "edit.cuh"
 
 #include <algorithm>
 
@@ -628,6 +629,101 @@ extern "C" int32_t stepth_cuda_apply_mask(stepth_ctx *ctx, uint8_t *rgba_inout, 
     LAUNCH_CHECK(ctx);
     STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(rgba_inout, ctx->main_rgba.p, n * 4, cudaMemcpyDeviceToHost, st));
     STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return STEPTH_OK;
+}
+
+// ---- editor operations -----------------------------------------------------------------------------
+static int32_t highlight(stepth_ctx *ctx, const uint8_t *rgba_in, const uint8_t *plane, size_t n, uint8_t *rgba_out, int mode) {
+    if (!ctx) return STEPTH_ERR_INVALID_ARG;
+    if (!rgba_in || !plane || !rgba_out) return set_err(ctx, STEPTH_ERR_INVALID_ARG, "highlight: null buffer");
+    if (n == 0) return STEPTH_OK;
+    STEPTH_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    TRY_RC(ensure(ctx, ctx->main_rgba, n * 4));
+    TRY_RC(ensure(ctx, ctx->rgba_out, n * 4));
+    TRY_RC(ensure(ctx, ctx->depth, n));
+    STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->main_rgba.p, rgba_in, n * 4, cudaMemcpyHostToDevice, st));
+    STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->depth.p, plane, n, cudaMemcpyHostToDevice, st));
+    const uint32_t grid = (uint32_t)std::min<size_t>((n + 255) / 256, (size_t)ctx->sm_count * 16);
+    highlight_kernel<<<grid, 256, 0, st>>>((const uint32_t *)ctx->main_rgba.p, (const uint8_t *)ctx->depth.p, n,
+                                           (uint32_t *)ctx->rgba_out.p, mode);
+    LAUNCH_CHECK(ctx);
+    STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(rgba_out, ctx->rgba_out.p, n * 4, cudaMemcpyDeviceToHost, st));
+    STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return STEPTH_OK;
+}
+
+extern "C" int32_t stepth_cuda_highlight_depth(stepth_ctx *ctx, const uint8_t *rgba_in, const uint8_t *depth, size_t n,
+                                               uint8_t *rgba_out) {
+    return highlight(ctx, rgba_in, depth, n, rgba_out, 0);
+}
+
+extern "C" int32_t stepth_cuda_highlight_mask(stepth_ctx *ctx, const uint8_t *rgba_in, const uint8_t *mask, size_t n,
+                                              uint8_t *rgba_out) {
+    return highlight(ctx, rgba_in, mask, n, rgba_out, 1);
+}
+
+static int32_t mask_logic(stepth_ctx *ctx, uint8_t *mask_inout, const uint8_t *other, size_t n, int op) {
+    if (!ctx) return STEPTH_ERR_INVALID_ARG;
+    if (!mask_inout || (op != 2 && !other)) return set_err(ctx, STEPTH_ERR_INVALID_ARG, "mask op: null buffer");
+    if (n == 0) return STEPTH_OK;
+    STEPTH_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    TRY_RC(ensure(ctx, ctx->mask, n));
+    TRY_RC(ensure(ctx, ctx->depth, n));
+    STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->mask.p, mask_inout, n, cudaMemcpyHostToDevice, st));
+    if (op != 2) STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->depth.p, other, n, cudaMemcpyHostToDevice, st));
+    const uint32_t grid = (uint32_t)std::min<size_t>((n + 255) / 256, (size_t)ctx->sm_count * 16);
+    mask_logic_kernel<<<grid, 256, 0, st>>>((uint8_t *)ctx->mask.p, (const uint8_t *)ctx->depth.p, n, op);
+    LAUNCH_CHECK(ctx);
+    STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(mask_inout, ctx->mask.p, n, cudaMemcpyDeviceToHost, st));
+    STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return STEPTH_OK;
+}
+
+extern "C" int32_t stepth_cuda_mask_and(stepth_ctx *ctx, uint8_t *mask_inout, const uint8_t *other, size_t n) {
+    return mask_logic(ctx, mask_inout, other, n, 0);
+}
+extern "C" int32_t stepth_cuda_mask_or(stepth_ctx *ctx, uint8_t *mask_inout, const uint8_t *other, size_t n) {
+    return mask_logic(ctx, mask_inout, other, n, 1);
+}
+extern "C" int32_t stepth_cuda_mask_not(stepth_ctx *ctx, uint8_t *mask_inout, size_t n) {
+    return mask_logic(ctx, mask_inout, nullptr, n, 2);
+}
+
+extern "C" int32_t stepth_cuda_image_replace(stepth_ctx *ctx, uint8_t *rgba_inout, const uint8_t *mask, uint32_t w, uint32_t h,
+                                             const uint8_t *other_rgba, uint32_t ow, uint32_t oh, uint32_t start_x,
+                                             uint32_t start_y) {
+    if (!ctx) return STEPTH_ERR_INVALID_ARG;
+    if (!rgba_inout || !mask || !other_rgba || w == 0 || h == 0 || ow == 0 || oh == 0 || (uint64_t)w * h > 0xffffffffull)
+        return set_err(ctx, STEPTH_ERR_INVALID_ARG, "image_replace: null or empty buffer");
+    // for y in start_y..(start_y + oh).min(h), for x in start_x..(start_x + ow).min(w)      mask_image.rs:101-102
+    const uint32_t x1 = (uint32_t)std::min<uint64_t>((uint64_t)start_x + ow, w), y1 = (uint32_t)std::min<uint64_t>((uint64_t)start_y + oh, h);
+    if (start_x >= x1 || start_y >= y1) return STEPTH_OK;  // empty ranges: nothing happens
+    STEPTH_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const size_t n = (size_t)w * h, no = (size_t)ow * oh;
+    TRY_RC(ensure(ctx, ctx->main_rgba, n * 4));
+    TRY_RC(ensure(ctx, ctx->rgba_out, no * 4));
+    TRY_RC(ensure(ctx, ctx->mask, n));
+    TRY_RC(ensure(ctx, ctx->small, 512));
+    TRY_RC(ensure_host_small(ctx, 512));
+    STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(ctx->small.p, 0, 4, st));
+    STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->main_rgba.p, rgba_inout, n * 4, cudaMemcpyHostToDevice, st));
+    STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->rgba_out.p, other_rgba, no * 4, cudaMemcpyHostToDevice, st));
+    STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->mask.p, mask, n, cudaMemcpyHostToDevice, st));
+    const size_t items = (size_t)(x1 - start_x) * (y1 - start_y);
+    const uint32_t grid = (uint32_t)std::min<size_t>((items + 255) / 256, (size_t)ctx->sm_count * 16);
+    image_replace_kernel<<<grid, 256, 0, st>>>((uint32_t *)ctx->main_rgba.p, (const uint8_t *)ctx->mask.p, w, h,
+                                               (const uint32_t *)ctx->rgba_out.p, ow, oh, start_x, start_y, x1, y1,
+                                               (int32_t *)ctx->small.p);
+    LAUNCH_CHECK(ctx);
+    STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_small, ctx->small.p, 4, cudaMemcpyDeviceToHost, st));
+    STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    const int32_t status = *(const int32_t *)ctx->h_small;
+    if (status != STEPTH_OK)
+        return set_err(ctx, status, "image_replace: a masked pixel of the window lies outside `other` (mask_image.rs:106)");
+    STEPTH_CUDA_TRY(ctx, cudaMemcpy(rgba_inout, ctx->main_rgba.p, n * 4, cudaMemcpyDeviceToHost));
     return STEPTH_OK;
 }
 

@@ -85,6 +85,24 @@ class MaskImage:
     def mask_reset(self):  # mask_image.rs:201-203
         self.mask = np.full(self.image.shape[:2], MASK_TRUE, np.uint8)
 
+    def _context(self) -> Context:
+        return self._ctx or default_context()
+
+    def highlight_mask(self) -> np.ndarray:  # mask_image.rs:57-73 -> RGBA8
+        return self._context().highlight_mask(self.image, self.mask)
+
+    def image_replace(self, other: "MaskImage", start_point) -> None:  # mask_image.rs:99-109
+        self.image = self._context().image_replace(self.image, self.mask, other.image, start_point[0], start_point[1])
+
+    def mask_and(self, other: "MaskImage") -> None:  # mask_image.rs:147-169 (equal sizes)
+        self.mask = self._context().mask_logic("and", self.mask, other.mask)
+
+    def mask_or(self, other: "MaskImage") -> None:  # mask_image.rs:171-193 (equal sizes)
+        self.mask = self._context().mask_logic("or", self.mask, other.mask)
+
+    def mask_not(self) -> None:  # mask_image.rs:195-197
+        self.mask = self._context().mask_logic("not", self.mask)
+
     def apply_mask(self) -> None:  # mask_image.rs:205-213
         ctx = self._ctx or default_context()
         self.image = ctx.apply_mask(self.image, self.mask)
@@ -146,6 +164,9 @@ class DepthImage:
         from PIL import Image
 
         return Image.fromarray(self.depth_plane.copy(), "L")
+
+    def highlight_depth(self) -> np.ndarray:  # :51-63 -> RGBA8
+        return self._context().highlight_depth(self.image, self.depth_plane)
 
     def load_depth(self, depth: np.ndarray) -> None:  # :37-49
         depth = np.ascontiguousarray(depth, dtype=np.uint8)

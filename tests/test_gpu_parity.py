@@ -503,3 +503,60 @@ def test_cpp_host_mirror(ctx, orc, tmp_path):
     r = subprocess.run([exe], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "cpp host mirror ok" in r.stdout
+
+
+# ---- editor operations ---------------------------------------------------------------------------
+@pytest.mark.parametrize("n_side", [(1, 1), (7, 3), (64, 33), (401, 257)])
+def test_editor_ops_vs_oracle(ctx, orc, n_side):
+    import stepth_b200 as sb
+
+    w, h = n_side
+    rng = np.random.default_rng(w * 31 + h)
+    rgba = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+    depth = rng.integers(0, 256, (h, w), dtype=np.uint8)
+    depth.reshape(-1)[: min(3, depth.size)] = [255, 0, 128][: min(3, depth.size)]
+    mask = rng.choice(np.array([0, 255, 254, 1], np.uint8), (h, w))
+    other = rng.choice(np.array([0, 255, 7], np.uint8), (h, w))
+    assert np.array_equal(ctx.highlight_depth(rgba, depth), orc.highlight_depth(rgba, depth))
+    assert np.array_equal(ctx.highlight_mask(rgba, mask), orc.highlight_mask(rgba, mask))
+    for op in ("and", "or"):
+        assert np.array_equal(ctx.mask_logic(op, mask, other), orc.mask_logic(op, mask, other))
+    assert np.array_equal(ctx.mask_logic("not", mask), orc.mask_logic("not", mask))
+    with pytest.raises(sb.StepthIOError):
+        ctx.mask_logic("and", mask, np.zeros((h + 1, w), np.uint8))
+
+
+def test_highlight_depth_every_value_pair(ctx, orc):
+    # all 256 x 256 (channel value, depth) pairs: the f32 product / clamp / truncation must agree everywhere
+    v, d = np.meshgrid(np.arange(256, dtype=np.uint8), np.arange(256, dtype=np.uint8))
+    rgba = np.stack([v, v[::-1], v.T, np.full_like(v, 77)], axis=-1)
+    assert np.array_equal(ctx.highlight_depth(rgba, d), orc.highlight_depth(rgba, d))
+    assert np.array_equal(ctx.highlight_mask(rgba, d), orc.highlight_mask(rgba, d))
+
+
+def test_image_replace_vs_oracle(ctx, orc):
+    import stepth_b200 as sb
+
+    rng = np.random.default_rng(3)
+    for (w, h, ow, oh, sx, sy) in [(50, 40, 50, 40, 0, 0), (50, 40, 60, 45, 10, 5), (33, 17, 40, 30, 32, 16), (20, 20, 5, 5, 25, 0)]:
+        rgba = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+        other = rng.integers(0, 256, (oh, ow, 4), dtype=np.uint8)
+        mask = rng.choice(np.array([0, 255, 200], np.uint8), (h, w))
+        assert np.array_equal(ctx.image_replace(rgba, mask, other, sx, sy), orc.image_replace(rgba, mask, other, sx, sy))
+    # the reference's out-of-bounds panic: a masked pixel of the window at x >= other.width
+    rgba = np.zeros((10, 10, 4), np.uint8)
+    other = np.ones((4, 4, 4), np.uint8)
+    mask = np.full((10, 10), 255, np.uint8)
+    with pytest.raises(sb.StepthPanic) as e:
+        ctx.image_replace(rgba, mask, other, 2, 2)
+    assert e.value.code == 7
+    with pytest.raises(orc.OracleError):
+        orc.image_replace(rgba, mask, other, 2, 2)
+    # through the public classes
+    a, b = sb.MaskImage.from_image(rgba, ctx), sb.MaskImage.from_image(other, ctx)
+    a.mask[:] = 0
+    a.mask[:4, :4] = 255
+    a.image_replace(b, (0, 0))
+    assert a.image[:4, :4].min() == 1 and a.image[4:].max() == 0
+    a.mask_not()
+    assert a.mask[0, 0] == 0 and a.mask[9, 9] == 255

@@ -262,3 +262,50 @@ def test_normalize_brightness(orc):
     rgb2 = np.array([[20, 20, 90], [60, 40, 150]], np.uint16)
     out = orc.normalize_brightness_rgb16(rgb1, rgb2, 0.05)
     assert out.tolist() == [[20, 20, 90], [60, 40, 150]]
+
+
+# ---- editor operations ---------------------------------------------------------------------------
+def test_highlight_depth_and_mask_hand_values(orc):
+    rgba = np.array([[[100, 200, 50, 7], [100, 200, 50, 9], [255, 3, 1, 0], [10, 20, 30, 40]]], np.uint8)
+    # depth_image.rs:51-63: m = d / 255 * 2 ; (v * m) clamped to [0, 255], truncated
+    out = orc.highlight_depth(rgba, np.array([[255, 0, 128, 64]], np.uint8))
+    m128, m64 = np.float32(128) / np.float32(255) * np.float32(2), np.float32(64) / np.float32(255) * np.float32(2)
+    assert out[0, 0].tolist() == [200, 255, 100, 7]          # x2, clamped; alpha untouched
+    assert out[0, 1].tolist() == [0, 0, 0, 9]
+    assert out[0, 2].tolist() == [255, int(np.float32(3) * m128), int(np.float32(1) * m128), 0]
+    assert out[0, 3].tolist() == [int(np.float32(10) * m64), int(np.float32(20) * m64), int(np.float32(30) * m64), 40]
+    # mask_image.rs:57-73: only mask == 255 is highlighted: r*2, g/2, b/2
+    out = orc.highlight_mask(rgba, np.array([[255, 0, 254, 255]], np.uint8))
+    assert out[0, 0].tolist() == [200, 100, 25, 7] and out[0, 1].tolist() == [100, 200, 50, 9]
+    assert out[0, 2].tolist() == [255, 3, 1, 0] and out[0, 3].tolist() == [20, 10, 15, 40]
+
+
+def test_mask_logic(orc):
+    a = np.array([255, 255, 0, 0, 254, 255], np.uint8)
+    b = np.array([255, 0, 255, 0, 255, 1], np.uint8)
+    assert orc.mask_logic("and", a, b).tolist() == [255, 0, 0, 0, 0, 0]      # only exact MASK_TRUE counts
+    assert orc.mask_logic("or", a, b).tolist() == [255, 255, 255, 0, 255, 255]
+    assert orc.mask_logic("not", a).tolist() == [0, 0, 255, 255, 1, 0]
+
+
+def test_image_replace_literal_indexing(orc):
+    # mask_image.rs:99-109 reads other.get_pixel(x, y) with SELF's coordinates (not relative to start_point)
+    rgba = np.zeros((4, 5, 4), np.uint8)
+    other = np.arange(3 * 4 * 4, dtype=np.uint8).reshape(3, 4, 4) + 1
+    mask = np.full((4, 5), 255, np.uint8)
+    mask[1, 2] = 0
+    exp = rgba.copy()
+    for y in range(1, 3):          # 1 .. min(1 + 3, 4) -> rows 1, 2, 3 ; row 3 is outside `other` (oh = 3)
+        for x in range(1, 4):      # 1 .. min(1 + 4, 5) -> cols 1 .. 4 ; col 4 is outside `other` (ow = 4)
+            if mask[y, x] == 255:
+                exp[y, x] = other[y, x]
+    # a masked pixel of the window outside `other` is the reference's out-of-bounds panic
+    with pytest.raises(orc.OracleError) as e:
+        orc.image_replace(rgba, mask, other, 1, 1)
+    assert e.value.code == 7
+    mask[3, :] = 0
+    mask[:, 4] = 0
+    out = orc.image_replace(rgba, mask, other, 1, 1)
+    assert np.array_equal(out, exp)
+    # empty window: start beyond the image
+    assert np.array_equal(orc.image_replace(rgba, mask, other, 5, 0), rgba)
