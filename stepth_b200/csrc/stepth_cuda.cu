@@ -78,6 +78,7 @@ extern "C" int32_t stepth_cuda_ctx_create(int32_t device, stepth_ctx **ctx_out) 
     if (const char *ev = getenv("STEPTH_NEAR_RINGS")) ctx->near_rings = std::max(1, atoi(ev));  // tuning knobs
     if (const char *ev = getenv("STEPTH_MID_RINGS")) ctx->mid_rings = atoi(ev);
     if (const char *ev = getenv("STEPTH_NEAR_COMPACT")) ctx->near_compact = atoi(ev);
+    if (const char *ev = getenv("STEPTH_BATCH_CHUNKS")) ctx->batch_chunks = atoi(ev);
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
         g_create_err = std::string("cudaStreamCreate failed: ") + cudaGetErrorString(e);
         delete ctx;
@@ -370,7 +371,8 @@ int32_t run_pairs(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_rgba, 
     STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(ctx->small.p, 0, sm.bytes, st));
     // The batch is cut into chunks of pairs that move through three streams: copy_in uploads chunk k+1 while the compute
     // stream works on chunk k and copy_out brings chunk k-1 back, so the PCIe transfers hide behind the kernels.
-    const uint32_t chunk = (blocks || n <= 2) ? n : (n + 3) / 4;
+    const uint32_t parts = (uint32_t)std::max(1, ctx->batch_chunks);
+    const uint32_t chunk = (blocks || n <= 2) ? n : (n + parts - 1) / parts;
     const uint32_t n_chunks = (n + chunk - 1) / chunk;
     while (ctx->events.size() < 2 * (size_t)n_chunks + 1) {
         cudaEvent_t e;
