@@ -428,6 +428,14 @@ def run_giant(args, torch, dist, ctx, dev, rank, world, flags):
     total_ms, _ = time_resident(torch, dist, step, args.steps, args.warmup, world)
     clocks = sampler.stop()
     value = args.steps * W * H * D / (total_ms * 1e-3) / 1e6
+    # one more (untimed) run with CUDA events between the stages: where each rank's time goes
+    runner.profile = True
+    runner.run(mb, ab, gather_depth=world > 1)
+    runner.profile = False
+    stage_ms = [runner.stage_ms]
+    if world > 1:
+        stage_ms = [None] * world
+        dist.all_gather_object(stage_ms, runner.stage_ms)
     if rank == 0:
         line = {
             "metric": METRIC, "value": round(value, 3), "unit": METRIC, "n_gpus": world, "steps": args.steps,
@@ -438,6 +446,7 @@ def run_giant(args, torch, dist, ctx, dev, rank, world, flags):
                        "l2": "inputs larger than L2",
                        "parallelism": f"row bands x{world}: allreduce(MAX) + 3-row halo all-gather + NCCL all-gather of depth bands"},
             "roofline": None, "cpu_baseline": None, "e2e": None, "gpu_launches": launches * args.steps, "clocks": clocks,
+            "stage_ms_per_rank": stage_ms,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

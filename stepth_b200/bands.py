@@ -105,6 +105,21 @@ class BandRunner:
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.plan = band_plan(self.h, self.add_h, self.max_rings, self.world)
         self.band = self.plan[self.rank]
+        self.profile = False      # True: `run` brackets its stages with CUDA events and leaves the times in `stage_ms`
+        self.stage_ms: dict[str, float] = {}
+        self._marks: list = []
+
+    def _mark(self, name: str) -> None:
+        if self.profile:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            self._marks.append((name, ev))
+
+    def _close_marks(self) -> None:
+        if self.profile and self._marks:
+            torch.cuda.synchronize()
+            self.stage_ms = {b[0]: round(a[1].elapsed_time(b[1]), 4) for a, b in zip(self._marks, self._marks[1:])}
+            self._marks = []
 
     # ---- exchange steps ------------------------------------------------------------------------------------------
     def _allreduce(self, t: torch.Tensor, op) -> torch.Tensor:
@@ -157,14 +172,17 @@ class BandRunner:
         b, f = self.band, self.flags
         dev = main_band.device
         rows = b.y1 - b.y0
+        self._mark("start")
         if rows > 0:
             d8, mx = self.st.search(main_band, add_band, self.precision, self.max_rings, f, b.y0, b.ay0, self.add_h, self.h)
             mx = mx.to(torch.int32)
         else:
             d8 = torch.empty((1, 0, self.w), dtype=torch.uint8, device=dev)
             mx = torch.zeros(1, dtype=torch.int32, device=dev)
+        self._mark("search")
         mx = self._allreduce(mx, dist.ReduceOp.MAX)                      # exchange 1: the normaliser
         src, src_y0 = self.exchange_halos(d8)                            # exchange 2: 3-row halos
+        self._mark("allreduce_max+halos")
         want_fg = bool(f & _ffi.FLAG_FOREGROUND)
         hist = torch.zeros((1, 256), dtype=torch.int32, device=dev) if want_fg else None
         out = {}
@@ -177,6 +195,7 @@ class BandRunner:
         # max == 0 is a property of the whole image: every rank sees the same all-reduced value
         out["status"] = _ffi.ERR_DIV_BY_ZERO_MAX if int(mx[0]) == 0 else int(status[0]) if rows > 0 else 0
         out["depth_band"] = depth
+        self._mark("finish")
         if want_fg and out["status"] == 0:
             hist = self._allreduce(hist, dist.ReduceOp.SUM)              # exchange 3: the histogram
             ranges, n_out, st2 = self.st.depth_split(hist)
@@ -189,6 +208,8 @@ class BandRunner:
                     out["mask_band"], out["rgba_band"] = mask, rgba_out
         if gather_depth:                                                 # exchange 4: assemble the map everywhere
             out["depth"] = self.gather_bands(depth)
+        self._mark("tail+gather")
+        self._close_marks()
         return out
 
     def gather_bands(self, band: torch.Tensor) -> torch.Tensor:
