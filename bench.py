@@ -164,6 +164,17 @@ def cpu_baseline(kind: str, budget_s: float = 20.0):
             "sample": f"{done} whole {W}x{H} '{kind}' pair(s), D={D}, oracle depth_dense with {threads} threads, {t_total:.1f} s"}
 
 
+def algorithmic_probes(kind: str):
+    """probes the reference's scan order needs per query (every pixel of a ring counted once), counted
+    by the oracle on pair seed 1 of the bench batch (the pairs of a batch are draws of the same distribution)"""
+    from oracle import oracle
+    from stepth_b200 import synth
+
+    m, a = synth.make_pair(kind, W, H, seed=1)
+    oracle.search_dense(m.numpy(), a.numpy(), PRECISION, D, threads=os.cpu_count() or 1, want_probes=True)
+    return oracle.last_unique_probes() / float(W * H)
+
+
 def run_reference(args):
     """--impl reference: the CPU port with the reference's own parallelism (8-9 chunks), each step one pair"""
     rank = int(os.environ.get("RANK", "0"))
@@ -376,6 +387,21 @@ def run_ours(args):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline(args.kind)
+        # the other half of SURVEY 8(d)'s roofline, t_roof = max(B_alg / BW_HBM, O_alg / P_INT): O_alg = 2 integer ops
+        # per probe of the reference order (oracle-counted), P_INT measured on this GPU by a register-only kernel
+        probes_q = algorithmic_probes(args.kind)
+        p_mixed, p_logic = ctx.int_peak(False), ctx.int_peak(True)
+        ops = 2.0 * probes_q * W * H * SUB
+        t_int_ms, t_hbm_ms = ops / p_mixed * 1e3, alg / (hbm * 1e9) * 1e3
+        roofline["int"] = {
+            "bound": "int-alu", "unit": "Tiop/s", "ops_per_launch": round(ops), "probes_per_query": round(probes_q, 2),
+            "achieved": round(ops / (search_launch_ms * 1e-3) / 1e12, 3), "peak": round(p_mixed / 1e12, 3),
+            "frac": round(ops / (search_launch_ms * 1e-3) / p_mixed, 4), "peak_logic_only": round(p_logic / 1e12, 3),
+            "peak_source": "measured (stepth_cuda_int_peak: LOP3+IMAD.IADD on both integer pipes; logic_only = LOP3+SHF, alu pipe)",
+            "t_roof_ms": round(max(t_int_ms, t_hbm_ms), 4), "t_hbm_ms": round(t_hbm_ms, 4), "t_int_ms": round(t_int_ms, 4),
+            "frac_of_t_roof": round(max(t_int_ms, t_hbm_ms) / search_launch_ms, 4),
+            "note": "O_alg = 2 ops x probes the reference order needs (oracle count, seed-1 pair x pairs per launch); "
+                    "the tile search skips probes, so frac may exceed 1 (SURVEY.md 8(d))"}
 
     if rank == 0:
         line = {

@@ -201,6 +201,12 @@ int32_t stepth_cuda_dev_histogram(stepth_ctx *ctx, void *stream, const uint8_t *
 /* number of kernel launches issued by this context so far (bench.py's gpu_launches) */
 uint64_t stepth_cuda_launch_count(const stepth_ctx *ctx);
 
+/* Measurement aid (no reference counterpart): the rate at which this device retires 32-bit logic/add instructions
+ * (thread-level ops per second), measured with a register-only kernel: logic_only = 0 mixes LOP3 with adds (both
+ * integer pipes, the highest rate any integer mix reaches), 1 = LOP3 + SHF (the alu pipe alone, the search's class).  bench.py divides the search's algorithmic
+ * integer work (2 ops per probe of the reference order, src/helpers.rs:26-47) by it. */
+int32_t stepth_cuda_int_peak(stepth_ctx *ctx, int32_t logic_only, double *ops_per_second_out);
+
 #ifdef __cplusplus
 }
 #endif

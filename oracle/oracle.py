@@ -156,6 +156,14 @@ def search_dense(main_px, add_rgb, precision, max_rings=255, pixelopps=PIXELOPPS
     return (out, int(pr.value)) if want_probes else out
 
 
+def last_unique_probes() -> int:
+    """in-bounds probes of the last search_* call, every pixel of a ring counted once (SURVEY.md 8(d) work figure)"""
+    f = lib().orc_last_unique_probes
+    f.restype = C.c_uint64
+    f.argtypes = []
+    return int(f())
+
+
 def search_dense_subset(main_px, add_rgb, precision, indices, max_rings=255, pixelopps=PIXELOPPS_ABS_ALL, threads=0):
     main_px = np.ascontiguousarray(main_px, dtype=np.uint8)
     add_rgb = np.ascontiguousarray(add_rgb, dtype=np.uint8)

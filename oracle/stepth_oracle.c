@@ -65,12 +65,12 @@ static inline int pixel_matches(const uint8_t *v, const uint8_t *what, const uin
  *           Some(v): still_in_bounds = true; match => return (distance, pos)   :33-41
  *     if !still_in_bounds: break                                  :49-51
  * ---------------------------------------------------------------------------------------------- */
-int orc_distance_dot_array(const uint8_t what[3], const uint8_t *add_rgb, uint32_t wa, uint32_t ha,
-                           uint32_t from_x, uint32_t from_y, uint32_t max, const uint8_t precision[3],
-                           int pixelopps, uint32_t *dist, uint32_t *pos_x, uint32_t *pos_y,
-                           uint64_t *probes) {
+static int dda_impl(const uint8_t what[3], const uint8_t *add_rgb, uint32_t wa, uint32_t ha,
+                    uint32_t from_x, uint32_t from_y, uint32_t max, const uint8_t precision[3],
+                    int pixelopps, uint32_t *dist, uint32_t *pos_x, uint32_t *pos_y,
+                    uint64_t *probes, uint64_t *unique) {
     const int64_t x = (int64_t)from_x, y = (int64_t)from_y;
-    uint64_t n_probes = 0;
+    uint64_t n_probes = 0, n_unique = 0;
     for (int64_t step = 0; step < (int64_t)max; ++step) {
         int still_in_bounds = 0;
         for (int pass = 0; pass < 2; ++pass) {
@@ -89,11 +89,16 @@ int orc_distance_dot_array(const uint8_t what[3], const uint8_t *add_rgb, uint32
                     const uint8_t *v = add_rgb + ((size_t)point_y * wa + (size_t)point_x) * 3;
                     still_in_bounds = 1;
                     ++n_probes;
+                    /* a probe repeats an earlier one of the same ring when it is a corner of the column pass, or any
+                     * probe of ring 0 after the first (bench.py's algorithmic-work figure counts each pixel once) */
+                    if (step == 0 ? (pass == 0 && k == 0) : (order || (j != sub_c - step && j != sub_c + step)))
+                        ++n_unique;
                     if (pixel_matches(v, what, precision, pixelopps)) {
                         if (dist) *dist = orc_distance_dot_dot(from_x, from_y, (uint32_t)point_x, (uint32_t)point_y);
                         if (pos_x) *pos_x = (uint32_t)point_x;
                         if (pos_y) *pos_y = (uint32_t)point_y;
                         if (probes) *probes = n_probes;
+                        if (unique) *unique = n_unique;
                         return 1;
                     }
                 }
@@ -102,7 +107,15 @@ int orc_distance_dot_array(const uint8_t what[3], const uint8_t *add_rgb, uint32
         if (!still_in_bounds) break;
     }
     if (probes) *probes = n_probes;
+    if (unique) *unique = n_unique;
     return 0;
+}
+
+int orc_distance_dot_array(const uint8_t what[3], const uint8_t *add_rgb, uint32_t wa, uint32_t ha,
+                           uint32_t from_x, uint32_t from_y, uint32_t max, const uint8_t precision[3],
+                           int pixelopps, uint32_t *dist, uint32_t *pos_x, uint32_t *pos_y,
+                           uint64_t *probes) {
+    return dda_impl(what, add_rgb, wa, ha, from_x, from_y, max, precision, pixelopps, dist, pos_x, pos_y, probes, NULL);
 }
 
 /* ------------------------------------------------------------------------------------------------
@@ -123,12 +136,12 @@ typedef struct {
     int pixelopps;
     size_t begin, end;
     uint8_t *d8_out;
-    uint64_t probes;
+    uint64_t probes, unique;
 } search_job;
 
 static void *search_worker(void *arg) {
     search_job *jb = (search_job *)arg;
-    uint64_t total = 0;
+    uint64_t total = 0, total_u = 0;
     for (size_t i = jb->begin; i < jb->end; ++i) {
         uint8_t what[3];
         uint32_t mx, my;
@@ -147,15 +160,21 @@ static void *search_worker(void *arg) {
             what[0] = m[0]; what[1] = m[1]; what[2] = m[2];
         }
         uint32_t d = 0; /* .unwrap_or((u32::MIN, Position::new(0,0)))   depth_image.rs:120 */
-        uint64_t pr = 0;
-        orc_distance_dot_array(what, jb->add_rgb, jb->wa, jb->ha, mx, my, jb->max_rings, jb->precision,
-                               jb->pixelopps, &d, NULL, NULL, &pr);
+        uint64_t pr = 0, un = 0;
+        dda_impl(what, jb->add_rgb, jb->wa, jb->ha, mx, my, jb->max_rings, jb->precision,
+                 jb->pixelopps, &d, NULL, NULL, &pr, &un);
         total += pr;
+        total_u += un;
         jb->d8_out[i] = (uint8_t)d; /* `d as u8`: wraps mod 256   depth_image.rs:121 */
     }
     jb->probes = total;
+    jb->unique = total_u;
     return NULL;
 }
+
+static uint64_t g_last_unique; /* unique probes of the last run_search (read by orc_last_unique_probes; bench bookkeeping) */
+
+uint64_t orc_last_unique_probes(void) { return g_last_unique; }
 
 static int32_t run_search(search_job proto, size_t n, int threads, uint64_t *probes_total) {
     if (n == 0) return ORC_TOO_FEW_BLOCKS;
@@ -186,6 +205,11 @@ static int32_t run_search(search_job proto, size_t n, int threads, uint64_t *pro
         uint64_t t = 0;
         for (size_t c = 0; c < n_chunks; ++c) t += jobs[c].probes;
         *probes_total = t;
+    }
+    {
+        uint64_t t = 0;
+        for (size_t c = 0; c < n_chunks; ++c) t += jobs[c].unique;
+        g_last_unique = t;
     }
     free(jobs);
     free(tids);

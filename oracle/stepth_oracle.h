@@ -75,6 +75,11 @@ int32_t orc_search_dense(const uint8_t *main_px, uint32_t main_stride, uint32_t 
                          uint32_t max_rings, int pixelopps, int threads, uint8_t *d8_out,
                          uint64_t *probes_total);
 
+/* in-bounds probes of the last orc_search_* call with every pixel of a ring counted once (the reference probes the
+ * corners of a ring twice and ring 0 four times, helpers.rs:28-31): the algorithmic-work figure of SURVEY.md 8(d).
+ * Not thread safe across concurrent searches; bench bookkeeping only. */
+uint64_t orc_last_unique_probes(void);
+
 /* as orc_search_dense but only for the listed pixel indices (y*w+x); used for bounded CPU-baseline samples */
 int32_t orc_search_dense_subset(const uint8_t *main_px, uint32_t main_stride, uint32_t w, uint32_t h,
                                 const uint8_t *add_rgb, uint32_t wa, uint32_t ha, const uint8_t precision[3],

@@ -91,6 +91,7 @@ SIGNATURES = {
     "stepth_cuda_dev_mask_apply": (_i32, [_vp, _vp, _u32, _sz, _u8p, _u8p, _u32, _i32p, _u8p, _u8p, _u8p]),
     "stepth_cuda_dev_histogram": (_i32, [_vp, _vp, _u8p, _sz, _u32p]),
     "stepth_cuda_launch_count": (C.c_uint64, [_vp]),
+    "stepth_cuda_int_peak": (_i32, [_vp, _i32, C.POINTER(C.c_double)]),
 }
 
 _lib = None

@@ -87,6 +87,14 @@ class Context:
     def launch_count(self) -> int:
         return int(self._lib.stepth_cuda_launch_count(self._h))
 
+    def int_peak(self, logic_only: bool = False) -> float:
+        """measured 32-bit logic/add ops per second of this device (measurement aid for bench.py's int roofline)"""
+        import ctypes as C
+
+        v = C.c_double(0.0)
+        self.check(self._lib.stepth_cuda_int_peak(self._h, int(logic_only), C.byref(v)))
+        return float(v.value)
+
     def check(self, rc: int):
         if rc == _ffi.OK:
             return

@@ -11,6 +11,7 @@
 #include "search_hier.cuh"
 #include "tail.cuh"
 #include "brightness.cuh"
+#include "intpeak.cuh"
 #include "edit.cuh"
 
 #include <algorithm>
@@ -771,6 +772,13 @@ extern "C" int32_t stepth_cuda_normalize_brightness_rgb16(stepth_ctx *ctx, const
                                                           const uint16_t *img2, size_t n2, double percent,
                                                           uint16_t *out) {
     return brightness(ctx, img1, n1, img2, n2, percent, out, 3);
+}
+
+// measured integer-ALU peak (LOP3/IADD3 class) of the context's device: bench.py's int-roofline denominator
+extern "C" int32_t stepth_cuda_int_peak(stepth_ctx *ctx, int32_t logic_only, double *ops_per_second_out) {
+    if (!ctx || !ops_per_second_out) return set_err(ctx, STEPTH_ERR_INVALID_ARG, "int_peak: null argument");
+    STEPTH_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    return measure_int_peak(ctx, logic_only != 0, ops_per_second_out);
 }
 
 // ============================================================================================================
