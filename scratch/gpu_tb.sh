@@ -1,0 +1,9 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
+timeout 600 python bench.py --steps 5 --warmup 3 --extra-kinds --no-cpu-baseline --no-e2e > gpurun_out/b.json 2> gpurun_out/b.err; echo "bench rc=$?"; tail -3 gpurun_out/b.err
+python - <<'PY'
+import json
+d=json.load(open('gpurun_out/b.json')); o=d.get('other_distributions',{})
+print("nat step", d['ms_per_step'], "search", d['roofline']['launch_ms'], " geo", o['geo']['search_ms_per_launch'], " worst", o['worst']['search_ms_per_launch'])
+PY

@@ -79,6 +79,14 @@ STEPTH_HD bool box_contains(const ColourBox &bx, uint32_t r, uint32_t g, uint32_
            b >= ((bx.lo >> 16) & 0xff) && b <= ((bx.hi >> 16) & 0xff);
 }
 
+// the predicate on one pixel straight from the definition (no box): abs/all |v_c - q_c| < p_c, sat/all sat_sub(v_c, q_c) < p_c
+STEPTH_HD bool pixel_in_box(uint32_t r, uint32_t g, uint32_t b, uint32_t col, uint32_t pr, uint32_t pg, uint32_t pb, bool sat) {
+    int dr = (int)r - (int)(col & 0xffu), dg = (int)g - (int)((col >> 8) & 0xffu), db = (int)b - (int)((col >> 16) & 0xffu);
+    if (sat) { dr = dr < 0 ? 0 : dr; dg = dg < 0 ? 0 : dg; db = db < 0 ? 0 : db; }
+    else { dr = dr < 0 ? -dr : dr; dg = dg < 0 ? -dg : dg; db = db < 0 ? -db : db; }
+    return dr < (int)pr && dg < (int)pg && db < (int)pb;
+}
+
 // floor(sqrt(n)) for n < 2^24: what `((dx^2 + dy^2) as f64).sqrt() as u32` yields (helpers.rs:3-7).
 STEPTH_HD uint32_t isqrt_u32(uint32_t n) {
 #ifdef __CUDA_ARCH__

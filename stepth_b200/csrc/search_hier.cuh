@@ -296,6 +296,7 @@ __device__ __forceinline__ void query_of(const SearchArgs &s, uint32_t pair, uin
     }
 }
 
+template <bool ONE_PAIR = false>  // ONE_PAIR: every lane of the warp works on the same pair (near kernel)
 __device__ __forceinline__ void publish_result(const SearchArgs &s, uint32_t pair, uint32_t qi, uint32_t key, bool active) {
     uint32_t d = 0;
     if (active) {
@@ -304,7 +305,13 @@ __device__ __forceinline__ void publish_result(const SearchArgs &s, uint32_t pai
     }
     // per-pair maximum: lanes of a warp may belong to different pairs only in the far kernel; match on the pair there
     const uint32_t mask = __activemask();
-    const uint32_t peers = __match_any_sync(mask, active ? pair : 0xffffffffu);
+    uint32_t peers;
+    if (ONE_PAIR) {  // two groups: the lanes with a result, and the rest (a lane must be a member of the mask it names)
+        const uint32_t act = __ballot_sync(mask, active);
+        peers = active ? act : (mask & ~act);
+    } else {
+        peers = __match_any_sync(mask, active ? pair : 0xffffffffu);
+    }
     const uint32_t m = __reduce_max_sync(peers, d);
     if (active && m && (threadIdx.x & 31) == (uint32_t)(__ffs(peers) - 1)) {
         if (m > *(volatile uint32_t *)(s.max_out + pair)) atomicMax(s.max_out + pair, m);
@@ -481,14 +488,14 @@ __global__ void __launch_bounds__(256, STEPTH_NEAR_MINB) search_near_kernel(Hier
     const uint32_t pair = BLOCKS ? 0u : blockIdx.z;
     const int tid = threadIdx.x;
     bool valid;
-    uint32_t qi = 0;
+    uint32_t qi = 0, X = 0, Y = 0;
     if (BLOCKS) {
         qi = blockIdx.x * 256u + tid;
         valid = qi < s.n_queries;
     } else {
         const int lane = tid & 31, warp = tid >> 5;
-        const uint32_t X = blockIdx.x * 32u + (warp & 3) * 8u + (lane & 7);
-        const uint32_t Y = blockIdx.y * 8u + (warp >> 2) * 4u + (lane >> 3);
+        X = blockIdx.x * 32u + (warp & 3) * 8u + (lane & 7);
+        Y = blockIdx.y * 8u + (warp >> 2) * 4u + (lane >> 3);
         valid = X < s.w && Y < s.h;
         qi = Y * s.w + X;
     }
@@ -498,7 +505,13 @@ __global__ void __launch_bounds__(256, STEPTH_NEAR_MINB) search_near_kernel(Hier
     uint32_t col = 0;
     if (valid) {
         int oyg;
-        query_of<BLOCKS>(s, pair, qi, ox, oyg, col);
+        if (BLOCKS) {
+            query_of<true>(s, pair, qi, ox, oyg, col);
+        } else {  // query_of<false> without the division: X, Y are at hand
+            ox = (int)((X + 1) >> 1);
+            oyg = (int)((Y + s.y0 + 1) >> 1);
+            col = reinterpret_cast<const uint32_t *>(s.main_rgba)[(size_t)pair * s.n_queries + qi] & 0xffffffu;
+        }
         const int src_wa = (int)s.wa, src_ha = (int)s.ha;
         // ring 0 out of bounds => `still_in_bounds` stays false => break => None   (helpers.rs:49-51)
         if (ox < src_wa && oyg < (int)s.add_img_h) {
@@ -506,8 +519,7 @@ __global__ void __launch_bounds__(256, STEPTH_NEAR_MINB) search_near_kernel(Hier
             bool hit0 = false;
             if (oyl >= 0 && oyl < src_ha) {
                 const uint8_t *px = s.add_rgb + (size_t)pair * src_ha * src_wa * 3 + ((size_t)oyl * src_wa + ox) * 3;
-                const ColourBox box = make_box(col & 0xff, (col >> 8) & 0xff, (col >> 16) & 0xff, s.pr, s.pg, s.pb, s.sat != 0);
-                hit0 = box_contains(box, px[0], px[1], px[2]);
+                hit0 = pixel_in_box(px[0], px[1], px[2], col, s.pr, s.pg, s.pb, s.sat != 0);
             }
             if (hit0) key = 0;
             else open = s.max_rings > 1;
@@ -516,7 +528,8 @@ __global__ void __launch_bounds__(256, STEPTH_NEAR_MINB) search_near_kernel(Hier
     if (COMPACT) {
         // Ring 0 settles about half of the queries of a natural pair; the rest are packed into the first warps of the CTA
         // so that the walk runs with full warps (and the other warps retire).
-        publish_result(s, pair, qi, key, valid && !open);
+        // settled at ring 0: a hit has distance 0 and `None` maps to 0 too (depth_image.rs:120), neither moves the maximum
+        if (valid && !open) s.d8[(size_t)pair * s.n_queries + qi] = 0;
         const int lane = tid & 31, warp = tid >> 5;
         const uint32_t bal = __ballot_sync(0xffffffffu, open);
         if (lane == 0) s_cnt[warp] = __popc(bal);
@@ -537,7 +550,7 @@ __global__ void __launch_bounds__(256, STEPTH_NEAR_MINB) search_near_kernel(Hier
         key = KEY_NONE;
         const bool still = !hier_rings_warp(has, a.planes, a.g, pair, q, (int)s.max_rings, 0, a.S1, s_le, s_ge, key, &s_ws[warp]);
         export_open(a, has && still, pair, e.x, key);
-        publish_result(s, pair, e.x, key, has && !still);
+        publish_result<true>(s, pair, e.x, key, has && !still);
         return;
     }
     if (__any_sync(0xffffffffu, open)) {
@@ -545,7 +558,7 @@ __global__ void __launch_bounds__(256, STEPTH_NEAR_MINB) search_near_kernel(Hier
         open = !hier_rings_warp(open, a.planes, a.g, pair, q, (int)s.max_rings, 0, a.S1, s_le, s_ge, key, &s_ws[tid >> 5]);
     }
     export_open(a, open, pair, qi, key);
-    publish_result(s, pair, qi, key, valid && !open);
+    publish_result<true>(s, pair, qi, key, valid && !open);
 }
 
 // FAR kernel: resumes the listed queries at coarse ring S0; a warp pulls 32 consecutive entries at a time.
