@@ -357,18 +357,41 @@ STEPTH_HD int tile_smin(const HierQuery &q, int TX, int TY) {
     return dxm > dym ? dxm : dym;
 }
 
+// keeps the bits i of m with tmin <= lo + i <= tmax
+__device__ __forceinline__ unsigned long long keep_range(unsigned long long m, int lo, int tmin, int tmax) {
+    int a = tmin - lo, b = tmax - lo;
+    a = a < 0 ? 0 : a;
+    if (b < a || a > 63) return 0ull;
+    b = b > 63 ? 63 : b;
+    return m & (~0ull << a) & (~0ull >> (63 - b));
+}
+
+// Drops the flagged tiles of ring S that cannot hold the answer: a tile whose nearest pixel lies beyond `limit` (the best
+// ring so far, or max_rings - 1).  A whole side goes when its line is too far; along the side the tiles within reach are a
+// run, so the pruning is one bit-range mask per side instead of a distance per tile.
+__device__ __forceinline__ void prune_sides(const HierQuery &q, int S, int limit, int rlo, int clo, unsigned long long &f0,
+                                            unsigned long long &f1, unsigned long long &f2, unsigned long long &f3) {
+    const int T0x = q.ox >> 3, T0y = q.oy >> 3;
+    const int xa = (q.ox - limit) >> 3, xb = (q.ox + limit) >> 3;   // tile columns with a pixel at |dx| <= limit
+    const int ya = (q.oy - limit) >> 3, yb = (q.oy + limit) >> 3;
+    f0 = (T0y + S) * 8 - q.oy > limit ? 0ull : keep_range(f0, rlo, xa, xb);
+    f1 = q.oy - ((T0y - S) * 8 + 7) > limit ? 0ull : keep_range(f1, rlo, xa, xb);
+    f2 = (T0x + S) * 8 - q.ox > limit ? 0ull : keep_range(f2, clo, ya, yb);
+    f3 = q.ox - ((T0x - S) * 8 + 7) > limit ? 0ull : keep_range(f3, clo, ya, yb);
+}
+
 // Lists the flagged tiles of one side of a ring as tasks of the warp, skipping tiles that cannot hold the answer (nearest
 // pixel beyond `limit` = the best ring so far, or max_rings - 1).  Returns the bits that did not fit into this pass.
-__device__ __forceinline__ unsigned long long emit_side(unsigned long long m, int lo, int line, bool is_col, const HierQuery &q,
-                                                        int limit, uint32_t lane, WarpScratch *ws) {
+__device__ __forceinline__ unsigned long long emit_side(unsigned long long m, int lo, int line, bool is_col, uint32_t lane,
+                                                        WarpScratch *ws) {
+    // task = owner << 26 | TX << 13 | TY: row sides step TX (bit 13), column sides step TY (bit 0)
+    const uint32_t code = lane << 26 | (is_col ? (uint32_t)line << 13 | (uint32_t)lo : (uint32_t)lo << 13 | (uint32_t)line);
+    const int sh = is_col ? 0 : 13;
     while (m) {
-        const int p = lo + __ffsll((long long)m) - 1;
-        const int TX = is_col ? line : p, TY = is_col ? p : line;
-        if (tile_smin(q, TX, TY) <= limit) {
-            const uint32_t slot = atomicAdd(&ws->n, 1u);
-            if (slot >= (uint32_t)WTASKS) return m;
-            ws->task[slot] = lane << 26 | (uint32_t)TX << 13 | (uint32_t)TY;
-        }
+        const int i = __ffsll((long long)m) - 1;
+        const uint32_t slot = atomicAdd(&ws->n, 1u);
+        if (slot >= (uint32_t)WTASKS) return m;
+        ws->task[slot] = code + ((uint32_t)i << sh);
         m &= m - 1;
     }
     return 0ull;
@@ -436,10 +459,11 @@ __device__ __forceinline__ bool hier_rings_warp(bool walking, const uint8_t *pla
             if (f0 | f1 | f2 | f3) {
                 // with a match in hand (or at the last rings) most flagged tiles are out of reach and are not listed
                 const int limit = min(D - 1, (int)(best >> 12));
-                f0 = emit_side(f0, rlo, T0y + S, false, q, limit, lane, ws);
-                if (!f0) f1 = emit_side(f1, rlo, T0y - S, false, q, limit, lane, ws);
-                if (!(f0 | f1)) f2 = emit_side(f2, clo, T0x + S, true, q, limit, lane, ws);
-                if (!(f0 | f1 | f2)) f3 = emit_side(f3, clo, T0x - S, true, q, limit, lane, ws);
+                if (limit < 8 * S + 7) prune_sides(q, S, limit, rlo, clo, f0, f1, f2, f3);  // else every tile of the ring is in reach
+                f0 = emit_side(f0, rlo, T0y + S, false, lane, ws);
+                if (!f0) f1 = emit_side(f1, rlo, T0y - S, false, lane, ws);
+                if (!(f0 | f1)) f2 = emit_side(f2, clo, T0x + S, true, lane, ws);
+                if (!(f0 | f1 | f2)) f3 = emit_side(f3, clo, T0x - S, true, lane, ws);
             }
             __syncwarp();
             const int n_pass = (int)min(ws->n, (uint32_t)WTASKS);
