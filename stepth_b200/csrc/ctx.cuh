@@ -29,10 +29,11 @@ struct stepth_ctx {
     // scratch for the host-buffer entry points
     Buf main_rgba, add_rgb, d8, depth, mask, rgba_out, blocks, plane, small, u16a, u16b, u16o, work;
     Buf worklist;  // two [count, cursor, pad..][uint2 entries] lists: queries handed from the near to the far kernel(s)
-    int near_rings = 4;  // coarse rings the near kernel walks (STEPTH_NEAR_RINGS)
+    int near_rings = 6;  // coarse rings the near kernel walks (STEPTH_NEAR_RINGS)
     int batch_chunks = 4;  // the batch entry point pipelines this many chunks of pairs over its three streams (STEPTH_BATCH_CHUNKS)
+    int upload_full_rows = 0;  // host-buffer entry points upload whole rows of the additional image (STEPTH_UPLOAD_FULL_ROWS)
     int near_compact = 1;  // the near kernel packs the queries that survive ring 0 into full warps (STEPTH_NEAR_COMPACT)
-    int mid_rings = 8;   // first far kernel walks coarse rings [near_rings, mid_rings); 0 = one far kernel (STEPTH_MID_RINGS)
+    int mid_rings = 10;  // first far kernel walks coarse rings [near_rings, mid_rings); 0 = one far kernel (STEPTH_MID_RINGS)
     Buf planes;  // two-level match bit-planes of the additional image(s) (tiles.cuh), rebuilt by every search
     // small per-pair state: [max u32][hist 256 u32][status i32][n_out u32][ranges 512 B] per pair
     void *h_small = nullptr;  // pinned mirror
