@@ -380,21 +380,23 @@ __device__ __forceinline__ void prune_sides(const HierQuery &q, int S, int limit
     f3 = q.ox - ((T0x - S) * 8 + 7) > limit ? 0ull : keep_range(f3, clo, ya, yb);
 }
 
-// Lists the flagged tiles of one side of a ring as tasks of the warp, skipping tiles that cannot hold the answer (nearest
-// pixel beyond `limit` = the best ring so far, or max_rings - 1).  Returns the bits that did not fit into this pass.
+// Lists the flagged tiles of one side of a ring as tasks of the warp from slot `slot` on (the lane reserved its slots with
+// one atomic for all four sides); the bits that do not fit below WTASKS come back and are listed again in the next pass.
 __device__ __forceinline__ unsigned long long emit_side(unsigned long long m, int lo, int line, bool is_col, uint32_t lane,
-                                                        WarpScratch *ws) {
+                                                        uint32_t &slot, WarpScratch *ws) {
     // task = owner << 26 | TX << 13 | TY: row sides step TX (bit 13), column sides step TY (bit 0)
     const uint32_t code = lane << 26 | (is_col ? (uint32_t)line << 13 | (uint32_t)lo : (uint32_t)lo << 13 | (uint32_t)line);
     const int sh = is_col ? 0 : 13;
-    while (m) {
-        const int i = __ffsll((long long)m) - 1;
-        const uint32_t slot = atomicAdd(&ws->n, 1u);
-        if (slot >= (uint32_t)WTASKS) return m;
-        ws->task[slot] = code + ((uint32_t)i << sh);
-        m &= m - 1;
+    uint32_t w0 = (uint32_t)m, w1 = (uint32_t)(m >> 32);
+    while (w0 && slot < (uint32_t)WTASKS) {
+        ws->task[slot++] = code + ((uint32_t)(__ffs((int)w0) - 1) << sh);
+        w0 &= w0 - 1;
     }
-    return 0ull;
+    while (!w0 && w1 && slot < (uint32_t)WTASKS) {
+        ws->task[slot++] = code + ((uint32_t)(__ffs((int)w1) + 31) << sh);
+        w1 &= w1 - 1;
+    }
+    return (unsigned long long)w1 << 32 | w0;
 }
 
 // All 32 lanes call this together.  `walking` lanes carry a query (v, q, best); the others only help with tile tests.
@@ -460,10 +462,14 @@ __device__ __forceinline__ bool hier_rings_warp(bool walking, const uint8_t *pla
                 // with a match in hand (or at the last rings) most flagged tiles are out of reach and are not listed
                 const int limit = min(D - 1, (int)(best >> 12));
                 if (limit < 8 * S + 7) prune_sides(q, S, limit, rlo, clo, f0, f1, f2, f3);  // else every tile of the ring is in reach
-                f0 = emit_side(f0, rlo, T0y + S, false, lane, ws);
-                if (!f0) f1 = emit_side(f1, rlo, T0y - S, false, lane, ws);
-                if (!(f0 | f1)) f2 = emit_side(f2, clo, T0x + S, true, lane, ws);
-                if (!(f0 | f1 | f2)) f3 = emit_side(f3, clo, T0x - S, true, lane, ws);
+                const uint32_t cnt = __popcll(f0) + __popcll(f1) + __popcll(f2) + __popcll(f3);
+                if (cnt) {
+                    uint32_t slot = atomicAdd(&ws->n, cnt);  // slots [slot, slot + cnt); those beyond WTASKS wait for the next pass
+                    f0 = emit_side(f0, rlo, T0y + S, false, lane, slot, ws);
+                    f1 = emit_side(f1, rlo, T0y - S, false, lane, slot, ws);
+                    f2 = emit_side(f2, clo, T0x + S, true, lane, slot, ws);
+                    f3 = emit_side(f3, clo, T0x - S, true, lane, slot, ws);
+                }
             }
             __syncwarp();
             const int n_pass = (int)min(ws->n, (uint32_t)WTASKS);
