@@ -507,85 +507,110 @@ __device__ __forceinline__ bool hier_rings_warp(bool walking, const uint8_t *pla
 #ifndef STEPTH_FAR_MINB
 #define STEPTH_FAR_MINB 10
 #endif
+#ifndef STEPTH_NEAR_KP
+#define STEPTH_NEAR_KP 4     // COMPACT: 32x8-pixel patches (or 256-block slices) one CTA settles before it walks
+#endif
+
+// ring 0 of one query (helpers.rs:26-47 with step = 0): `open` = the walk has to go on
+template <bool BLOCKS>
+__device__ __forceinline__ void ring0_of(const SearchArgs &s, uint32_t pair, uint32_t qi, uint32_t X, uint32_t Y, int &ox, int &oyl,
+                                         uint32_t &col, uint32_t &key, bool &open) {
+    int oyg;
+    if (BLOCKS) {
+        query_of<true>(s, pair, qi, ox, oyg, col);
+    } else {  // query_of<false> without the division: X, Y are at hand
+        ox = (int)((X + 1) >> 1);
+        oyg = (int)((Y + s.y0 + 1) >> 1);
+        col = reinterpret_cast<const uint32_t *>(s.main_rgba)[(size_t)pair * s.n_queries + qi] & 0xffffffu;
+    }
+    const int src_wa = (int)s.wa, src_ha = (int)s.ha;
+    // ring 0 out of bounds => `still_in_bounds` stays false => break => None   (helpers.rs:49-51)
+    if (ox < src_wa && oyg < (int)s.add_img_h) {
+        oyl = oyg - (int)s.add_y0;  // origin row inside the sub-image held on this device
+        bool hit0 = false;
+        if (oyl >= 0 && oyl < src_ha) {
+            const uint8_t *px = s.add_rgb + (size_t)pair * src_ha * src_wa * 3 + ((size_t)oyl * src_wa + ox) * 3;
+            hit0 = pixel_in_box(px[0], px[1], px[2], col, s.pr, s.pg, s.pb, s.sat != 0);
+        }
+        if (hit0) key = 0;
+        else open = s.max_rings > 1;
+    }
+}
+
 template <bool BLOCKS, bool COMPACT>
 __global__ void __launch_bounds__(256, STEPTH_NEAR_MINB) search_near_kernel(HierArgs a) {
+    constexpr int KP = COMPACT ? STEPTH_NEAR_KP : 1;
     __shared__ unsigned long long s_le[DIAG_N], s_ge[DIAG_N];
     __shared__ WarpScratch s_ws[8];
-    __shared__ uint4 s_open[COMPACT ? 256 : 1];  // queries that survive ring 0: {qi, ox, oy, colour}
-    __shared__ uint32_t s_cnt[8];
-    load_diag_tables(s_le, s_ge);
+    __shared__ uint4 s_open[COMPACT ? KP * 256 : 1];  // queries that survive ring 0: {qi, ox, oy, colour}
+    __shared__ uint32_t s_n;
+    if (threadIdx.x == 0) s_n = 0;
+    load_diag_tables(s_le, s_ge);  // ends with __syncthreads()
     const SearchArgs &s = a.s;
     const uint32_t pair = BLOCKS ? 0u : blockIdx.z;
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (COMPACT) {
+        // Ring 0 settles about half of the queries of a natural pair.  The CTA runs ring 0 for KP patches, queues the
+        // survivors in shared memory and then walks them 256 at a time: full warps, and every warp of the CTA stays busy.
+#pragma unroll 1
+        for (int k = 0; k < KP; ++k) {
+            bool valid;
+            uint32_t qi, X = 0, Y = 0;
+            if (BLOCKS) {
+                qi = (blockIdx.x * KP + k) * 256u + tid;
+                valid = qi < s.n_queries;
+            } else {
+                X = (blockIdx.x * KP + k) * 32u + (warp & 3) * 8u + (lane & 7);
+                Y = blockIdx.y * 8u + (warp >> 2) * 4u + (lane >> 3);
+                valid = X < s.w && Y < s.h;
+                qi = Y * s.w + X;
+            }
+            uint32_t key = KEY_NONE, col = 0;
+            bool open = false;
+            int ox = 0, oyl = 0;
+            if (valid) ring0_of<BLOCKS>(s, pair, qi, X, Y, ox, oyl, col, key, open);
+            // settled at ring 0: a hit has distance 0 and `None` maps to 0 too (depth_image.rs:120), neither moves the maximum
+            if (valid && !open) s.d8[(size_t)pair * s.n_queries + qi] = 0;
+            const uint32_t bal = __ballot_sync(0xffffffffu, open);
+            if (bal) {
+                uint32_t base = 0;
+                if (lane == __ffs(bal) - 1) base = atomicAdd(&s_n, (uint32_t)__popc(bal));
+                base = __shfl_sync(0xffffffffu, base, __ffs(bal) - 1);
+                if (open) s_open[base + __popc(bal & ((1u << lane) - 1u))] = make_uint4(qi, (uint32_t)ox, (uint32_t)oyl, col);
+            }
+        }
+        __syncthreads();
+        const uint32_t n_open = s_n;
+#pragma unroll 1
+        for (uint32_t i0 = (uint32_t)warp * 32u; i0 < n_open; i0 += 256u) {  // warp-uniform
+            const bool has = i0 + lane < n_open;
+            const uint4 e = has ? s_open[i0 + lane] : make_uint4(0, 0, 0, 0);
+            const HierQuery q = make_query((int)e.y, (int)e.z, e.w);
+            uint32_t key = KEY_NONE;
+            const bool still = !hier_rings_warp(has, a.planes, a.g, pair, q, (int)s.max_rings, 0, a.S1, s_le, s_ge, key, &s_ws[warp]);
+            export_open(a, has && still, pair, e.x, key);
+            publish_result<true>(s, pair, e.x, key, has && !still);
+        }
+        return;
+    }
     bool valid;
     uint32_t qi = 0, X = 0, Y = 0;
     if (BLOCKS) {
         qi = blockIdx.x * 256u + tid;
         valid = qi < s.n_queries;
     } else {
-        const int lane = tid & 31, warp = tid >> 5;
         X = blockIdx.x * 32u + (warp & 3) * 8u + (lane & 7);
         Y = blockIdx.y * 8u + (warp >> 2) * 4u + (lane >> 3);
         valid = X < s.w && Y < s.h;
         qi = Y * s.w + X;
     }
-    uint32_t key = KEY_NONE;
+    uint32_t key = KEY_NONE, col = 0;
     bool open = false;
     int ox = 0, oyl = 0;
-    uint32_t col = 0;
-    if (valid) {
-        int oyg;
-        if (BLOCKS) {
-            query_of<true>(s, pair, qi, ox, oyg, col);
-        } else {  // query_of<false> without the division: X, Y are at hand
-            ox = (int)((X + 1) >> 1);
-            oyg = (int)((Y + s.y0 + 1) >> 1);
-            col = reinterpret_cast<const uint32_t *>(s.main_rgba)[(size_t)pair * s.n_queries + qi] & 0xffffffu;
-        }
-        const int src_wa = (int)s.wa, src_ha = (int)s.ha;
-        // ring 0 out of bounds => `still_in_bounds` stays false => break => None   (helpers.rs:49-51)
-        if (ox < src_wa && oyg < (int)s.add_img_h) {
-            oyl = oyg - (int)s.add_y0;  // origin row inside the sub-image held on this device
-            bool hit0 = false;
-            if (oyl >= 0 && oyl < src_ha) {
-                const uint8_t *px = s.add_rgb + (size_t)pair * src_ha * src_wa * 3 + ((size_t)oyl * src_wa + ox) * 3;
-                hit0 = pixel_in_box(px[0], px[1], px[2], col, s.pr, s.pg, s.pb, s.sat != 0);
-            }
-            if (hit0) key = 0;
-            else open = s.max_rings > 1;
-        }
-    }
-    if (COMPACT) {
-        // Ring 0 settles about half of the queries of a natural pair; the rest are packed into the first warps of the CTA
-        // so that the walk runs with full warps (and the other warps retire).
-        // settled at ring 0: a hit has distance 0 and `None` maps to 0 too (depth_image.rs:120), neither moves the maximum
-        if (valid && !open) s.d8[(size_t)pair * s.n_queries + qi] = 0;
-        const int lane = tid & 31, warp = tid >> 5;
-        const uint32_t bal = __ballot_sync(0xffffffffu, open);
-        if (lane == 0) s_cnt[warp] = __popc(bal);
-        __syncthreads();
-        uint32_t pre = 0, n_open = 0;
-#pragma unroll
-        for (int w = 0; w < 8; ++w) {
-            const uint32_t c = s_cnt[w];
-            if (w < warp) pre += c;
-            n_open += c;
-        }
-        if (open) s_open[pre + __popc(bal & ((1u << lane) - 1u))] = make_uint4(qi, (uint32_t)ox, (uint32_t)oyl, col);
-        __syncthreads();
-        if ((uint32_t)(warp * 32) >= n_open) return;  // warp-uniform
-        const bool has = (uint32_t)tid < n_open;
-        const uint4 e = has ? s_open[tid] : make_uint4(0, 0, 0, 0);
-        const HierQuery q = make_query((int)e.y, (int)e.z, e.w);
-        key = KEY_NONE;
-        const bool still = !hier_rings_warp(has, a.planes, a.g, pair, q, (int)s.max_rings, 0, a.S1, s_le, s_ge, key, &s_ws[warp]);
-        export_open(a, has && still, pair, e.x, key);
-        publish_result<true>(s, pair, e.x, key, has && !still);
-        return;
-    }
+    if (valid) ring0_of<BLOCKS>(s, pair, qi, X, Y, ox, oyl, col, key, open);
     if (__any_sync(0xffffffffu, open)) {
         const HierQuery q = make_query(ox, oyl, col);
-        open = !hier_rings_warp(open, a.planes, a.g, pair, q, (int)s.max_rings, 0, a.S1, s_le, s_ge, key, &s_ws[tid >> 5]);
+        open = !hier_rings_warp(open, a.planes, a.g, pair, q, (int)s.max_rings, 0, a.S1, s_le, s_ge, key, &s_ws[warp]);
     }
     export_open(a, open, pair, qi, key);
     publish_result<true>(s, pair, qi, key, valid && !open);
@@ -675,12 +700,12 @@ inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const Search
     h.wl_out = (uint2 *)(wl0 + 64);
     h.wl_out_count = (uint32_t *)wl0;
     if (a.blocks) {
-        if (ctx->near_compact) search_near_kernel<true, true><<<dim3((a.n_queries + 255) / 256, 1, 1), 256, 0, st>>>(h);
+        if (ctx->near_compact) search_near_kernel<true, true><<<dim3((a.n_queries + 256 * STEPTH_NEAR_KP - 1) / (256 * STEPTH_NEAR_KP), 1, 1), 256, 0, st>>>(h);
         else search_near_kernel<true, false><<<dim3((a.n_queries + 255) / 256, 1, 1), 256, 0, st>>>(h);
     } else {
         const uint32_t gy = (a.h + 7) / 8;
         if (gy > 65535u) return set_err(ctx, STEPTH_ERR_INVALID_ARG, "band taller than 524280 rows");
-        if (ctx->near_compact) search_near_kernel<false, true><<<dim3((a.w + 31) / 32, gy, n_pairs), 256, 0, st>>>(h);
+        if (ctx->near_compact) search_near_kernel<false, true><<<dim3((a.w + 32 * STEPTH_NEAR_KP - 1) / (32 * STEPTH_NEAR_KP), gy, n_pairs), 256, 0, st>>>(h);
         else search_near_kernel<false, false><<<dim3((a.w + 31) / 32, gy, n_pairs), 256, 0, st>>>(h);
     }
     ctx->launches++;
