@@ -115,8 +115,14 @@ struct TileBuildArgs {
 
 // 32x32 bit-matrix transpose across the lanes of a warp: in: lane i holds row i; out: lane i holds column i
 __device__ __forceinline__ uint32_t warp_bit_transpose(uint32_t x, int lane) {
+    {   // the 16- and 8-bit steps move whole bytes: one byte permute each
+        uint32_t y = __shfl_xor_sync(0xffffffffu, x, 16);
+        x = __byte_perm(x, y, (lane & 16) ? 0x3276u : 0x5410u);   // hi: {y.b2, y.b3 | x.b2, x.b3}   lo: {x.b0, x.b1 | y.b0, y.b1}
+        y = __shfl_xor_sync(0xffffffffu, x, 8);
+        x = __byte_perm(x, y, (lane & 8) ? 0x3715u : 0x6240u);    // hi: bytes {y1, x1, y3, x3}      lo: bytes {x0, y0, x2, y2}
+    }
 #pragma unroll
-    for (int s = 0; s < 5; ++s) {
+    for (int s = 2; s < 5; ++s) {
         const int d = 16 >> s;
         const uint32_t m = d == 16 ? 0x0000ffffu : d == 8 ? 0x00ff00ffu : d == 4 ? 0x0f0f0f0fu : d == 2 ? 0x33333333u : 0x55555555u;
         const uint32_t y = __shfl_xor_sync(0xffffffffu, x, d);
@@ -127,6 +133,11 @@ __device__ __forceinline__ uint32_t warp_bit_transpose(uint32_t x, int lane) {
 
 // ---- 512-bit shifts spread over the 16 lanes of a half warp (lane16 = word index, word 0 = bits 0..31) ------------------
 __device__ __forceinline__ uint32_t shl512(uint32_t x, int lane16, int nbits) {  // nbits warp-uniform, 0 <= nbits < 512
+    if (nbits < 32) {  // the doubling steps of a dilation by a typical precision: the neighbour word is all that moves
+        uint32_t lo = __shfl_up_sync(0xffffffffu, x, 1, 16);
+        if (lane16 == 0) lo = 0;
+        return __funnelshift_l(lo, x, nbits);
+    }
     const int wsh = nbits >> 5, bsh = nbits & 31;
     uint32_t hi = __shfl_up_sync(0xffffffffu, x, wsh, 16);
     uint32_t lo = __shfl_up_sync(0xffffffffu, x, (wsh + 1) & 15, 16);
@@ -164,26 +175,49 @@ __device__ __forceinline__ uint32_t dilate_values(uint32_t x, int lane16, int R,
 // (warp OR-reductions) is dilated into E, 256 bits per (tile, channel); the CTA transposes the 32 tiles x 256 values of
 // a channel into 256 words of 32 tile bits and stores the cell with coalesced lines.
 __global__ void __launch_bounds__(256) tile_planes_kernel(TileBuildArgs a) {
-    __shared__ uint8_t s_px[3][8][256 + 4];
+    __shared__ uint32_t s_raw[8][192];    // [row][interleaved RGB of 256 pixels]
+    __shared__ uint2 s_tab[3][256];       // plane membership (plane_bits) of every value of a channel
     __shared__ uint32_t s_E[3][8][32];  // [channel][value word g][tile]: bit b <-> q = 32 g + b
     const uint32_t pair = blockIdx.z, xw = blockIdx.x, TY = blockIdx.y;
     const uint32_t wa = a.g.wa, ha = a.g.ha;
     const uint8_t *add = a.add_rgb + (size_t)pair * a.src_pair_bytes;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, lane16 = lane & 15;
     const uint32_t x_base = xw * 256u, y_base = TY * 8u;
-    for (int i = tid; i < 8 * 768; i += 256) {
-        const int r = i / 768, k = i - r * 768;
-        const uint32_t x = x_base + k / 3, y = y_base + r;
-        uint8_t v = 0;
-        if (x < wa && y < ha) v = add[((size_t)y * a.g.src_wa + x_base) * 3 + k];
-        s_px[k % 3][r][k / 3] = v;
+    // the strip as it lies in memory (interleaved RGB, 768 bytes per row); rows start on a word when the pitch allows it
+    const size_t pitch = (size_t)a.g.src_wa * 3;
+    if ((pitch & 3) == 0 && (reinterpret_cast<uintptr_t>(add) & 3) == 0) {
+        const uint32_t row_words = (uint32_t)(pitch >> 2);            // words of one image row
+        for (int i = tid; i < 8 * 192; i += 256) {
+            const int r = i / 192, k = i - r * 192;
+            const uint32_t y = y_base + r, wi = xw * 192u + k;         // word inside the row
+            uint32_t v = 0;
+            if (y < ha && wi < row_words) v = reinterpret_cast<const uint32_t *>(add + (size_t)y * pitch)[wi];
+            s_raw[r][k] = v;
+        }
+    } else {
+        uint8_t *raw = reinterpret_cast<uint8_t *>(&s_raw[0][0]);
+        for (int i = tid; i < 8 * 768; i += 256) {
+            const int r = i / 768, k = i - r * 768;
+            const uint32_t x = x_base + k / 3, y = y_base + r;
+            uint8_t v = 0;
+            if (x < a.g.src_wa && y < ha) v = add[(size_t)y * pitch + (size_t)x_base * 3 + k];
+            raw[r * 768 + k] = v;
+        }
     }
     for (int i = tid; i < 3 * 8 * 32; i += 256) (&s_E[0][0][0])[i] = 0;
+    const int prec[3] = {(int)a.pr, (int)a.pg, (int)a.pb};
+    const bool sat = a.sat != 0;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        uint32_t lo, hi;
+        plane_bits(tid, prec[c], sat, true, lo, hi);
+        s_tab[c][tid] = make_uint2(lo, hi);
+    }
     __syncthreads();
     uint8_t *pair_base = a.planes + (size_t)pair * a.g.pair_bytes;
     unsigned long long *fine = reinterpret_cast<unsigned long long *>(pair_base);
-    const int prec[3] = {(int)a.pr, (int)a.pg, (int)a.pb};
-    const bool sat = a.sat != 0;
+    const uint8_t *raw = reinterpret_cast<const uint8_t *>(&s_raw[0][0]);
+    const bool same_prec = prec[0] == prec[1] && prec[1] == prec[2];
 #pragma unroll 1
     for (int t = 0; t < 4; ++t) {
         const int tl = warp * 4 + t;                 // tile inside the cell
@@ -194,10 +228,9 @@ __global__ void __launch_bounds__(256) tile_planes_kernel(TileBuildArgs a) {
         uint32_t pw01 = 0, pw2 = 0;  // value-presence words: lanes 0-15 channel 0 | lanes 16-31 channel 1;  channel 2
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-            const int v0 = s_px[c][ly][tl * 8 + lx], v1 = s_px[c][ly + 4][tl * 8 + lx];
-            uint32_t lo0, hi0, lo1, hi1;
-            plane_bits(v0, prec[c], sat, ok0, lo0, hi0);
-            plane_bits(v1, prec[c], sat, ok1, lo1, hi1);
+            const int v0 = raw[ly * 768 + (tl * 8 + lx) * 3 + c], v1 = raw[(ly + 4) * 768 + (tl * 8 + lx) * 3 + c];
+            const uint2 t0 = s_tab[c][v0], t1 = s_tab[c][v1];
+            uint32_t lo0 = ok0 ? t0.x : 0u, hi0 = ok0 ? t0.y : 0u, lo1 = ok1 ? t1.x : 0u, hi1 = ok1 ? t1.y : 0u;
             lo0 = warp_bit_transpose(lo0, lane);
             lo1 = warp_bit_transpose(lo1, lane);
             hi0 = warp_bit_transpose(hi0, lane);
@@ -205,8 +238,13 @@ __global__ void __launch_bounds__(256) tile_planes_kernel(TileBuildArgs a) {
             unsigned long long *rec = fine + (((size_t)TY * a.g.ntx + TX) * 3 + c) * T_SLOTS;
             rec[lane] = (unsigned long long)lo0 | ((unsigned long long)lo1 << 32);
             if (lane < W_USED - 32) rec[32 + lane] = (unsigned long long)hi0 | ((unsigned long long)hi1 << 32);
-#pragma unroll
-            for (int g = 0; g < 8; ++g) {
+            // the set of values present in the tile, one 32-value word at a time: only the words some pixel falls into
+            // are visited (a natural tile spans one to three of the eight)
+            uint32_t need = (ok0 ? 1u << (v0 >> 5) : 0u) | (ok1 ? 1u << (v1 >> 5) : 0u);
+            need = __reduce_or_sync(0xffffffffu, need);
+            while (need) {
+                const int g = __ffs((int)need) - 1;
+                need &= need - 1;
                 uint32_t contrib = 0;
                 if (ok0 && (v0 >> 5) == g) contrib |= 1u << (v0 & 31);
                 if (ok1 && (v1 >> 5) == g) contrib |= 1u << (v1 & 31);
@@ -220,7 +258,7 @@ __global__ void __launch_bounds__(256) tile_planes_kernel(TileBuildArgs a) {
         }
         // the precision differs per channel, so the three dilations are separate calls (warp-uniform shift counts)
         const uint32_t e0 = dilate_values(pw01, lane16, prec[0] - 1, sat);   // lanes 0-15 carry channel 0
-        const uint32_t e1 = dilate_values(pw01, lane16, prec[1] - 1, sat);   // lanes 16-31 carry channel 1
+        const uint32_t e1 = same_prec ? e0 : dilate_values(pw01, lane16, prec[1] - 1, sat);   // lanes 16-31 carry channel 1
         const uint32_t e2 = dilate_values(pw2, lane16, prec[2] - 1, sat);    // both halves carry channel 2
         if (lane16 < 8) {
             if (lane < 16) { s_E[0][lane16][tl] = e0; s_E[2][lane16][tl] = e2; }
