@@ -290,24 +290,38 @@ __global__ void __launch_bounds__(256) coarse_transpose_kernel(TileBuildArgs a) 
     const uint32_t *crp = reinterpret_cast<const uint32_t *>(pair_base + a.g.off_crp);
     uint32_t *ccp = reinterpret_cast<uint32_t *>(pair_base + a.g.off_ccp);
     constexpr int PER_WARP = C_CELL / CT_PARTS / 8;  // 12 planes per warp, four loads in flight at a time
-    const uint32_t TY = by * 32u + lane, TX = bx * 32u + lane;
+    const uint32_t TY = by * 32u + lane;
     const uint32_t *src = crp + ((size_t)TY * a.g.nxw + bx) * C_CELL * 2;
-    uint32_t *dst = ccp + ((size_t)TX * a.g.nyw + by) * C_CELL * 2;
     const int cj0 = (int)part * (C_CELL / CT_PARTS) + warp * PER_WARP;
-#pragma unroll 1
-    for (int i = 0; i < PER_WARP; i += 4) {
-        uint32_t x[4];
+    // all twelve low halves are requested before any is used (the kernel is latency bound): six 16-byte loads per lane, each
+    // bringing two (low, high) window words of which the low ones belong to this 32x32 block
+    static_assert(PER_WARP % 2 == 0, "two planes per 16-byte load");
+    uint32_t x[PER_WARP];
+    const uint4 *src4 = reinterpret_cast<const uint4 *>(src + (size_t)cj0 * 2);  // cj0 is a multiple of 12: 32-byte aligned
 #pragma unroll
-        for (int u = 0; u < 4; ++u) x[u] = TY < a.g.nty ? src[(cj0 + i + u) * 2] : 0u;
+    for (int i = 0; i < PER_WARP / 2; ++i) {
+        const uint4 t = TY < a.g.nty ? __ldg(src4 + i) : make_uint4(0, 0, 0, 0);
+        x[2 * i] = t.x;
+        x[2 * i + 1] = t.z;
+    }
+    // transposed words go through shared memory so that a warp stores one tile column at a time: the 96 planes of this part
+    // are 96 consecutive (low, high) words of the column's cell -> runs of 8-byte-strided words instead of 32 scattered ones
+    constexpr int PART = C_CELL / CT_PARTS;            // 96 planes
+    __shared__ uint32_t s_t[32][PART + 1];             // [tile column][plane]
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const uint32_t t = warp_bit_transpose(x[u], lane);
-            if (TX < a.g.ntx) {
-                uint32_t *d = dst + (cj0 + i + u) * 2;
-                d[0] = t;
-                if (by > 0) d[1 - C_CELL * 2] = t;
-                if (by + 1 == a.g.nyw) d[1] = 0u;
-            }
+    for (int i = 0; i < PER_WARP; ++i) s_t[lane][warp * PER_WARP + i] = warp_bit_transpose(x[i], lane);
+    __syncthreads();
+    const int p0 = (int)part * PART;
+    for (int k = warp; k < 32; k += 8) {               // tile column 32 bx + k
+        const uint32_t TXk = bx * 32u + k;
+        if (TXk >= a.g.ntx) break;                     // warp-uniform; later columns of this warp are beyond the grid too
+        uint32_t *d = ccp + ((size_t)TXk * a.g.nyw + by) * C_CELL * 2 + p0 * 2;
+#pragma unroll
+        for (int j = lane; j < PART; j += 32) {
+            const uint32_t t = s_t[k][j];
+            d[j * 2] = t;
+            if (by > 0) d[j * 2 + 1 - C_CELL * 2] = t;
+            if (by + 1 == a.g.nyw) d[j * 2 + 1] = 0u;
         }
     }
 }
