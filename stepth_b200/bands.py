@@ -217,7 +217,13 @@ class BandRunner:
         if self.world == 1:
             return band
         n, _, w = band.shape
-        max_rows = max(p.y1 - p.y0 for p in self.plan)
+        rows = [p.y1 - p.y0 for p in self.plan]
+        if n == 1 and len(set(rows)) == 1:
+            # equal bands of one pair are consecutive slabs of the assembled map: gather straight into it
+            out = torch.empty((1, self.h, w), dtype=band.dtype, device=band.device)
+            dist.all_gather_into_tensor(out.view(-1), band.contiguous().view(-1), group=self.group)
+            return out
+        max_rows = max(rows)
         padded = torch.zeros((n, max_rows, w), dtype=band.dtype, device=band.device)
         padded[:, : band.shape[1]] = band
         parts = [torch.empty_like(padded) for _ in range(self.world)]

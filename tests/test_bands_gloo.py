@@ -100,7 +100,7 @@ def _worker(rank, world, port, w, h, rings, seed, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,w,h,rings", [(2, 64, 46, 12), (3, 40, 10, 6)])
+@pytest.mark.parametrize("world,w,h,rings", [(2, 64, 46, 12), (3, 40, 10, 6), (2, 64, 48, 12)])  # the last: equal bands (direct gather)
 def test_row_bands_over_gloo_equal_the_whole_image(orc, world, w, h, rings):
     import stepth_b200 as sb  # noqa: F401
     from stepth_b200 import synth
