@@ -27,97 +27,113 @@ struct SplitArgs {
     uint32_t max_iters;
 };
 
+// With the centre list ascending (it is built so, :214-216, and sorted after every iteration, :189) "nearest centre, the
+// first one on ties" (:171-179) cuts the value axis into consecutive intervals: centre c_k owns (mid(c_k-1, c_k), mid(c_k, c_k+1)]
+// with mid = floor((a + b) / 2).  Sums, counts, minima and maxima of an interval come from prefix tables of the histogram,
+// so one Lloyd iteration is O(centres) for a single thread and needs no barrier at all.
 __global__ void __launch_bounds__(256) depth_split_kernel(SplitArgs a) {
-    __shared__ unsigned long long s_sum[256];
-    __shared__ unsigned long long s_cnt[256];
-    __shared__ uint32_t s_min[256], s_max[256];
-    __shared__ uint8_t s_prev[256], s_new[256], s_is_key[256];
-    __shared__ uint32_t s_nprev, s_nnew;
-    __shared__ int s_state;  // 0 = iterate, 1 = converged, >1 = error code + 1
-    __shared__ uint32_t s_gmin, s_gmax;
+    __shared__ unsigned long long s_S[257];   // s_S[v + 1] = sum_{u <= v} u * h[u]
+    __shared__ uint32_t s_C[257];             // s_C[v + 1] = sum_{u <= v} h[u]
+    __shared__ uint32_t s_h[256];
+    __shared__ uint16_t s_ge[257], s_le[256]; // next / previous non-empty bin (256 / 0xffff = none)
+    __shared__ uint8_t s_prev[256], s_new[256];
 
     const uint32_t pair = blockIdx.x;
     const int v = threadIdx.x;
     if (a.status[pair] != STEPTH_OK) return;  // e.g. max == 0: the reference panicked before reaching here
-    const uint32_t hv = a.hist[(size_t)pair * 256 + v];
-    if (v == 0) { s_gmin = 255; s_gmax = 0; s_state = 0; }
+    s_h[v] = a.hist[(size_t)pair * 256 + v];
     __syncthreads();
-    if (hv) { atomicMin(&s_gmin, (uint32_t)v); atomicMax(&s_gmax, (uint32_t)v); }
-    __syncthreads();
-    if (v == 0) {
-        // :212-216  (img_min..img_max).step_by(((img_max - img_min) / (zones - 1)) as usize - 1)
-        if (s_gmax < s_gmin) {
-            s_state = STEPTH_ERR_DEGENERATE_DEPTH + 1;  // empty image: min().unwrap() on None
-        } else {
-            uint32_t q = (s_gmax - s_gmin) / (a.zones - 1);
-            if (q <= 1) {
-                s_state = STEPTH_ERR_DEGENERATE_DEPTH + 1;  // usize underflow / step_by(0)
-            } else {
-                uint32_t step = q - 1, n = 0;
-                for (uint32_t c = s_gmin; c < s_gmax; c += step) s_prev[n++] = (uint8_t)c;
-                s_nprev = n;
-            }
-        }
-    }
-    __syncthreads();
+    if (v != 0) return;
 
-    for (uint32_t iter = 1; s_state == 0; ++iter) {
-        s_sum[v] = 0; s_cnt[v] = 0; s_min[v] = 255; s_max[v] = 0; s_is_key[v] = 0;
-        __syncthreads();
-        const uint32_t np = s_nprev;
-        if ((uint32_t)v < np) s_is_key[s_prev[v]] = 1;
-        if (hv) {
-            int best = 0, best_d = abs((int)s_prev[0] - v);
-            for (uint32_t k = 1; k < np; ++k) {
-                int d = abs((int)s_prev[k] - v);
-                if (d < best_d) { best_d = d; best = (int)k; }  // strict: the first minimum wins (min_by)
-            }
-            const int key = s_prev[best];
-            atomicAdd(&s_sum[key], (unsigned long long)hv * (unsigned long long)v);
-            atomicAdd(&s_cnt[key], (unsigned long long)hv);
-            atomicMin(&s_min[key], (uint32_t)v);
-            atomicMax(&s_max[key], (uint32_t)v);
-        }
-        __syncthreads();
-        if (v == 0) {
-            uint32_t nn = 0;
-            for (int key = 0; key < 256; ++key)  // ascending keys; the list is sorted below anyway
-                if (s_is_key[key]) {
-                    unsigned long long c = s_cnt[key];
-                    s_new[nn++] = (uint8_t)(s_sum[key] / (c ? c : 1ull));
-                }
-            for (uint32_t i = 1; i < nn; ++i) {  // new_centroids.sort()
-                uint8_t x = s_new[i];
-                int j = (int)i - 1;
-                while (j >= 0 && s_new[j] > x) { s_new[j + 1] = s_new[j]; --j; }
-                s_new[j + 1] = x;
-            }
-            bool same = true;
-            uint32_t m = np < nn ? np : nn;
-            for (uint32_t k = 0; k < m; ++k)
-                if (s_prev[k] != s_new[k]) { same = false; break; }
-            s_nnew = nn;
-            if (same) {
-                int st = 1;
-                for (uint32_t k = 0; k < nn; ++k) {
-                    uint8_t c = s_new[k];
-                    if (!s_is_key[c] || s_cnt[c] == 0) { st = STEPTH_ERR_DEGENERATE_DEPTH + 1; break; }
-                    a.ranges[(size_t)pair * 512 + 2 * k] = (uint8_t)s_min[c];
-                    a.ranges[(size_t)pair * 512 + 2 * k + 1] = (uint8_t)s_max[c];
-                }
-                if (st == 1 && nn == 0) st = STEPTH_ERR_DEGENERATE_DEPTH + 1;
-                a.n_out[pair] = nn;
-                s_state = st;
-            } else if (iter >= a.max_iters) {
-                s_state = STEPTH_ERR_NO_CONVERGENCE + 1;
-            } else {
-                for (uint32_t k = 0; k < nn; ++k) s_prev[k] = s_new[k];
-                s_nprev = nn;
-            }
-        }
-        __syncthreads();
+    unsigned long long S = 0;
+    uint32_t C = 0;
+    s_S[0] = 0; s_C[0] = 0;
+    int last = 0xffff, gmin = -1, gmax = -1;
+    for (int u = 0; u < 256; ++u) {
+        const uint32_t h = s_h[u];
+        S += (unsigned long long)h * (unsigned long long)u;
+        C += h;
+        s_S[u + 1] = S; s_C[u + 1] = C;
+        if (h) { last = u; if (gmin < 0) gmin = u; gmax = u; }
+        s_le[u] = (uint16_t)last;
     }
-    if (v == 0 && s_state > 1) a.status[pair] = s_state - 1;
+    int next = 256;
+    s_ge[256] = 256;
+    for (int u = 255; u >= 0; --u) {
+        if (s_h[u]) next = u;
+        s_ge[u] = (uint16_t)next;
+    }
+    int state = 0;  // 0 = iterate, 1 = converged, > 1 = error code + 1
+    uint32_t np = 0;
+    // :212-216  (img_min..img_max).step_by(((img_max - img_min) / (zones - 1)) as usize - 1)
+    if (gmin < 0) {
+        state = STEPTH_ERR_DEGENERATE_DEPTH + 1;  // empty image: min().unwrap() on None
+    } else {
+        const uint32_t q = (uint32_t)(gmax - gmin) / (a.zones - 1);
+        if (q <= 1) {
+            state = STEPTH_ERR_DEGENERATE_DEPTH + 1;  // usize underflow / step_by(0)
+        } else {
+            const uint32_t step = q - 1;
+            for (uint32_t c = (uint32_t)gmin; c < (uint32_t)gmax; c += step) s_prev[np++] = (uint8_t)c;
+        }
+    }
+    for (uint32_t iter = 1; state == 0; ++iter) {
+        // one new centroid per DISTINCT centre value (the HashMap keys, :166-170); equal centres are neighbours
+        uint32_t nn = 0;
+        int lo = 0;  // first value of the current centre's interval
+        for (uint32_t k = 0; k < np; ++k) {
+            const int key = s_prev[k];
+            if (k > 0 && key == (int)s_prev[k - 1]) continue;
+            uint32_t kn = k + 1;
+            while (kn < np && (int)s_prev[kn] == key) ++kn;
+            const int hi = kn < np ? (key + (int)s_prev[kn]) >> 1 : 255;  // ties go to the earlier (smaller) centre
+            const unsigned long long sum = s_S[hi + 1] - s_S[lo];
+            const uint32_t cnt = s_C[hi + 1] - s_C[lo];
+            s_new[nn++] = (uint8_t)(sum / (cnt ? cnt : 1u));            // :185-188  sum / len.max(1)
+            lo = hi + 1;
+        }
+        for (uint32_t i = 1; i < nn; ++i) {  // new_centroids.sort()   :189
+            const uint8_t x = s_new[i];
+            int j = (int)i - 1;
+            while (j >= 0 && s_new[j] > x) { s_new[j + 1] = s_new[j]; --j; }
+            s_new[j + 1] = x;
+        }
+        bool same = true;   // :190-196  zip truncates to the shorter list
+        const uint32_t m = np < nn ? np : nn;
+        for (uint32_t k = 0; k < m; ++k)
+            if (s_prev[k] != s_new[k]) { same = false; break; }
+        if (same) {
+            // :197-207  clusters.get(c).unwrap(), then min / max of the cluster: both unwraps can panic
+            int st = 1;
+            for (uint32_t k = 0; k < nn && st == 1; ++k) {
+                const int c = s_new[k];
+                // the interval of centre value c among the previous centres (c must be one of them)
+                int lo2 = 0, hi2 = -1;
+                bool found = false;
+                for (uint32_t j = 0; j < np; ++j) {
+                    const int key = s_prev[j];
+                    if (j > 0 && key == (int)s_prev[j - 1]) continue;
+                    uint32_t jn = j + 1;
+                    while (jn < np && (int)s_prev[jn] == key) ++jn;
+                    hi2 = jn < np ? (key + (int)s_prev[jn]) >> 1 : 255;
+                    if (key == c) { found = true; break; }
+                    lo2 = hi2 + 1;
+                }
+                if (!found || s_C[hi2 + 1] == s_C[lo2]) { st = STEPTH_ERR_DEGENERATE_DEPTH + 1; break; }
+                a.ranges[(size_t)pair * 512 + 2 * k] = (uint8_t)s_ge[lo2];
+                a.ranges[(size_t)pair * 512 + 2 * k + 1] = (uint8_t)s_le[hi2];
+            }
+            if (st == 1 && nn == 0) st = STEPTH_ERR_DEGENERATE_DEPTH + 1;
+            a.n_out[pair] = nn;
+            state = st;
+        } else if (iter >= a.max_iters) {
+            state = STEPTH_ERR_NO_CONVERGENCE + 1;
+        } else {
+            for (uint32_t k = 0; k < nn; ++k) s_prev[k] = s_new[k];
+            np = nn;
+        }
+    }
+    if (state > 1) a.status[pair] = state - 1;
 }
 
 // ------------------------------------------------------------------------------------------------------------

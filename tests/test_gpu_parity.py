@@ -236,7 +236,12 @@ def test_depth_split_vs_oracle(ctx, orc, zones, assets):
     planes = [assets["depth"], orc.invert_depth(assets["depth"]),
               rng.integers(0, 256, 5000, dtype=np.uint8),
               np.clip(rng.normal(120, 30, 20000), 0, 255).astype(np.uint8),
-              np.array([0] * 50 + [255] * 3 + [100] * 20, np.uint8)]
+              np.array([0] * 50 + [255] * 3 + [100] * 20, np.uint8),
+              # sparse value sets: empty clusters, centres that collapse, neighbours one apart
+              np.array([3] * 7 + [4] * 9 + [250] * 2, np.uint8),
+              np.array([10, 12, 14, 200, 202, 255] * 5, np.uint8),
+              rng.choice(np.array([0, 1, 2, 128, 254, 255], np.uint8), 3000),
+              np.repeat(np.arange(0, 256, 17, dtype=np.uint8), 11)]
     import stepth_b200 as sb
 
     for d in planes:
