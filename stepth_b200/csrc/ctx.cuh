@@ -17,6 +17,9 @@ struct stepth_ctx {
     cudaStream_t stream = nullptr;    // compute (and the single-pair copies)
     cudaStream_t copy_in = nullptr;   // batch entry point: host->device copies of the next chunk of pairs
     cudaStream_t copy_out = nullptr;  // batch entry point: device->host copies of the previous chunk
+    cudaStream_t stream2 = nullptr;   // batch entry point: second compute stream (chunks alternate, so one chunk's first
+                                      // kernels fill the SMs while the previous chunk's last, poorly filled ones drain)
+    int slot = 0;                     // which scratch set (planes / worklist) the next search launch uses
     std::vector<cudaEvent_t> events;  // pool for the chunk hand-offs between the three streams
     std::string err;
     uint64_t launches = 0;
@@ -30,10 +33,12 @@ struct stepth_ctx {
     Buf main_rgba, add_rgb, d8, depth, mask, rgba_out, blocks, plane, small, u16a, u16b, u16o, work;
     Buf worklist;  // two [count, cursor, pad..][uint2 entries] lists: queries handed from the near to the far kernel(s)
     int near_rings = 6;  // coarse rings the near kernel walks (STEPTH_NEAR_RINGS)
-    int batch_chunks = 4;  // the batch entry point pipelines this many chunks of pairs over its three streams (STEPTH_BATCH_CHUNKS)
+    int batch_chunks = 8;  // the batch entry point pipelines this many chunks of pairs over its three streams (STEPTH_BATCH_CHUNKS)
     int upload_full_rows = 0;  // host-buffer entry points upload whole rows of the additional image (STEPTH_UPLOAD_FULL_ROWS)
     int near_compact = 1;  // the near kernel packs the queries that survive ring 0 into full warps (STEPTH_NEAR_COMPACT)
     int mid_rings = 10;  // first far kernel walks coarse rings [near_rings, mid_rings); 0 = one far kernel (STEPTH_MID_RINGS)
+    Buf planes2, worklist2;  // scratch set of slot 1
+    int two_streams = 1;     // STEPTH_TWO_STREAMS
     Buf planes;  // two-level match bit-planes of the additional image(s) (tiles.cuh), rebuilt by every search
     // small per-pair state: [max u32][hist 256 u32][status i32][n_out u32][ranges 512 B] per pair
     void *h_small = nullptr;  // pinned mirror

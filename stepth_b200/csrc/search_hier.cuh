@@ -671,11 +671,12 @@ inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const Search
         cover_h = (uint32_t)std::max<int64_t>(1, std::min<int64_t>(a.ha, last_row + 1));
     }
     h.g = make_tile_geom(cover_w, cover_h, a.wa);
-    int32_t rc = ensure(ctx, ctx->planes, h.g.pair_bytes * n_pairs);
+    stepth_ctx::Buf &planes = ctx->slot ? ctx->planes2 : ctx->planes, &worklist = ctx->slot ? ctx->worklist2 : ctx->worklist;
+    int32_t rc = ensure(ctx, planes, h.g.pair_bytes * n_pairs);
     if (rc != STEPTH_OK) return rc;
-    h.planes = (const uint8_t *)ctx->planes.p;
+    h.planes = (const uint8_t *)planes.p;
     if (h.g.nty > 65535u) return set_err(ctx, STEPTH_ERR_INVALID_ARG, "too many tile rows for one launch");
-    TileBuildArgs p{a.add_rgb, (size_t)a.ha * a.wa * 3, (uint8_t *)ctx->planes.p, h.g, a.pr, a.pg, a.pb, a.sat};
+    TileBuildArgs p{a.add_rgb, (size_t)a.ha * a.wa * 3, (uint8_t *)planes.p, h.g, a.pr, a.pg, a.pb, a.sat};
     tile_planes_kernel<<<dim3(h.g.nxw, h.g.nty, n_pairs), 256, 0, st>>>(p);
     ctx->launches++;
     STEPTH_CUDA_TRY(ctx, cudaGetLastError());
@@ -687,9 +688,9 @@ inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const Search
     const size_t cap = (size_t)a.n_queries * n_pairs;
     if (cap > 0xfffffff0ull) return set_err(ctx, STEPTH_ERR_INVALID_ARG, "more than 2^32 queries in one launch");
     const size_t wl_bytes = 64 + cap * sizeof(uint2);
-    rc = ensure(ctx, ctx->worklist, 2 * wl_bytes);
+    rc = ensure(ctx, worklist, 2 * wl_bytes);
     if (rc != STEPTH_OK) return rc;
-    uint8_t *wl0 = (uint8_t *)ctx->worklist.p, *wl1 = wl0 + wl_bytes;
+    uint8_t *wl0 = (uint8_t *)worklist.p, *wl1 = wl0 + wl_bytes;
     STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(wl0, 0, 64, st));
     STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(wl1, 0, 64, st));
     h.wl_cap = (uint32_t)cap;

@@ -80,6 +80,7 @@ extern "C" int32_t stepth_cuda_ctx_create(int32_t device, stepth_ctx **ctx_out) 
     if (const char *ev = getenv("STEPTH_MID_RINGS")) ctx->mid_rings = atoi(ev);
     if (const char *ev = getenv("STEPTH_NEAR_COMPACT")) ctx->near_compact = atoi(ev);
     if (const char *ev = getenv("STEPTH_BATCH_CHUNKS")) ctx->batch_chunks = atoi(ev);
+    if (const char *ev = getenv("STEPTH_TWO_STREAMS")) ctx->two_streams = atoi(ev);
     if (const char *ev = getenv("STEPTH_UPLOAD_FULL_ROWS")) ctx->upload_full_rows = atoi(ev);
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
         g_create_err = std::string("cudaStreamCreate failed: ") + cudaGetErrorString(e);
@@ -87,6 +88,7 @@ extern "C" int32_t stepth_cuda_ctx_create(int32_t device, stepth_ctx **ctx_out) 
         return STEPTH_ERR_CUDA;
     }
     if (cudaStreamCreateWithFlags(&ctx->copy_in, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&ctx->copy_out, cudaStreamNonBlocking) != cudaSuccess) {
         g_create_err = "cudaStreamCreate (copy streams) failed";
         stepth_cuda_ctx_destroy(ctx);
@@ -102,7 +104,7 @@ extern "C" void stepth_cuda_ctx_destroy(stepth_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     stepth_ctx::Buf *bufs[] = {&ctx->main_rgba, &ctx->add_rgb, &ctx->d8,   &ctx->depth, &ctx->mask, &ctx->rgba_out,
                                &ctx->blocks,    &ctx->plane,   &ctx->small, &ctx->u16a,  &ctx->u16b, &ctx->u16o,
-                               &ctx->work,      &ctx->planes, &ctx->worklist};
+                               &ctx->work,      &ctx->planes, &ctx->worklist, &ctx->planes2, &ctx->worklist2};
     for (auto *b : bufs)
         if (b->p) cudaFree(b->p);
     for (auto &kv : ctx->taps)
@@ -111,6 +113,7 @@ extern "C" void stepth_cuda_ctx_destroy(stepth_ctx *ctx) {
     for (cudaEvent_t e : ctx->events) cudaEventDestroy(e);
     if (ctx->copy_in) cudaStreamDestroy(ctx->copy_in);
     if (ctx->copy_out) cudaStreamDestroy(ctx->copy_out);
+    if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -382,22 +385,27 @@ int32_t run_pairs(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_rgba, 
     if (chunk >= 2 && chunk < n) bounds.push_back(chunk / 2);
     while (bounds.back() < n) bounds.push_back(std::min(n, bounds.back() + chunk));
     const uint32_t n_chunks = (uint32_t)bounds.size() - 1;
-    while (ctx->events.size() < 2 * (size_t)n_chunks + 1) {
+    while (ctx->events.size() < 2 * (size_t)n_chunks + 2) {
         cudaEvent_t e;
         STEPTH_CUDA_TRY(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         ctx->events.push_back(e);
     }
     const bool piped = n_chunks > 1;
     cudaStream_t s_in = piped ? ctx->copy_in : st, s_out = piped ? ctx->copy_out : st;
+    const bool two = piped && ctx->two_streams && ctx->stream2;
+    cudaStream_t st0 = st;
     if (piped) {  // the copy streams must not overtake the memset / earlier work on the compute stream
         STEPTH_CUDA_TRY(ctx, cudaEventRecord(ctx->events[2 * n_chunks], st));
         STEPTH_CUDA_TRY(ctx, cudaStreamWaitEvent(s_in, ctx->events[2 * n_chunks], 0));
         STEPTH_CUDA_TRY(ctx, cudaStreamWaitEvent(s_out, ctx->events[2 * n_chunks], 0));
+        if (two) STEPTH_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream2, ctx->events[2 * n_chunks], 0));
     }
     uint8_t *d_main = (uint8_t *)ctx->main_rgba.p, *d_add = (uint8_t *)ctx->add_rgb.p, *d_d8 = (uint8_t *)ctx->d8.p;
     uint8_t *d_depth = (uint8_t *)ctx->depth.p, *d_mask = (uint8_t *)ctx->mask.p, *d_rgba = (uint8_t *)ctx->rgba_out.p;
     for (uint32_t k = 0; k < n_chunks; ++k) {
         const uint32_t i0 = bounds[k], i1 = bounds[k + 1], nc = i1 - i0;
+        ctx->slot = two ? (int)(k & 1) : 0;   // chunks alternate between two compute streams, each with its own scratch
+        st = ctx->slot ? ctx->stream2 : st0;
         for (uint32_t i = i0; i < i1; ++i) {
             const uint8_t *rgba_src = blocks ? (want_apply ? rgba_in[i] : nullptr) : main_rgba[i];
             if (rgba_src)
@@ -455,6 +463,12 @@ int32_t run_pairs(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_rgba, 
             if (want_apply && rgba_out[i])
                 STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(rgba_out[i], d_rgba + px * 4 * i, px * 4, cudaMemcpyDeviceToHost, s_out));
         }
+    }
+    ctx->slot = 0;
+    st = st0;
+    if (two) {  // the small state of the odd chunks is written on stream2
+        STEPTH_CUDA_TRY(ctx, cudaEventRecord(ctx->events[2 * n_chunks + 1], ctx->stream2));
+        STEPTH_CUDA_TRY(ctx, cudaStreamWaitEvent(st, ctx->events[2 * n_chunks + 1], 0));
     }
     STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_small, ctx->small.p, sm.bytes, cudaMemcpyDeviceToHost, st));
     if (raw_d8_out) STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(raw_d8_out, ctx->d8.p, n_q * n, cudaMemcpyDeviceToHost, st));
