@@ -64,6 +64,27 @@ def test_search_dense_ragged_shapes(ctx, orc, w, h, wa, ha):
         assert np.array_equal(gpu_raw(ctx, m, a, prec, 255), ref), (w, h, wa, ha, prec)
 
 
+@pytest.mark.parametrize("w,h,rings,rho", [(200, 120, 64, 0.0), (272, 96, 128, 0.002), (130, 130, 255, 0.0005)])
+def test_search_every_tile_flagged(ctx, orc, w, h, rings, rho):
+    """Adversarial for the tile search: every pixel of the additional image matches the query colour in exactly two
+    channels (which ones varies per pixel), so the per-channel tile-occupancy level flags EVERY tile while the exact test
+    rejects it.  A warp then lists far more tiles than its task array holds (the overflow passes) and, once a planted
+    match is found, drops most of them by the range masks.  rho = density of planted true matches."""
+    rng = np.random.default_rng(w * 7 + rings)
+    base = np.array([60, 130, 200], np.uint8)
+    m = np.broadcast_to(base, (h, w, 3)).copy()
+    m += rng.integers(0, 5, (h, w, 3), dtype=np.uint8)          # query colours within a few levels of the base
+    a = np.broadcast_to(base, (h, w, 3)).copy()
+    off = rng.integers(0, 3, (h, w))                             # the channel that is far off (never within precision 36)
+    a[np.arange(h)[:, None], np.arange(w)[None, :], off] = np.array([160, 30, 100], np.uint8)[off]
+    planted = rng.random((h, w)) < rho
+    a[planted] = base
+    a[h // 2 + 3, w // 2 + 5] = base                             # at least one match: max != 0
+    m = rgba_of(m)
+    ref = orc.search_dense(m, a, P36, rings, threads=8)
+    assert np.array_equal(gpu_raw(ctx, m, a, P36, rings), ref)
+
+
 @pytest.mark.parametrize("rings", [1, 2, 3, 17, 255, 256, 300, 512])
 def test_search_max_rings_and_u8_wrap(ctx, orc, rings):
     # a far planted match: origins near (0,0), the only matching pixels sit 280..420 away -> d >= 256 wraps
