@@ -175,7 +175,8 @@ __device__ __forceinline__ uint32_t dilate_values(uint32_t x, int lane16, int R,
 // (warp OR-reductions) is dilated into E, 256 bits per (tile, channel); the CTA transposes the 32 tiles x 256 values of
 // a channel into 256 words of 32 tile bits and stores the cell with coalesced lines.
 __global__ void __launch_bounds__(256) tile_planes_kernel(TileBuildArgs a) {
-    __shared__ uint32_t s_raw[8][192];    // [row][interleaved RGB of 256 pixels]
+    __shared__ __align__(16) uint32_t s_raw[8][192];    // [row][interleaved RGB of 256 pixels]
+    __shared__ __align__(8) unsigned long long s_bar;   // mbarrier of the bulk copies
     __shared__ uint2 s_tab[3][256];       // plane membership (plane_bits) of every value of a channel
     __shared__ uint32_t s_E[3][8][32];  // [channel][value word g][tile]: bit b <-> q = 32 g + b
     const uint32_t pair = blockIdx.z, xw = blockIdx.x, TY = blockIdx.y;
@@ -183,9 +184,28 @@ __global__ void __launch_bounds__(256) tile_planes_kernel(TileBuildArgs a) {
     const uint8_t *add = a.add_rgb + (size_t)pair * a.src_pair_bytes;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, lane16 = lane & 15;
     const uint32_t x_base = xw * 256u, y_base = TY * 8u;
-    // the strip as it lies in memory (interleaved RGB, 768 bytes per row); rows start on a word when the pitch allows it
+    // the strip as it lies in memory (interleaved RGB, 768 bytes per row).  When the rows start on 16 bytes the TMA unit
+    // brings them in (one bulk copy per row, completion counted on an mbarrier) while the CTA builds its tables
     const size_t pitch = (size_t)a.g.src_wa * 3;
-    if ((pitch & 3) == 0 && (reinterpret_cast<uintptr_t>(add) & 3) == 0) {
+    const uint32_t row_bytes = min(768u, (a.g.src_wa - x_base) * 3u);   // x_base < wa <= src_wa
+    const uint32_t rows = min(8u, ha - y_base);
+    const bool bulk = (pitch & 15) == 0 && (reinterpret_cast<uintptr_t>(add) & 15) == 0 && (row_bytes & 15) == 0;
+    const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar);
+    if (bulk) {
+        if (tid == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(1));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(rows * row_bytes) : "memory");
+            for (uint32_t r = 0; r < rows; ++r) {
+                const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&s_raw[r][0]);
+                const uint8_t *src = add + (size_t)(y_base + r) * pitch + (size_t)x_base * 3;
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                             "l"(src), "r"(row_bytes), "r"(bar)
+                             : "memory");
+            }
+        }
+    } else if ((pitch & 3) == 0 && (reinterpret_cast<uintptr_t>(add) & 3) == 0) {
         const uint32_t row_words = (uint32_t)(pitch >> 2);            // words of one image row
         for (int i = tid; i < 8 * 192; i += 256) {
             const int r = i / 192, k = i - r * 192;
@@ -213,7 +233,16 @@ __global__ void __launch_bounds__(256) tile_planes_kernel(TileBuildArgs a) {
         plane_bits(tid, prec[c], sat, true, lo, hi);
         s_tab[c][tid] = make_uint2(lo, hi);
     }
-    __syncthreads();
+    __syncthreads();   // tables, s_E, the staged strip of the non-bulk paths -- and the mbarrier's initialisation
+    if (bulk) {        // rows and columns beyond the image keep whatever shared memory held: their pixels are masked (ok0 / ok1)
+        uint32_t done;
+        do {
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                         : "=r"(done)
+                         : "r"(bar), "r"(0)
+                         : "memory");
+        } while (!done);
+    }
     uint8_t *pair_base = a.planes + (size_t)pair * a.g.pair_bytes;
     unsigned long long *fine = reinterpret_cast<unsigned long long *>(pair_base);
     const uint8_t *raw = reinterpret_cast<const uint8_t *>(&s_raw[0][0]);
