@@ -192,10 +192,16 @@ class BandRunner:
         else:
             depth = torch.empty((1, 0, self.w), dtype=torch.uint8, device=dev)
             status = torch.zeros(1, dtype=torch.int32, device=dev)
-        # max == 0 is a property of the whole image: every rank sees the same all-reduced value
-        out["status"] = _ffi.ERR_DIV_BY_ZERO_MAX if int(mx[0]) == 0 else int(status[0]) if rows > 0 else 0
+        # max == 0 is a property of the whole image: every rank sees the same all-reduced value.  Without the fused tail
+        # nothing on the host depends on the status, so it is read once, after the last exchange has been enqueued (a
+        # blocking read here would expose every later launch and collective to the host's latency).
+        def read_status() -> int:
+            return _ffi.ERR_DIV_BY_ZERO_MAX if int(mx[0]) == 0 else int(status[0]) if rows > 0 else 0
+
         out["depth_band"] = depth
         self._mark("finish")
+        if want_fg:
+            out["status"] = read_status()
         if want_fg and out["status"] == 0:
             hist = self._allreduce(hist, dist.ReduceOp.SUM)              # exchange 3: the histogram
             ranges, n_out, st2 = self.st.depth_split(hist)
@@ -208,6 +214,8 @@ class BandRunner:
                     out["mask_band"], out["rgba_band"] = mask, rgba_out
         if gather_depth:                                                 # exchange 4: assemble the map everywhere
             out["depth"] = self.gather_bands(depth)
+        if not want_fg:
+            out["status"] = read_status()
         self._mark("tail+gather")
         self._close_marks()
         return out
