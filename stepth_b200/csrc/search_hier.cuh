@@ -357,46 +357,51 @@ STEPTH_HD int tile_smin(const HierQuery &q, int TX, int TY) {
     return dxm > dym ? dxm : dym;
 }
 
+// flags of the tile run [lo, hi] of plane line `line` as one 32-bit word (bit i <-> tile lo + i); needs hi - lo < 31, which holds
+// for the sides of coarse rings <= 15 (at most 31 tiles): the run lies inside the 64-tile window that starts at lo & ~31
+__device__ __forceinline__ uint32_t side_flags32(const unsigned long long *plane, int wpl, int line, int n_lines, int lo, int hi,
+                                                 const HierQuery &q) {
+    if ((unsigned)line >= (unsigned)n_lines || lo > hi) return 0u;
+    const unsigned long long w = coarse_window(plane, (uint32_t)(line * wpl + (lo >> 5)), q);
+    const uint32_t m = __funnelshift_r((uint32_t)w, (uint32_t)(w >> 32), lo & 31);
+    return m & ((2u << (hi - lo)) - 1u);
+}
+
 // keeps the bits i of m with tmin <= lo + i <= tmax
-__device__ __forceinline__ unsigned long long keep_range(unsigned long long m, int lo, int tmin, int tmax) {
+__device__ __forceinline__ uint32_t keep_range(uint32_t m, int lo, int tmin, int tmax) {
     int a = tmin - lo, b = tmax - lo;
     a = a < 0 ? 0 : a;
-    if (b < a || a > 63) return 0ull;
-    b = b > 63 ? 63 : b;
-    return m & (~0ull << a) & (~0ull >> (63 - b));
+    if (b < a || a > 31) return 0u;
+    b = b > 31 ? 31 : b;
+    return m & (~0u << a) & (~0u >> (31 - b));
 }
 
 // Drops the flagged tiles of ring S that cannot hold the answer: a tile whose nearest pixel lies beyond `limit` (the best
 // ring so far, or max_rings - 1).  A whole side goes when its line is too far; along the side the tiles within reach are a
 // run, so the pruning is one bit-range mask per side instead of a distance per tile.
-__device__ __forceinline__ void prune_sides(const HierQuery &q, int S, int limit, int rlo, int clo, unsigned long long &f0,
-                                            unsigned long long &f1, unsigned long long &f2, unsigned long long &f3) {
+__device__ __forceinline__ void prune_sides(const HierQuery &q, int S, int limit, int rlo, int clo, uint32_t &f0, uint32_t &f1,
+                                            uint32_t &f2, uint32_t &f3) {
     const int T0x = q.ox >> 3, T0y = q.oy >> 3;
     const int xa = (q.ox - limit) >> 3, xb = (q.ox + limit) >> 3;   // tile columns with a pixel at |dx| <= limit
     const int ya = (q.oy - limit) >> 3, yb = (q.oy + limit) >> 3;
-    f0 = (T0y + S) * 8 - q.oy > limit ? 0ull : keep_range(f0, rlo, xa, xb);
-    f1 = q.oy - ((T0y - S) * 8 + 7) > limit ? 0ull : keep_range(f1, rlo, xa, xb);
-    f2 = (T0x + S) * 8 - q.ox > limit ? 0ull : keep_range(f2, clo, ya, yb);
-    f3 = q.ox - ((T0x - S) * 8 + 7) > limit ? 0ull : keep_range(f3, clo, ya, yb);
+    f0 = (T0y + S) * 8 - q.oy > limit ? 0u : keep_range(f0, rlo, xa, xb);
+    f1 = q.oy - ((T0y - S) * 8 + 7) > limit ? 0u : keep_range(f1, rlo, xa, xb);
+    f2 = (T0x + S) * 8 - q.ox > limit ? 0u : keep_range(f2, clo, ya, yb);
+    f3 = q.ox - ((T0x - S) * 8 + 7) > limit ? 0u : keep_range(f3, clo, ya, yb);
 }
 
 // Lists the flagged tiles of one side of a ring as tasks of the warp from slot `slot` on (the lane reserved its slots with
 // one atomic for all four sides); the bits that do not fit below WTASKS come back and are listed again in the next pass.
-__device__ __forceinline__ unsigned long long emit_side(unsigned long long m, int lo, int line, bool is_col, uint32_t lane,
-                                                        uint32_t &slot, WarpScratch *ws) {
+__device__ __forceinline__ uint32_t emit_side(uint32_t m, int lo, int line, bool is_col, uint32_t lane, uint32_t &slot,
+                                              WarpScratch *ws) {
     // task = owner << 26 | TX << 13 | TY: row sides step TX (bit 13), column sides step TY (bit 0)
     const uint32_t code = lane << 26 | (is_col ? (uint32_t)line << 13 | (uint32_t)lo : (uint32_t)lo << 13 | (uint32_t)line);
     const int sh = is_col ? 0 : 13;
-    uint32_t w0 = (uint32_t)m, w1 = (uint32_t)(m >> 32);
-    while (w0 && slot < (uint32_t)WTASKS) {
-        ws->task[slot++] = code + ((uint32_t)(__ffs((int)w0) - 1) << sh);
-        w0 &= w0 - 1;
+    while (m && slot < (uint32_t)WTASKS) {
+        ws->task[slot++] = code + ((uint32_t)(__ffs((int)m) - 1) << sh);
+        m &= m - 1;
     }
-    while (!w0 && w1 && slot < (uint32_t)WTASKS) {
-        ws->task[slot++] = code + ((uint32_t)(__ffs((int)w1) + 31) << sh);
-        w1 &= w1 - 1;
-    }
-    return (unsigned long long)w1 << 32 | w0;
+    return m;
 }
 
 // All 32 lanes call this together.  `walking` lanes carry a query (v, q, best); the others only help with tile tests.
@@ -412,7 +417,7 @@ __device__ __forceinline__ bool hier_rings_warp(bool walking, const uint8_t *pla
     const int xmax = v.ntx - 1, ymax = v.nty - 1;
     bool final_ = !walking;
     for (int S = S0; S < S_end; ++S) {
-        unsigned long long f0 = 0, f1 = 0, f2 = 0, f3 = 0;
+        uint32_t f0 = 0, f1 = 0, f2 = 0, f3 = 0;
         int rlo = 0, clo = 0;
         const bool go = walking && !final_;
         if (go) {
@@ -426,13 +431,14 @@ __device__ __forceinline__ bool hier_rings_warp(bool walking, const uint8_t *pla
                 rlo = T0x - S < 0 ? 0 : T0x - S;
                 clo = T0y - S + 1 < 0 ? 0 : T0y - S + 1;
                 const int rhi = T0x + S > xmax ? xmax : T0x + S, chi = T0y + S - 1 > ymax ? ymax : T0y + S - 1;
-                if (S <= 16) {
-                    f0 = side_flags(v.crp, v.nxw, T0y + S, v.nty, rlo, rhi, q);
-                    f1 = side_flags(v.crp, v.nxw, T0y - S, v.nty, rlo, rhi, q);
-                    f2 = side_flags(v.ccp, v.nyw, T0x + S, v.ntx, clo, chi, q);
-                    f3 = side_flags(v.ccp, v.nyw, T0x - S, v.ntx, clo, chi, q);
+                if (S <= 15) {
+                    // a side is at most 31 tiles: 32-bit flags, the warp pools the tile tests below
+                    f0 = side_flags32(v.crp, v.nxw, T0y + S, v.nty, rlo, rhi, q);
+                    f1 = side_flags32(v.crp, v.nxw, T0y - S, v.nty, rlo, rhi, q);
+                    f2 = side_flags32(v.ccp, v.nyw, T0x + S, v.ntx, clo, chi, q);
+                    f3 = side_flags32(v.ccp, v.nyw, T0x - S, v.ntx, clo, chi, q);
                 } else {
-                    // sides longer than one window (max_rings > 134): this lane tests its tiles itself, window by window
+                    // longer sides (max_rings > 120): this lane tests its tiles itself, window by window
 #pragma unroll 1
                     for (int side = 0; side < 4; ++side) {
                         const bool is_col = side >= 2;
@@ -454,7 +460,7 @@ __device__ __forceinline__ bool hier_rings_warp(bool walking, const uint8_t *pla
             }
         }
         // ---- pool the tile tests of the warp -----------------------------------------------------------------------------
-        while (__any_sync(0xffffffffu, (f0 | f1 | f2 | f3) != 0ull)) {
+        while (__any_sync(0xffffffffu, (f0 | f1 | f2 | f3) != 0u)) {
             if (lane == 0) ws->n = 0;
             ws->best[lane] = best;
             __syncwarp();
@@ -462,7 +468,7 @@ __device__ __forceinline__ bool hier_rings_warp(bool walking, const uint8_t *pla
                 // with a match in hand (or at the last rings) most flagged tiles are out of reach and are not listed
                 const int limit = min(D - 1, (int)(best >> 12));
                 if (limit < 8 * S + 7) prune_sides(q, S, limit, rlo, clo, f0, f1, f2, f3);  // else every tile of the ring is in reach
-                const uint32_t cnt = __popcll(f0) + __popcll(f1) + __popcll(f2) + __popcll(f3);
+                const uint32_t cnt = __popc(f0) + __popc(f1) + __popc(f2) + __popc(f3);
                 if (cnt) {
                     uint32_t slot = atomicAdd(&ws->n, cnt);  // slots [slot, slot + cnt); those beyond WTASKS wait for the next pass
                     f0 = emit_side(f0, rlo, T0y + S, false, lane, slot, ws);
