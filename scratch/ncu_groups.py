@@ -19,7 +19,7 @@ _src = open("/root/repo/stepth_b200/csrc/search_hier.cuh").read().split("\n")
 _marks = [("tile_min_key", "STEPTH_HD uint32_t tile_min_key"), ("HierQuery", "struct HierQuery {"), ("fine_test", "STEPTH_HD void fine_test"),
           ("coarse_window/side_flags", "STEPTH_HD unsigned long long coarse_window"), ("hier_rings (host)", "STEPTH_HD bool hier_rings("),
           ("HierArgs..", "struct HierArgs {"), ("query_of", "void query_of("), ("publish_result", "template <bool ONE_PAIR"),
-          ("export_open", "void export_open("), ("scratch", "constexpr int WTASKS"), ("prune_sides", "unsigned long long keep_range("),
+          ("export_open", "void export_open("), ("scratch", "constexpr int WTASKS"), ("prune_sides", "uint32_t side_flags32("),
           ("emit_side", "unsigned long long emit_side("), ("walk: ring setup", "bool hier_rings_warp("),
           ("walk: pool listing", "// ---- pool the tile tests of the warp"), ("walk: pool tests", "const int n_pass ="),
           ("walk: ring end", "if (go && best != KEY_NONE"), ("near kernel body", "#ifndef STEPTH_NEAR_MINB"),
