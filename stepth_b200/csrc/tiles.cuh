@@ -18,10 +18,11 @@
 // bits are 0 in every plane: the reference skips out-of-bounds probes (helpers.rs:19-25,44).
 //
 // FINE level (u64 words).  One record per 8x8 tile, 3 channels x 64 slots:
-//   slot 0..31 U[0..31] | 32 U[-1] | 33 U[32] | 34..41 NTA[0..7] | 42..49 NTB[0..7] | 50..63 unused (never written)
+//   slot 0 U[-1] | 1..32 U[0..31] | 33 U[32] | 34..41 NTA[0..7] | 42..49 NTB[0..7] | 50..63 unused (never written)
+//   (U[j-1], U[j], U[j+1] of a query are three consecutive words: one address, no special cases at j = 0 and j = 31)
 //   F[((TY * ntx + TX) * 3 + c) * 64 + slot]      bit (ly * 8 + lx) <-> pixel (8 TX + lx, 8 TY + ly)
-// The 32 U words of one channel of one tile are 256 contiguous bytes: lanes that look at the same tile with different
-// query colours hit two 128-byte lines.
+// The 34 U words of one channel of one tile are contiguous: lanes that look at the same tile with different query colours
+// hit two or three 128-byte lines.
 //
 // COARSE level: E_c[q] bit = "some pixel of this tile has channel c inside T(q)", one plane per exact query value
 // q = 0..255.  A cell is a 64-tile WINDOW that starts every 32 tiles (u64 = {tiles 32w .. 32w+31, tiles 32w+32 .. 32w+63}),
@@ -45,7 +46,7 @@ constexpr int T_SLOTS = 64;          // u64 slots per channel of a tile record
 constexpr int T_REC = 3 * T_SLOTS;   // u64 words per tile record (192 = 1536 bytes)
 constexpr int C_Q = 256;             // coarse planes per channel: one per exact query value
 constexpr int C_CELL = 3 * C_Q;      // u64 windows per coarse cell (768 = 6144 bytes)
-constexpr int W_UM1 = 32, W_UP32 = 33, W_NTA = 34, W_NTB = 42, W_USED = 50;
+constexpr int W_UM1 = 0, W_U0 = 1, W_UP32 = 33, W_NTA = 34, W_NTB = 42, W_USED = 50;
 static_assert(NB * QSTEP == 256 && NB == 32, "the layouts assume 32 bins of 8 levels");
 
 struct TileGeom {
@@ -78,9 +79,9 @@ inline TileGeom make_tile_geom(uint32_t wa, uint32_t ha, uint32_t src_wa) {
 }
 
 // slot offsets (inside one channel of a tile record) a query value q needs
-STEPTH_HD uint32_t w_u(uint32_t q) { return q >> QSHIFT; }
-STEPTH_HD uint32_t w_um1(uint32_t q) { uint32_t j = q >> QSHIFT; return j ? j - 1 : (uint32_t)W_UM1; }
-STEPTH_HD uint32_t w_up1(uint32_t q) { uint32_t j = q >> QSHIFT; return j < NB - 1 ? j + 1 : (uint32_t)W_UP32; }
+STEPTH_HD uint32_t w_um1(uint32_t q) { return q >> QSHIFT; }          // U[j - 1]
+STEPTH_HD uint32_t w_u(uint32_t q) { return (q >> QSHIFT) + 1; }      // U[j]
+STEPTH_HD uint32_t w_up1(uint32_t q) { return (q >> QSHIFT) + 2; }    // U[j + 1]
 STEPTH_HD uint32_t w_nta(uint32_t q) { return W_NTA + (q & (QSTEP - 1)); }
 STEPTH_HD uint32_t w_ntb(uint32_t q) { return W_NTB + (q & (QSTEP - 1)); }
 
@@ -265,8 +266,9 @@ __global__ void __launch_bounds__(256) tile_planes_kernel(TileBuildArgs a) {
             hi0 = warp_bit_transpose(hi0, lane);
             hi1 = warp_bit_transpose(hi1, lane);
             unsigned long long *rec = fine + (((size_t)TY * a.g.ntx + TX) * 3 + c) * T_SLOTS;
-            rec[lane] = (unsigned long long)lo0 | ((unsigned long long)lo1 << 32);
-            if (lane < W_USED - 32) rec[32 + lane] = (unsigned long long)hi0 | ((unsigned long long)hi1 << 32);
+            rec[W_U0 + lane] = (unsigned long long)lo0 | ((unsigned long long)lo1 << 32);
+            // hi word of lane 0 = U[-1] -> slot 0; lane 1 = U[32] -> slot 33; lanes 2..17 = NTA / NTB -> slots 34..49
+            if (lane < W_USED - 32) rec[lane ? 32 + lane : W_UM1] = (unsigned long long)hi0 | ((unsigned long long)hi1 << 32);
             // the set of values present in the tile, one 32-value word at a time: only the words some pixel falls into
             // are visited (a natural tile spans one to three of the eight)
             uint32_t need = (ok0 ? 1u << (v0 >> 5) : 0u) | (ok1 ? 1u << (v1 >> 5) : 0u);

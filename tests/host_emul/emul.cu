@@ -28,7 +28,7 @@ void build_planes_host(const uint8_t *add, const TileGeom &g, int pr, int pg, in
                 plane_bits(add[((size_t)y * g.src_wa + x) * 3 + c], prec[c], sat, true, lo, hi);
                 unsigned long long *rec = fine + (((size_t)TY * g.ntx + TX) * 3 + c) * T_SLOTS;
                 for (int j = 0; j < 32; ++j)
-                    if (lo & (1u << j)) rec[j] |= 1ull << bit;
+                    if (lo & (1u << j)) rec[W_U0 + j] |= 1ull << bit;
                 // coarse level: one plane per exact query value q with v inside T(q)
                 const int v = add[((size_t)y * g.src_wa + x) * 3 + c], p = prec[c];
                 for (int q = 0; q < 256; ++q) {
@@ -42,7 +42,7 @@ void build_planes_host(const uint8_t *add, const TileGeom &g, int pr, int pg, in
                     }
                 }
                 for (int j = 0; j < W_USED - 32; ++j)
-                    if (hi & (1u << j)) rec[32 + j] |= 1ull << bit;
+                    if (hi & (1u << j)) rec[j ? 32 + j : W_UM1] |= 1ull << bit;
             }
         }
 }
