@@ -37,7 +37,8 @@ struct stepth_ctx {
     int upload_full_rows = 0;  // host-buffer entry points upload whole rows of the additional image (STEPTH_UPLOAD_FULL_ROWS)
     int near_compact = 1;  // the near kernel packs the queries that survive ring 0 into full warps (STEPTH_NEAR_COMPACT)
     int mid_rings = 10;  // first far kernel walks coarse rings [near_rings, mid_rings); 0 = one far kernel (STEPTH_MID_RINGS)
-    Buf planes2, worklist2;  // scratch set of slot 1
+    Buf planes2, worklist2, work2;  // scratch set of slot 1 (work / work2: the plane between the two streaming finish passes)
+    int finish_streaming = 1;       // STEPTH_FINISH_STREAMING: 0 = always the tiled finish kernel
     int two_streams = 1;     // STEPTH_TWO_STREAMS
     Buf planes;  // two-level match bit-planes of the additional image(s) (tiles.cuh), rebuilt by every search
     // small per-pair state: [max u32][hist 256 u32][status i32][n_out u32][ranges 512 B] per pair

@@ -213,4 +213,177 @@ __global__ void __launch_bounds__(256) finish_kernel(FinishArgs a) {
     }
 }
 
+
+// ---- streaming form of K2 for the default mode (STEPTH_RESAMPLE_U8, rows that are whole words) ---------------------------
+// The u8 intermediate of the two-pass resample (image 0.23.14 rounds `vertical_sample`'s output to the pixel type before
+// `horizontal_sample` reads it) makes the passes two plain streaming kernels with a 1 B/px plane between them: no shared
+// memory tile, no barriers, every thread works on four (vertical) or eight (horizontal) neighbouring pixels out of
+// registers.  The extra plane costs 2 B/px of HBM traffic -- a few microseconds -- and removes the staging that bounded
+// the tiled kernel.  Arithmetic and order are the tiled kernel's (and the reference's): t = t + px * w in tap order.
+
+// exact float of an integer below 2^23 without the (quarter-rate) conversion unit: 2^23 + n has n in its low mantissa bits
+__device__ __forceinline__ float small_to_float(uint32_t n) { return __fsub_rn(__uint_as_float(0x4b000000u | n), 8388608.0f); }
+
+// (v * 255 / max) as u8 (depth_image.rs:127) without a table: floor(n / d) = umulhi(n, floor(2^32 / d) + 1) holds for
+// n <= 65025, d <= 255 (error term n * d < 2^32); d == 1 would overflow the constant and needs no division
+struct NormDiv {
+    uint32_t magic, one;
+    __device__ __forceinline__ explicit NormDiv(uint32_t mx) : magic(mx == 1u ? 0u : 0xffffffffu / mx + 1u), one(mx == 1u) {}
+    __device__ __forceinline__ float operator()(uint32_t v) const {
+        const uint32_t n = v * 255u;
+        return small_to_float(one ? n : __umulhi(n, magic));
+    }
+};
+
+// clamp(t, 0, 255) then f32::round (half away from zero), for 0 <= t < 255.5 -- a normalised sum of values in [0, 255]
+// never leaves that range, so the clamp is the identity on the rounded result.  t + 2^23 rounds to nearest-even into the
+// low mantissa bits; the two differ only on an exact tie that went down, which the exact remainder t - r shows.
+__device__ __forceinline__ uint32_t round_u8(float t) {
+    const float u = __fadd_rn(t, 8388608.0f);
+    const float d = __fsub_rn(t, __fsub_rn(u, 8388608.0f));
+    return (__float_as_uint(u) & 0x1ffu) + (d == 0.5f ? 1u : 0u);
+}
+
+constexpr int FV_ROWS = 21;  // output rows per thread of the vertical pass (27 row loads for 21 rows); a multiple of 7
+
+__global__ void __launch_bounds__(128) finish_vert_kernel(FinishArgs a, uint8_t *tmp) {
+    const uint32_t pair = blockIdx.z;
+    const uint32_t mx = a.max_in[pair];
+    if (mx == 0) {  // depth_image.rs:127 divides by zero -> panic; reported per pair, nothing written
+        if (a.status && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) a.status[pair] = STEPTH_ERR_DIV_BY_ZERO_MAX;
+        return;
+    }
+    const NormDiv norm(mx);
+    const int wq = (int)(a.w >> 2), xq = blockIdx.x * 128 + threadIdx.x;
+    if (xq >= wq) return;
+    const int r0 = blockIdx.y * FV_ROWS, rows = min(FV_ROWS, (int)a.out_rows - r0);
+    const int gy0 = (int)a.out_y0 + r0, img_h = (int)a.img_h;
+    const uint8_t *srcp = a.src + (size_t)pair * a.src_rows * a.w;
+    uint32_t *dst = reinterpret_cast<uint32_t *>(tmp + (size_t)pair * a.out_rows * a.w) + (size_t)r0 * wq + xq;
+    if (gy0 >= 3 && gy0 + rows + 3 <= img_h) {
+        // every row of the segment has the seven interior taps: a seven-row window per column slides down in registers
+        const uint32_t *col = reinterpret_cast<const uint32_t *>(srcp) + (size_t)(gy0 - 3 - (int)a.src_y0) * wq + xq;
+        float win[7][4];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+            const uint32_t px = __ldg(col + (size_t)k * wq);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) win[k][c] = norm((px >> (8 * c)) & 0xffu);
+        }
+        // the window index cycles with period 7: seven rows are unrolled (static register indices), the groups loop
+#pragma unroll 1
+        for (int j0 = 0; j0 < FV_ROWS; j0 += 7) {
+#pragma unroll
+            for (int jj = 0; jj < 7; ++jj) {
+                const int j = j0 + jj;
+                if (j < rows) {
+                    const uint32_t px = __ldg(col + (size_t)(j + 6) * wq);
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) win[(jj + 6) % 7][c] = norm((px >> (8 * c)) & 0xffu);
+                    uint32_t out = 0;
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        float t = 0.0f;
+#pragma unroll
+                        for (int k = 0; k < 7; ++k) t = __fadd_rn(t, __fmul_rn(win[(jj + k) % 7][c], a.wy_int[k]));
+                        out |= round_u8(t) << (8 * c);
+                    }
+                    dst[(size_t)j * wq] = out;
+                }
+            }
+        }
+    } else {
+        // a border row in reach: per output through the host-built tap rows (rare: the first and last segments only)
+        for (int j = 0; j < rows; ++j) {
+            const TapRow &tp = a.taps_y[gy0 + j];
+            uint32_t out = 0;
+            for (int c = 0; c < 4; ++c) {
+                float t = 0.0f;
+                for (int k = 0; k < tp.cnt; ++k) {
+                    const uint32_t v = srcp[(size_t)(tp.left + k - (int)a.src_y0) * a.w + 4 * xq + c];
+                    t = __fadd_rn(t, __fmul_rn(norm(v), tp.w[k]));
+                }
+                out |= round_u8(t) << (8 * c);
+            }
+            dst[(size_t)j * wq] = out;
+        }
+    }
+}
+
+// horizontal pass + invert + histogram: a thread owns 8 neighbouring outputs of a row, a CTA 256 columns x 32 rows
+__global__ void __launch_bounds__(256) finish_horz_kernel(FinishArgs a, const uint8_t *tmp) {
+    __shared__ uint32_t s_hist[256];
+    const uint32_t pair = blockIdx.z;
+    if (a.max_in[pair] == 0) return;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    s_hist[tid] = 0;
+    __syncthreads();
+    const int w = (int)a.w, x0 = blockIdx.x * 256 + lane * 8;
+    const uint32_t inv = a.invert ? 0xffffffffu : 0u;
+    const uint8_t *tplane = tmp + (size_t)pair * a.out_rows * a.w;
+    uint8_t *dplane = a.dst + (size_t)pair * a.out_rows * a.w;
+    for (int it = 0; it < 4; ++it) {
+        const int row = blockIdx.y * 32 + it * 8 + warp;
+        if (row >= (int)a.out_rows || x0 >= w) continue;
+        const uint8_t *trow = tplane + (size_t)row * w;
+        uint32_t o[2] = {0u, 0u};
+        if (x0 >= 4 && x0 + 12 <= w) {
+            // columns x0 - 4 .. x0 + 11 as four words; output j reads columns x0 + j - 3 .. x0 + j + 3
+            const uint32_t *tw = reinterpret_cast<const uint32_t *>(trow + x0 - 4);
+            float b[16];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t px = __ldg(tw + k);
+#pragma unroll
+                for (int c = 0; c < 4; ++c)   // one byte permute builds the bits of 2^23 + byte
+                    b[4 * k + c] = __fsub_rn(__uint_as_float(__byte_perm(px, 0x4b000000u, 0x7540u | c)), 8388608.0f);
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                float t = 0.0f;
+#pragma unroll
+                for (int k = 0; k < 7; ++k) t = __fadd_rn(t, __fmul_rn(b[j + 1 + k], a.wx_int[k]));
+                o[j >> 2] |= round_u8(t) << (8 * (j & 3));
+            }
+        } else {
+            for (int j = 0; j < 8; ++j) {
+                const int gx = x0 + j;
+                if (gx >= w) break;
+                float t = 0.0f;
+                if (gx >= 3 && gx + 4 <= w) {
+                    for (int k = 0; k < 7; ++k) t = __fadd_rn(t, __fmul_rn((float)trow[gx - 3 + k], a.wx_int[k]));
+                } else {
+                    const TapRow &tp = a.taps_x[gx];
+                    for (int k = 0; k < tp.cnt; ++k) t = __fadd_rn(t, __fmul_rn((float)trow[tp.left + k], tp.w[k]));
+                }
+                o[j >> 2] |= round_u8(t) << (8 * (j & 3));
+            }
+        }
+        o[0] ^= inv;
+        o[1] ^= inv;
+        uint32_t *drow = reinterpret_cast<uint32_t *>(dplane + (size_t)row * w + x0);   // w % 4 == 0: word aligned
+        const int n = min(8, w - x0);                                                      // 4 or 8 (w % 4 == 0)
+        drow[0] = o[0];
+        if (n == 8) drow[1] = o[1];
+        if (a.hist) {
+            // neighbouring outputs are mostly equal: feed the shared-memory histogram run-length encoded
+            uint32_t run_val = o[0] & 0xffu, run_len = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (j < n) {
+                    const uint32_t v = (o[j >> 2] >> (8 * (j & 3))) & 0xffu;
+                    if (v != run_val) { atomicAdd(&s_hist[run_val], run_len); run_val = v; run_len = 0; }
+                    ++run_len;
+                }
+            }
+            atomicAdd(&s_hist[run_val], run_len);
+        }
+    }
+    if (a.hist) {
+        __syncthreads();
+        const uint32_t c = s_hist[tid];
+        if (c) atomicAdd(&a.hist[(size_t)pair * 256 + tid], c);
+    }
+}
+
 }  // namespace stepth

@@ -81,6 +81,7 @@ extern "C" int32_t stepth_cuda_ctx_create(int32_t device, stepth_ctx **ctx_out) 
     if (const char *ev = getenv("STEPTH_NEAR_COMPACT")) ctx->near_compact = atoi(ev);
     if (const char *ev = getenv("STEPTH_BATCH_CHUNKS")) ctx->batch_chunks = atoi(ev);
     if (const char *ev = getenv("STEPTH_TWO_STREAMS")) ctx->two_streams = atoi(ev);
+    if (const char *ev = getenv("STEPTH_FINISH_STREAMING")) ctx->finish_streaming = atoi(ev);
     if (const char *ev = getenv("STEPTH_UPLOAD_FULL_ROWS")) ctx->upload_full_rows = atoi(ev);
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
         g_create_err = std::string("cudaStreamCreate failed: ") + cudaGetErrorString(e);
@@ -104,7 +105,7 @@ extern "C" void stepth_cuda_ctx_destroy(stepth_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     stepth_ctx::Buf *bufs[] = {&ctx->main_rgba, &ctx->add_rgb, &ctx->d8,   &ctx->depth, &ctx->mask, &ctx->rgba_out,
                                &ctx->blocks,    &ctx->plane,   &ctx->small, &ctx->u16a,  &ctx->u16b, &ctx->u16o,
-                               &ctx->work,      &ctx->planes, &ctx->worklist, &ctx->planes2, &ctx->worklist2};
+                               &ctx->work,      &ctx->planes, &ctx->worklist, &ctx->planes2, &ctx->worklist2, &ctx->work2};
     for (auto *b : bufs)
         if (b->p) cudaFree(b->p);
     for (auto &kv : ctx->taps)
@@ -248,6 +249,21 @@ extern "C" int32_t stepth_cuda_dev_finish(stepth_ctx *ctx, void *stream, uint32_
         if (rc != STEPTH_OK) return rc;
         rc = get_taps(ctx, st, w, &a.taps_x, a.wx_int);
         if (rc != STEPTH_OK) return rc;
+    }
+    if (a.mode == STEPTH_RESAMPLE_U8 && (w & 3) == 0 && w >= 8 && ctx->finish_streaming &&
+        ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(depth_out)) & 3) == 0) {
+        // the default mode on whole-word rows: two streaming kernels with a 1 B/px plane between them (finish.cuh)
+        stepth_ctx::Buf &tmp = ctx->slot ? ctx->work2 : ctx->work;
+        int32_t rc = ensure(ctx, tmp, (size_t)n_pairs * out_rows * w);
+        if (rc != STEPTH_OK) return rc;
+        dim3 gv((w / 4 + 127) / 128, (out_rows + FV_ROWS - 1) / FV_ROWS, n_pairs);
+        dim3 gh((w + 255) / 256, (out_rows + 31) / 32, n_pairs);
+        if (gv.y > 65535) return set_err(ctx, STEPTH_ERR_INVALID_ARG, "dev_finish: more than 1M rows in one band");
+        finish_vert_kernel<<<gv, 128, 0, st>>>(a, (uint8_t *)tmp.p);
+        LAUNCH_CHECK(ctx);
+        finish_horz_kernel<<<gh, 256, 0, st>>>(a, (const uint8_t *)tmp.p);
+        LAUNCH_CHECK(ctx);
+        return STEPTH_OK;
     }
     dim3 grid((w + FIN_TILE_W - 1) / FIN_TILE_W, (out_rows + FIN_TILE_H - 1) / FIN_TILE_H, n_pairs);
     if (grid.y > 65535) return set_err(ctx, STEPTH_ERR_INVALID_ARG, "dev_finish: more than 2M rows in one band");
