@@ -135,7 +135,9 @@ def test_depth_dense_vs_oracle(ctx, orc, resample, kind, w, h):
     assert np.array_equal(out["depth"], ref)
 
 
-@pytest.mark.parametrize("shape", [(8, 1), (1, 9), (2, 7), (5, 5), (6, 300), (300, 6), (40, 129)])
+@pytest.mark.parametrize("shape", [(8, 1), (1, 9), (2, 7), (5, 5), (6, 300), (300, 6), (40, 129),
+                                   # whole-word rows take the streaming form of K2: several row segments / column blocks
+                                   (129, 40), (50, 1040), (7, 8), (30, 12), (3, 16), (22, 516), (64, 260)])
 def test_finish_small_and_border_shapes(ctx, orc, shape):
     """the Gaussian's border renormalisation and tiny images (fewer than 7 taps), through the band-capable K2"""
     from stepth_b200 import device
@@ -151,6 +153,23 @@ def test_finish_small_and_border_shapes(ctx, orc, shape):
         depth, status = device.finish(ctx, src, mxt, h, g)
         assert int(status[0]) == 0
         assert np.array_equal(depth[0].cpu().numpy(), orc.gaussian_resample_unit(norm, o)), (shape, g)
+
+
+def test_finish_normalise_every_max(ctx, orc):
+    """(v * 255 / max) as u8 for every possible max: the streaming K2 divides by a multiply-high constant, not a table"""
+    from stepth_b200 import device
+
+    h, w = 9, 256
+    for mx in list(range(1, 256)):
+        raw = (np.arange(h * w, dtype=np.int64).reshape(h, w) * 7919 % (mx + 1)).astype(np.uint8)
+        raw[4, 100] = mx
+        norm, got_mx = orc.normalise(raw)
+        assert got_mx == mx
+        src = torch.from_numpy(raw).cuda().unsqueeze(0)
+        mxt = torch.tensor([mx], dtype=torch.int32, device="cuda")
+        depth, status = device.finish(ctx, src, mxt, h, 1)
+        assert int(status[0]) == 0
+        assert np.array_equal(depth[0].cpu().numpy(), orc.gaussian_resample_unit(norm, orc.RESAMPLE_U8)), mx
 
 
 def test_fused_tail_vs_oracle(ctx, orc):
