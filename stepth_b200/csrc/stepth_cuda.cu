@@ -408,7 +408,10 @@ int32_t run_pairs(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_rgba, 
     }
     const bool piped = n_chunks > 1;
     cudaStream_t s_in = piped ? ctx->copy_in : st, s_out = piped ? ctx->copy_out : st;
-    const bool two = piped && ctx->two_streams && ctx->stream2;
+    // two alternating compute streams pay off for small chunks (their poorly filled last kernels overlap the next chunk's
+    // first ones); a chunk that fills the GPU by itself only finishes later that way, and so does its copy-out (measured:
+    // 1080p pairs 4.31 -> 4.03 ms per 16, one 4K pair per chunk 5.54 -> 5.92 ms per 4)
+    const bool two = piped && ctx->two_streams && ctx->stream2 && (uint64_t)chunk * px <= 6000000ull;
     cudaStream_t st0 = st;
     if (piped) {  // the copy streams must not overtake the memset / earlier work on the compute stream
         STEPTH_CUDA_TRY(ctx, cudaEventRecord(ctx->events[2 * n_chunks], st));
