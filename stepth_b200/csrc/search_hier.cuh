@@ -17,10 +17,14 @@
 //     best key so far has ring <= 8S; a tile whose nearest pixel is farther than the best ring so far (or >= max) is skipped.
 //
 // Work per query is data dependent (most queries stop at ring 0; a few percent walk to the last ring), so the walk is
-// split: the NEAR kernel (one thread per main pixel / per block) does ring 0, packs the survivors into full warps and
-// walks the first coarse rings; what is still open goes to a work list; the FAR kernel runs twice over the (shrinking)
-// list, 32 consecutive entries per warp, pulled with an atomic cursor.  Inside a warp the expensive, rare tile tests are
-// pooled (hier_rings_warp).  `d as u8` (depth_image.rs:120-121) and the per-pair maximum (:124) leave with the result.
+// split: the NEAR kernel does ring 0 for four patches of main pixels (or slices of the block list), queues the survivors
+// in shared memory and walks them 256 at a time through the first coarse rings (full warps, no warp retires early); what
+// is still open goes to a work list; the FAR kernel runs twice over the (shrinking) list, 32 consecutive entries per
+// warp, pulled with an atomic cursor.  Inside a warp the expensive, rare tile tests are pooled (hier_rings_warp): lanes
+// list their flagged tiles as tasks (one shared-memory atomic per lane, tiles out of reach of the best ring so far dropped
+// by one bit-range mask per side), the 32 lanes take 32 tasks at a time.  Rings <= 15 have sides of at most 31 tiles and
+// use 32-bit flags; longer sides are walked per lane, window by window.  `d as u8` (depth_image.rs:120-121) and the
+// per-pair maximum (:124) leave with the result.
 // hier_rings() is the same walk for ONE query without the pooling: tests/host_emul compiles it for the host.
 #pragma once
 #include <algorithm>
