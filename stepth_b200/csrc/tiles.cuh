@@ -122,12 +122,17 @@ __device__ __forceinline__ uint32_t warp_bit_transpose(uint32_t x, int lane) {
         y = __shfl_xor_sync(0xffffffffu, x, 8);
         x = __byte_perm(x, y, (lane & 8) ? 0x3715u : 0x6240u);    // hi: bytes {y1, x1, y3, x3}      lo: bytes {x0, y0, x2, y2}
     }
+    // 4-, 2-, 1-bit steps: a lane keeps the half of every 2d-bit group that stays (mask km), sends the other half already
+    // moved to where the partner wants it (a rotate: the bits that would wrap are zero after masking) and ORs in what comes
 #pragma unroll
     for (int s = 2; s < 5; ++s) {
         const int d = 16 >> s;
-        const uint32_t m = d == 16 ? 0x0000ffffu : d == 8 ? 0x00ff00ffu : d == 4 ? 0x0f0f0f0fu : d == 2 ? 0x33333333u : 0x55555555u;
-        const uint32_t y = __shfl_xor_sync(0xffffffffu, x, d);
-        x = (lane & d) ? (((y >> d) & m) | (x & ~m)) : ((x & m) | ((y << d) & ~m));
+        const uint32_t m = d == 4 ? 0x0f0f0f0fu : d == 2 ? 0x33333333u : 0x55555555u;
+        const uint32_t km = (lane & d) ? ~m : m;             // lane-constant: hoisted out of the callers' loops
+        const int rot = (lane & d) ? d : 32 - d;             // upper lane sends its low halves up (<< d), lower lane its high halves down (>> d)
+        const uint32_t give = x & ~km;
+        const uint32_t y = __shfl_xor_sync(0xffffffffu, __funnelshift_l(give, give, rot), d);
+        x = (x & km) | y;
     }
     return x;
 }
