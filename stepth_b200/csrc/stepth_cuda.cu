@@ -82,6 +82,7 @@ extern "C" int32_t stepth_cuda_ctx_create(int32_t device, stepth_ctx **ctx_out) 
     if (const char *ev = getenv("STEPTH_BATCH_CHUNKS")) ctx->batch_chunks = atoi(ev);
     if (const char *ev = getenv("STEPTH_TWO_STREAMS")) ctx->two_streams = atoi(ev);
     if (const char *ev = getenv("STEPTH_FINISH_STREAMING")) ctx->finish_streaming = atoi(ev);
+    if (const char *ev = getenv("STEPTH_TRACE")) ctx->trace = atoi(ev);
     if (const char *ev = getenv("STEPTH_UPLOAD_FULL_ROWS")) ctx->upload_full_rows = atoi(ev);
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
         g_create_err = std::string("cudaStreamCreate failed: ") + cudaGetErrorString(e);
@@ -403,10 +404,17 @@ int32_t run_pairs(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_rgba, 
     const uint32_t n_chunks = (uint32_t)bounds.size() - 1;
     while (ctx->events.size() < 2 * (size_t)n_chunks + 2) {
         cudaEvent_t e;
-        STEPTH_CUDA_TRY(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        STEPTH_CUDA_TRY(ctx, cudaEventCreateWithFlags(&e, ctx->trace ? cudaEventDefault : cudaEventDisableTiming));
         ctx->events.push_back(e);
     }
     const bool piped = n_chunks > 1;
+    std::vector<cudaEvent_t> t_out;  // trace only: end of each chunk's copy-out
+    if (ctx->trace && piped)
+        for (uint32_t k = 0; k < n_chunks; ++k) {
+            cudaEvent_t e;
+            STEPTH_CUDA_TRY(ctx, cudaEventCreate(&e));
+            t_out.push_back(e);
+        }
     cudaStream_t s_in = piped ? ctx->copy_in : st, s_out = piped ? ctx->copy_out : st;
     // two alternating compute streams pay off for small chunks (their poorly filled last kernels overlap the next chunk's
     // first ones); a chunk that fills the GPU by itself only finishes later that way, and so does its copy-out (measured:
@@ -482,6 +490,7 @@ int32_t run_pairs(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_rgba, 
             if (want_apply && rgba_out[i])
                 STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(rgba_out[i], d_rgba + px * 4 * i, px * 4, cudaMemcpyDeviceToHost, s_out));
         }
+        if (!t_out.empty()) STEPTH_CUDA_TRY(ctx, cudaEventRecord(t_out[k], s_out));
     }
     ctx->slot = 0;
     st = st0;
@@ -495,6 +504,18 @@ int32_t run_pairs(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_rgba, 
     if (piped) {
         STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(s_in));
         STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(s_out));
+    }
+    if (!t_out.empty()) {
+        fprintf(stderr, "stepth trace: %u pairs in %u chunks%s (ms after the start: copy-in, compute, copy-out)\n", n, n_chunks,
+                two ? ", two compute streams" : "");
+        for (uint32_t k = 0; k < n_chunks; ++k) {
+            float a = 0, b = 0, c = 0;
+            cudaEventElapsedTime(&a, ctx->events[2 * n_chunks], ctx->events[2 * k]);
+            cudaEventElapsedTime(&b, ctx->events[2 * n_chunks], ctx->events[2 * k + 1]);
+            cudaEventElapsedTime(&c, ctx->events[2 * n_chunks], t_out[k]);
+            fprintf(stderr, "  chunk %u [%u,%u): %.3f %.3f %.3f\n", k, bounds[k], bounds[k + 1], a, b, c);
+            cudaEventDestroy(t_out[k]);
+        }
     }
 
     int32_t first_bad = STEPTH_OK;
