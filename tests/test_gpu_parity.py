@@ -64,6 +64,49 @@ def test_search_dense_ragged_shapes(ctx, orc, w, h, wa, ha):
         assert np.array_equal(gpu_raw(ctx, m, a, prec, 255), ref), (w, h, wa, ha, prec)
 
 
+@pytest.mark.parametrize("seed", range(40))
+def test_search_seeded_random_cases(ctx, orc, seed):
+    """Shapes, additional-image shapes, colour depth, per-channel precision and ring limit all drawn from a seed."""
+    rng = np.random.default_rng(1000 + seed)
+    w, h = int(rng.integers(1, 280)), int(rng.integers(1, 200))
+    if rng.random() < 0.5:
+        wa, ha = w, h
+    else:
+        wa, ha = int(rng.integers(1, 320)), int(rng.integers(1, 240))
+    levels = int(rng.choice([3, 6, 16, 64, 256, 256]))
+    prec = [int(rng.choice([1, 2, 4, 9, 20, 36, 70, 128, 255])) for _ in range(3)]
+    if seed % 13 == 0:
+        prec[seed % 3] = 0   # nothing matches: every query runs out of rings
+    rings = int(rng.choice([1, 2, 5, 6, 7, 10, 11, 15, 16, 17, 33, 64, 128, 255, 300]))
+    m, a = rand_pair(w, h, wa, ha, seed=seed, levels=levels)
+    ref = orc.search_dense(m, a, prec, rings, threads=4)
+    assert np.array_equal(gpu_raw(ctx, m, a, prec, rings), ref), (w, h, wa, ha, levels, prec, rings)
+
+
+@pytest.mark.parametrize("env", [
+    {"STEPTH_NEAR_RINGS": "1", "STEPTH_MID_RINGS": "2"},
+    {"STEPTH_NEAR_RINGS": "3", "STEPTH_MID_RINGS": "3"},
+    {"STEPTH_NEAR_RINGS": "40", "STEPTH_MID_RINGS": "0"},
+    {"STEPTH_NEAR_COMPACT": "0"},
+    {"STEPTH_BATCH_CHUNKS": "3", "STEPTH_TWO_STREAMS": "0", "STEPTH_TRACE": "1"},
+    {"STEPTH_BATCH_CHUNKS": "16", "STEPTH_UPLOAD_FULL_ROWS": "1", "STEPTH_FINISH_STREAMING": "0"},
+])
+def test_tuning_knobs_do_not_change_results(orc, env, monkeypatch):
+    """The stage boundaries, compaction, chunking and upload knobs are schedule only: same bytes out."""
+    import stepth_b200 as sb
+
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    c = sb.Context(0)
+    n, w, h = 5, 232, 120
+    pairs = [synth_pair("nat" if i % 2 else "geo", w, h, seed=70 + i) for i in range(n)]
+    got = c.depth_dense_batch([p[0] for p in pairs], [p[1] for p in pairs], P36, 128, sb.RESAMPLE_U8)
+    for i, (m, a) in enumerate(pairs):
+        want = orc.depth_dense(m, a, P36, 128, resample=orc.RESAMPLE_U8, threads=4)
+        assert got["status"][i] == 0
+        assert np.array_equal(got["depth"][i], want), (env, i)
+
+
 @pytest.mark.parametrize("w,h,rings,rho", [(200, 120, 64, 0.0), (272, 96, 128, 0.002), (130, 130, 255, 0.0005)])
 def test_search_every_tile_flagged(ctx, orc, w, h, rings, rho):
     """Adversarial for the tile search: every pixel of the additional image matches the query colour in exactly two
