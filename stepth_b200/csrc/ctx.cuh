@@ -139,4 +139,17 @@ inline int32_t get_taps(stepth_ctx *ctx, cudaStream_t st, uint32_t n, const TapR
     return STEPTH_OK;
 }
 
+// FinishArgs::wx_edge for a row of n >= 8 samples (the table is already cached by get_taps)
+inline void edge_taps(stepth_ctx *ctx, uint32_t n, float (*edge)[7]) {
+    const std::vector<TapRow> &t = ctx->taps.find(n)->second.host;
+    for (int e = 0; e < 6; ++e) {
+        const long long i = e < 3 ? e : (long long)n - 6 + e;   // the output column
+        const TapRow &r = t[(size_t)i];
+        for (int k = 0; k < 7; ++k) {
+            const long long col = i - 3 + k, idx = col - r.left;
+            edge[e][k] = (col >= 0 && col < (long long)n && idx >= 0 && idx < r.cnt) ? r.w[idx] : 0.0f;
+        }
+    }
+}
+
 }  // namespace stepth

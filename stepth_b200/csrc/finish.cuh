@@ -40,6 +40,10 @@ struct FinishArgs {
     uint32_t mode;           // STEPTH_RESAMPLE_*
     uint32_t invert;
     float wy_int[7], wx_int[7];  // the taps of an interior index of each axis (all interior indices share them)
+    // the taps of the three first and three last columns laid on the interior's 7-column footprint (columns i - 3 ..
+    // i + 3), 0 where the footprint leaves the row: 0.0 + 0 * 0 and t + 0 * 0 change nothing, so summing all seven in
+    // order gives the bits of the clipped sum (rows of 8 or more columns; filled by stepth_cuda_dev_finish)
+    float wx_edge[6][7];
 };
 
 // clamp(t, 0.0, 255.0) then f32::round (half away from zero), as NumCast::from(FloatNearest(t)) does
@@ -327,13 +331,14 @@ __global__ void __launch_bounds__(256) finish_horz_kernel(FinishArgs a, const ui
         if (row >= (int)a.out_rows || x0 >= w) continue;
         const uint8_t *trow = tplane + (size_t)row * w;
         uint32_t o[2] = {0u, 0u};
-        if (x0 >= 4 && x0 + 12 <= w) {
-            // columns x0 - 4 .. x0 + 11 as four words; output j reads columns x0 + j - 3 .. x0 + j + 3
+        {
+            // columns x0 - 4 .. x0 + 11 as four words (0 for a word off the row); output j reads columns x0 + j - 3 .. x0 + j + 3
             const uint32_t *tw = reinterpret_cast<const uint32_t *>(trow + x0 - 4);
             float b[16];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                const uint32_t px = __ldg(tw + k);
+                const int c0 = x0 - 4 + 4 * k;
+                const uint32_t px = (c0 >= 0 && c0 + 4 <= w) ? __ldg(tw + k) : 0u;
 #pragma unroll
                 for (int c = 0; c < 4; ++c)   // one byte permute builds the bits of 2^23 + byte
                     b[4 * k + c] = __fsub_rn(__uint_as_float(__byte_perm(px, 0x4b000000u, 0x7540u | c)), 8388608.0f);
@@ -345,19 +350,22 @@ __global__ void __launch_bounds__(256) finish_horz_kernel(FinishArgs a, const ui
                 for (int k = 0; k < 7; ++k) t = __fadd_rn(t, __fmul_rn(b[j + 1 + k], a.wx_int[k]));
                 o[j >> 2] |= round_u8(t) << (8 * (j & 3));
             }
-        } else {
-            for (int j = 0; j < 8; ++j) {
-                const int gx = x0 + j;
-                if (gx >= w) break;
-                float t = 0.0f;
-                if (gx >= 3 && gx + 4 <= w) {
-                    for (int k = 0; k < 7; ++k) t = __fadd_rn(t, __fmul_rn((float)trow[gx - 3 + k], a.wx_int[k]));
-                } else {
-                    const TapRow &tp = a.taps_x[gx];
-                    for (int k = 0; k < tp.cnt; ++k) t = __fadd_rn(t, __fmul_rn((float)trow[tp.left + k], tp.w[k]));
-                }
-                o[j >> 2] |= round_u8(t) << (8 * (j & 3));
+            // the first and the last thread of a row redo their three border outputs with the border's own weights
+#define STEPTH_EDGE_OUT(J, E)                                                                          \
+    {                                                                                                  \
+        float t = 0.0f;                                                                                \
+        _Pragma("unroll") for (int k = 0; k < 7; ++k) t = __fadd_rn(t, __fmul_rn(b[(J) + 1 + k], a.wx_edge[E][k])); \
+        o[(J) >> 2] = (o[(J) >> 2] & ~(0xffu << (8 * ((J)&3)))) | (round_u8(t) << (8 * ((J)&3)));     \
+    }
+            if (x0 == 0) {
+                STEPTH_EDGE_OUT(0, 0) STEPTH_EDGE_OUT(1, 1) STEPTH_EDGE_OUT(2, 2)
             }
+            if (x0 + 8 == w) {
+                STEPTH_EDGE_OUT(5, 3) STEPTH_EDGE_OUT(6, 4) STEPTH_EDGE_OUT(7, 5)
+            } else if (x0 + 4 == w) {
+                STEPTH_EDGE_OUT(1, 3) STEPTH_EDGE_OUT(2, 4) STEPTH_EDGE_OUT(3, 5)
+            }
+#undef STEPTH_EDGE_OUT
         }
         o[0] ^= inv;
         o[1] ^= inv;

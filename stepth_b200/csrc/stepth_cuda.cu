@@ -255,6 +255,7 @@ extern "C" int32_t stepth_cuda_dev_finish(stepth_ctx *ctx, void *stream, uint32_
         ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(depth_out)) & 3) == 0) {
         // the default mode on whole-word rows: two streaming kernels with a 1 B/px plane between them (finish.cuh)
         stepth_ctx::Buf &tmp = ctx->slot ? ctx->work2 : ctx->work;
+        edge_taps(ctx, w, a.wx_edge);
         int32_t rc = ensure(ctx, tmp, (size_t)n_pairs * out_rows * w);
         if (rc != STEPTH_OK) return rc;
         dim3 gv((w / 4 + 127) / 128, (out_rows + FV_ROWS - 1) / FV_ROWS, n_pairs);
