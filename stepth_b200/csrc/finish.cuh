@@ -248,7 +248,10 @@ __device__ __forceinline__ uint32_t round_u8(float t) {
     return (__float_as_uint(u) & 0x1ffu) + (d == 0.5f ? 1u : 0u);
 }
 
-constexpr int FV_ROWS = 21;  // output rows per thread of the vertical pass (27 row loads for 21 rows); a multiple of 7
+#ifndef STEPTH_FV_ROWS
+#define STEPTH_FV_ROWS 21
+#endif
+constexpr int FV_ROWS = STEPTH_FV_ROWS;  // output rows per thread of the vertical pass (27 row loads for 21 rows); a multiple of 7
 
 __global__ void __launch_bounds__(128) finish_vert_kernel(FinishArgs a, uint8_t *tmp) {
     const uint32_t pair = blockIdx.z;
@@ -264,13 +267,16 @@ __global__ void __launch_bounds__(128) finish_vert_kernel(FinishArgs a, uint8_t 
     const int gy0 = (int)a.out_y0 + r0, img_h = (int)a.img_h;
     const uint8_t *srcp = a.src + (size_t)pair * a.src_rows * a.w;
     uint32_t *dst = reinterpret_cast<uint32_t *>(tmp + (size_t)pair * a.out_rows * a.w) + (size_t)r0 * wq + xq;
-    if (gy0 >= 3 && gy0 + rows + 3 <= img_h) {
-        // every row of the segment has the seven interior taps: a seven-row window per column slides down in registers
-        const uint32_t *col = reinterpret_cast<const uint32_t *>(srcp) + (size_t)(gy0 - 3 - (int)a.src_y0) * wq + xq;
+    if (img_h >= 8) {
+        // a seven-row window per column slides down in registers.  Rows off the image enter as 0 and the three first / last
+        // output rows take their own weights laid on the seven-row footprint (0 where it leaves the image): 0.0 + 0 * 0 and
+        // t + 0 * 0 change nothing, so the seven-term sum in order has the bits of the clipped sum
+        const uint32_t *col = reinterpret_cast<const uint32_t *>(srcp) + ((ptrdiff_t)(gy0 - 3 - (int)a.src_y0) * wq + xq);
         float win[7][4];
 #pragma unroll
         for (int k = 0; k < 6; ++k) {
-            const uint32_t px = __ldg(col + (size_t)k * wq);
+            const int gr = gy0 - 3 + k;
+            const uint32_t px = (gr >= 0 && gr < img_h) ? __ldg(col + (ptrdiff_t)k * wq) : 0u;
 #pragma unroll
             for (int c = 0; c < 4; ++c) win[k][c] = norm((px >> (8 * c)) & 0xffu);
         }
@@ -281,23 +287,41 @@ __global__ void __launch_bounds__(128) finish_vert_kernel(FinishArgs a, uint8_t 
             for (int jj = 0; jj < 7; ++jj) {
                 const int j = j0 + jj;
                 if (j < rows) {
-                    const uint32_t px = __ldg(col + (size_t)(j + 6) * wq);
+                    const int gy = gy0 + j;
+                    const uint32_t px = gy + 3 < img_h ? __ldg(col + (ptrdiff_t)(j + 6) * wq) : 0u;
 #pragma unroll
                     for (int c = 0; c < 4; ++c) win[(jj + 6) % 7][c] = norm((px >> (8 * c)) & 0xffu);
                     uint32_t out = 0;
+                    if (gy >= 3 && gy + 4 <= img_h) {
 #pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        float t = 0.0f;
+                        for (int c = 0; c < 4; ++c) {
+                            float t = 0.0f;
 #pragma unroll
-                        for (int k = 0; k < 7; ++k) t = __fadd_rn(t, __fmul_rn(win[(jj + k) % 7][c], a.wy_int[k]));
-                        out |= round_u8(t) << (8 * c);
+                            for (int k = 0; k < 7; ++k) t = __fadd_rn(t, __fmul_rn(win[(jj + k) % 7][c], a.wy_int[k]));
+                            out |= round_u8(t) << (8 * c);
+                        }
+                    } else {   // a border row (the same for the whole warp)
+                        const TapRow &tp = a.taps_y[gy];
+                        float wk[7];
+#pragma unroll
+                        for (int k = 0; k < 7; ++k) {
+                            const int idx = gy - 3 + k - tp.left;
+                            wk[k] = (idx >= 0 && idx < tp.cnt) ? tp.w[idx] : 0.0f;
+                        }
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {
+                            float t = 0.0f;
+#pragma unroll
+                            for (int k = 0; k < 7; ++k) t = __fadd_rn(t, __fmul_rn(win[(jj + k) % 7][c], wk[k]));
+                            out |= round_u8(t) << (8 * c);
+                        }
                     }
                     dst[(size_t)j * wq] = out;
                 }
             }
         }
     } else {
-        // a border row in reach: per output through the host-built tap rows (rare: the first and last segments only)
+        // images of fewer than 8 rows: per output through the host-built tap rows
         for (int j = 0; j < rows; ++j) {
             const TapRow &tp = a.taps_y[gy0 + j];
             uint32_t out = 0;
