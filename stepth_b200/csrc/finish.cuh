@@ -44,6 +44,7 @@ struct FinishArgs {
     // i + 3), 0 where the footprint leaves the row: 0.0 + 0 * 0 and t + 0 * 0 change nothing, so summing all seven in
     // order gives the bits of the clipped sum (rows of 8 or more columns; filled by stepth_cuda_dev_finish)
     float wx_edge[6][7];
+    uint32_t seg_rows;       // output rows per thread of the vertical pass: FV_ROWS, or 7 for a launch that would leave SMs idle
 };
 
 // clamp(t, 0.0, 255.0) then f32::round (half away from zero), as NumCast::from(FloatNearest(t)) does
@@ -263,7 +264,7 @@ __global__ void __launch_bounds__(128) finish_vert_kernel(FinishArgs a, uint8_t 
     const NormDiv norm(mx);
     const int wq = (int)(a.w >> 2), xq = blockIdx.x * 128 + threadIdx.x;
     if (xq >= wq) return;
-    const int r0 = blockIdx.y * FV_ROWS, rows = min(FV_ROWS, (int)a.out_rows - r0);
+    const int seg = (int)a.seg_rows, r0 = blockIdx.y * seg, rows = min(seg, (int)a.out_rows - r0);
     const int gy0 = (int)a.out_y0 + r0, img_h = (int)a.img_h;
     const uint8_t *srcp = a.src + (size_t)pair * a.src_rows * a.w;
     uint32_t *dst = reinterpret_cast<uint32_t *>(tmp + (size_t)pair * a.out_rows * a.w) + (size_t)r0 * wq + xq;
@@ -282,7 +283,7 @@ __global__ void __launch_bounds__(128) finish_vert_kernel(FinishArgs a, uint8_t 
         }
         // the window index cycles with period 7: seven rows are unrolled (static register indices), the groups loop
 #pragma unroll 1
-        for (int j0 = 0; j0 < FV_ROWS; j0 += 7) {
+        for (int j0 = 0; j0 < seg; j0 += 7) {
 #pragma unroll
             for (int jj = 0; jj < 7; ++jj) {
                 const int j = j0 + jj;

@@ -258,7 +258,9 @@ extern "C" int32_t stepth_cuda_dev_finish(stepth_ctx *ctx, void *stream, uint32_
         edge_taps(ctx, w, a.wx_edge);
         int32_t rc = ensure(ctx, tmp, (size_t)n_pairs * out_rows * w);
         if (rc != STEPTH_OK) return rc;
-        dim3 gv((w / 4 + 127) / 128, (out_rows + FV_ROWS - 1) / FV_ROWS, n_pairs);
+        a.seg_rows = FV_ROWS;   // a small launch takes short segments: more threads, shorter dependent chains (one 1080p pair: 16 -> 9 us)
+        if ((uint64_t)((w / 4 + 127) / 128) * ((out_rows + FV_ROWS - 1) / FV_ROWS) * n_pairs < (uint64_t)ctx->sm_count * 9) a.seg_rows = 7;
+        dim3 gv((w / 4 + 127) / 128, (out_rows + a.seg_rows - 1) / a.seg_rows, n_pairs);
         dim3 gh((w + 255) / 256, (out_rows + 31) / 32, n_pairs);
         if (gv.y > 65535) return set_err(ctx, STEPTH_ERR_INVALID_ARG, "dev_finish: more than 1M rows in one band");
         finish_vert_kernel<<<gv, 128, 0, st>>>(a, (uint8_t *)tmp.p);
