@@ -34,6 +34,8 @@ struct stepth_ctx {
     Buf worklist;  // two [count, cursor, pad..][uint2 entries] lists: queries handed from the near to the far kernel(s)
     int near_rings = 6;  // coarse rings the near kernel walks (STEPTH_NEAR_RINGS)
     int batch_chunks = 8;  // the batch entry point pipelines this many chunks of pairs over its three streams (STEPTH_BATCH_CHUNKS)
+    cudaEvent_t main_ready = nullptr;  // set by the batch entry point: the dense search waits for it between K0 and K1 (the
+                                       // main images are still on their way up while the planes of the additional ones are built)
     int trace = 0;  // STEPTH_TRACE=1: the batch entry point prints each chunk's copy-in / compute / copy-out end times to stderr
     int upload_full_rows = 0;  // host-buffer entry points upload whole rows of the additional image (STEPTH_UPLOAD_FULL_ROWS)
     int near_compact = 1;  // the near kernel packs the queries that survive ring 0 into full warps (STEPTH_NEAR_COMPACT)

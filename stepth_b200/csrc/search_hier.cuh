@@ -695,6 +695,11 @@ inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const Search
     coarse_transpose_kernel<<<dim3(h.g.nxw, h.g.nyw, n_pairs * CT_PARTS), 256, 0, st>>>(p);
     ctx->launches++;
     STEPTH_CUDA_TRY(ctx, cudaGetLastError());
+    if (ctx->main_ready) {   // K0 needed the additional images only; the queries come from the main ones
+        cudaEvent_t ev = ctx->main_ready;
+        ctx->main_ready = nullptr;
+        STEPTH_CUDA_TRY(ctx, cudaStreamWaitEvent(st, ev, 0));
+    }
 
     // work lists: [count, cursor, pad ..][entries]; at most one entry per query
     const size_t cap = (size_t)a.n_queries * n_pairs;

@@ -159,6 +159,12 @@ extern "C" int32_t stepth_cuda_dev_search_dense(stepth_ctx *ctx, void *stream, c
         (uint64_t)s->w * s->h > 0xffffffffull || ((uintptr_t)main_rgba & 3))
         return set_err(ctx, STEPTH_ERR_INVALID_ARG, "dev_search_dense: bad shape or unaligned RGBA plane");
     cudaStream_t st = (cudaStream_t)stream;
+    const bool hier = !(params->flags & STEPTH_FLAG_LITERAL_SEARCH) && params->precision[0] && params->precision[1] && params->precision[2];
+    if (ctx->main_ready && !hier) {   // only the tile search has work to do before it needs the main images
+        cudaEvent_t ev = ctx->main_ready;
+        ctx->main_ready = nullptr;
+        STEPTH_CUDA_TRY(ctx, cudaStreamWaitEvent(st, ev, 0));
+    }
     STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(max_out, 0, sizeof(uint32_t) * s->n_pairs, st));
     if (params->precision[0] == 0 || params->precision[1] == 0 || params->precision[2] == 0) {
         // `x < 0` is false for every u8: nothing ever matches, every distance is None -> 0   (helpers.rs:35)
@@ -180,7 +186,12 @@ extern "C" int32_t stepth_cuda_dev_search_dense(stepth_ctx *ctx, void *stream, c
         LAUNCH_CHECK(ctx);
         return STEPTH_OK;
     }
-    return launch_search_hier(ctx, st, a, s->n_pairs);
+    const int32_t rc = launch_search_hier(ctx, st, a, s->n_pairs);
+    if (ctx->main_ready) {   // an error before K1: the wait is still owed to the caller's stream
+        cudaStreamWaitEvent(st, ctx->main_ready, 0);
+        ctx->main_ready = nullptr;
+    }
+    return rc;
 }
 
 extern "C" int32_t stepth_cuda_dev_search_blocks(stepth_ctx *ctx, void *stream, const stepth_params *params,
@@ -405,12 +416,15 @@ int32_t run_pairs(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_rgba, 
     if (chunk >= 2 && chunk < n) bounds.push_back(chunk / 2);
     while (bounds.back() < n) bounds.push_back(std::min(n, bounds.back() + chunk));
     const uint32_t n_chunks = (uint32_t)bounds.size() - 1;
-    while (ctx->events.size() < 2 * (size_t)n_chunks + 2) {
+    while (ctx->events.size() < 3 * (size_t)n_chunks + 2) {
         cudaEvent_t e;
         STEPTH_CUDA_TRY(ctx, cudaEventCreateWithFlags(&e, ctx->trace ? cudaEventDefault : cudaEventDisableTiming));
         ctx->events.push_back(e);
     }
-    const bool piped = n_chunks > 1;
+    // dense pairs always go through the copy streams: the additional images go up first and K0 runs on them while the main
+    // images follow (`split`)
+    const bool split = !blocks;
+    const bool piped = n_chunks > 1 || split;
     std::vector<cudaEvent_t> t_out;  // trace only: end of each chunk's copy-out
     if (ctx->trace && piped)
         for (uint32_t k = 0; k < n_chunks; ++k) {
@@ -422,7 +436,7 @@ int32_t run_pairs(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_rgba, 
     // two alternating compute streams pay off for small chunks (their poorly filled last kernels overlap the next chunk's
     // first ones); a chunk that fills the GPU by itself only finishes later that way, and so does its copy-out (measured:
     // 1080p pairs 4.31 -> 4.03 ms per 16, one 4K pair per chunk 5.54 -> 5.92 ms per 4)
-    const bool two = piped && ctx->two_streams && ctx->stream2 && (uint64_t)chunk * px <= 6000000ull;
+    const bool two = n_chunks > 1 && ctx->two_streams && ctx->stream2 && (uint64_t)chunk * px <= 6000000ull;
     cudaStream_t st0 = st;
     if (piped) {  // the copy streams must not overtake the memset / earlier work on the compute stream
         STEPTH_CUDA_TRY(ctx, cudaEventRecord(ctx->events[2 * n_chunks], st));
@@ -437,18 +451,25 @@ int32_t run_pairs(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_rgba, 
         ctx->slot = two ? (int)(k & 1) : 0;   // chunks alternate between two compute streams, each with its own scratch
         st = ctx->slot ? ctx->stream2 : st0;
         for (uint32_t i = i0; i < i1; ++i) {
-            const uint8_t *rgba_src = blocks ? (want_apply ? rgba_in[i] : nullptr) : main_rgba[i];
-            if (rgba_src)
-                STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(d_main + px * 4 * i, rgba_src, px * 4, cudaMemcpyHostToDevice, s_in));
             if (wa_d == wa)
                 STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(d_add + add_bytes * i, add_rgb[i], add_bytes, cudaMemcpyHostToDevice, s_in));
             else
                 STEPTH_CUDA_TRY(ctx, cudaMemcpy2DAsync(d_add + add_bytes * i, (size_t)wa_d * 3, add_rgb[i], (size_t)wa * 3,
                                                        (size_t)wa_d * 3, ha_d, cudaMemcpyHostToDevice, s_in));
         }
+        if (split) {   // the compute stream may start K0 now; K1 waits for the second event (ctx->main_ready)
+            STEPTH_CUDA_TRY(ctx, cudaEventRecord(ctx->events[2 * n_chunks + 2 + k], s_in));
+            STEPTH_CUDA_TRY(ctx, cudaStreamWaitEvent(st, ctx->events[2 * n_chunks + 2 + k], 0));
+        }
+        for (uint32_t i = i0; i < i1; ++i) {
+            const uint8_t *rgba_src = blocks ? (want_apply ? rgba_in[i] : nullptr) : main_rgba[i];
+            if (rgba_src)
+                STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(d_main + px * 4 * i, rgba_src, px * 4, cudaMemcpyHostToDevice, s_in));
+        }
         if (piped) {
             STEPTH_CUDA_TRY(ctx, cudaEventRecord(ctx->events[2 * k], s_in));
-            STEPTH_CUDA_TRY(ctx, cudaStreamWaitEvent(st, ctx->events[2 * k], 0));
+            if (split) ctx->main_ready = ctx->events[2 * k];
+            else STEPTH_CUDA_TRY(ctx, cudaStreamWaitEvent(st, ctx->events[2 * k], 0));
         }
         uint32_t *c_max = sm.max(ctx->small.p) + i0, *c_hist = sm.hist(ctx->small.p) + 256 * (size_t)i0;
         int32_t *c_status = sm.status(ctx->small.p) + i0;
@@ -496,6 +517,7 @@ int32_t run_pairs(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_rgba, 
         if (!t_out.empty()) STEPTH_CUDA_TRY(ctx, cudaEventRecord(t_out[k], s_out));
     }
     ctx->slot = 0;
+    ctx->main_ready = nullptr;
     st = st0;
     if (two) {  // the small state of the odd chunks is written on stream2
         STEPTH_CUDA_TRY(ctx, cudaEventRecord(ctx->events[2 * n_chunks + 1], ctx->stream2));
