@@ -480,6 +480,27 @@ def test_full_size_production_equals_in_order_kernel(ctx, orc, kind, w, h, rings
     assert torch.equal(pipe.rgba_out, m[None] * keep.unsqueeze(-1))
 
 
+@pytest.mark.parametrize("n,kind", [(1, "nat"), (2, "geo"), (4, "nat"), (8, "nat"), (8, "geo")])
+def test_launch_shapes_of_every_batch_size(ctx, orc, n, kind):
+    """The search picks patches per CTA (1, 2, 4) and one or two far stages by the size of the launch: every choice
+    against the in-order kernel on the same 1080p pairs, and sampled against the oracle."""
+    import stepth_b200 as sb
+    from stepth_b200 import device, synth
+
+    w, h, rings = 1920, 1080, 128
+    pairs = [synth.make_pair(kind, w, h, 20 + i, device="cuda") for i in range(n)]
+    m = torch.stack([p[0] for p in pairs])
+    a = torch.stack([p[1] for p in pairs])
+    d8, mx = device.search_dense(ctx, m, a, P36, rings)
+    d8_lit, mx_lit = device.search_dense(ctx, m, a, P36, rings, flags=sb.FLAG_LITERAL_SEARCH)
+    assert torch.equal(d8, d8_lit) and torch.equal(mx, mx_lit)
+    rng = np.random.default_rng(n)
+    idx = rng.choice(w * h, 1500, replace=False).astype(np.uint32)
+    i = n - 1
+    sub, _ = orc.search_dense_subset(m[i].cpu().numpy(), a[i].cpu().numpy(), P36, idx, rings, threads=8)
+    assert np.array_equal(d8[i].reshape(-1).cpu().numpy()[idx], sub)
+
+
 def test_full_size_worst_case_sampled(ctx, orc):
     from stepth_b200 import device, synth
 
