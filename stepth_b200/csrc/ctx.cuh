@@ -39,7 +39,7 @@ struct stepth_ctx {
     int trace = 0;  // STEPTH_TRACE=1: the batch entry point prints each chunk's copy-in / compute / copy-out end times to stderr
     int upload_full_rows = 0;  // host-buffer entry points upload whole rows of the additional image (STEPTH_UPLOAD_FULL_ROWS)
     int near_compact = 1;  // the near kernel packs the queries that survive ring 0 into full warps (STEPTH_NEAR_COMPACT)
-    int mid_rings = 10;  // first far kernel walks coarse rings [near_rings, mid_rings); 0 = one far kernel (STEPTH_MID_RINGS)
+    int mid_rings = 0;   // > near_rings: a second resumption point (FAR-1 walks rings [near_rings, mid_rings)); 0 = the far stage runs once (STEPTH_MID_RINGS)
     Buf planes2, worklist2, work2;  // scratch set of slot 1 (work / work2: the plane between the two streaming finish passes)
     int finish_streaming = 1;       // STEPTH_FINISH_STREAMING: 0 = always the tiled finish kernel
     int two_streams = 1;     // STEPTH_TWO_STREAMS

@@ -741,9 +741,9 @@ inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const Search
     STEPTH_CUDA_TRY(ctx, cudaGetLastError());
 
     // FAR: one or two resumptions; the last one walks to the end
-    // a small launch resumes once, not twice: its far stages are bound by their longest walks, not by throughput
-    // (one 1080p pair 0.260 -> 0.241 ms, two 0.420 -> 0.403 ms, four 0.726 -> 0.715 ms)
-    const int mid = per_sm >= 320 ? ctx->mid_rings : 0;
+    // one resumption by default: with the pooled tile tests a second stage boundary no longer pays (16 pairs 1080p: nat 2.318 ->
+    // 2.308 ms, worst case 6.59 -> 6.00 ms; one pair 0.260 -> 0.241 ms); STEPTH_MID_RINGS brings it back
+    const int mid = ctx->mid_rings;
     const uint32_t far_grid = (uint32_t)ctx->sm_count * 16;
     uint8_t *in = wl0, *out = wl1;
     if (mid > h.S1) {
