@@ -9,6 +9,6 @@ timeout 600 python bench.py --workload 4k_fused --steps 5 --warmup 3 --no-cpu-ba
 timeout 600 python bench.py --workload batch4k --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/bench_batch4k_n1.json 2> gpurun_out/benchb4k.err; echo "batch4k rc=$?"; tail -3 gpurun_out/benchb4k.err
 timeout 600 python bench.py --workload giant --steps 3 --warmup 3 > gpurun_out/bench_giant_n1.json 2> gpurun_out/benchg.err; echo "giant rc=$?"; tail -3 gpurun_out/benchg.err
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"search_|tile_planes|coarse_transpose|finish_|mask_apply|depth_split" -c 60 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/ncu_launch.log 2>&1; echo "ncu launches rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:"search_|tile_planes|coarse_transpose|finish_" -c 7 -f -o gpurun_out/hier_full python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"search_|tile_planes|coarse_transpose|finish_" -c 6 -f -o gpurun_out/hier_full python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?"
 STEPTH_TRACE=1 timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/bench_trace.json 2> gpurun_out/trace.err; echo "trace rc=$?"; tail -12 gpurun_out/trace.err
 timeout 300 python bench.py --pairs 1 --steps 30 --warmup 5 --no-cpu-baseline > gpurun_out/bench_1080p_one_pair.json 2> gpurun_out/b1.err; echo "one pair rc=$?"
