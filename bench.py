@@ -1,24 +1,31 @@
 #!/usr/bin/env python
 """bench.py -- Mpx*disparities/s of the depth-from-additional hot path (BASELINE.json's metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--kind nat|geo|worst] [--pairs B]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME] [--kind nat|geo|worst]
 
-One "step" = one pass of the hot path (ring search -> normalise -> unit-scale Gaussian -> Luma8 depth,
-depth_image.rs:110-134) over one batch of B synthetic stereo pairs of BASELINE.json's configs[1] shape
-(1920x1080 RGB pair, max_rings = 128, precision [36;3]); the batch is larger than L2 (B = 16 -> 232 MB of inputs).
-Pairs are independent, so N ranks each process their own B pairs with no data-path collective ("scaling": "weak").
+One "step" = one pass of the hot path (ring search -> normalise -> unit-scale Gaussian -> Luma8 depth [-> invert ->
+select_foreground -> apply_mask], depth_image.rs:110-134,220-245, mask_image.rs:205-213) over one batch of synthetic
+stereo pairs.  The DEFAULT workload is BASELINE.json configs[3], the configuration the north-star's scaling target is
+stated on: 64 pairs of 3840x2160, 256 rings, fused tail, dealt to the N ranks ("scaling": "strong").  The line also
+carries `other_workloads`: configs[0] (the README pair, block mode and dense), configs[1] (1080p / 128 rings),
+configs[2] (4K fused, 4 pairs) and configs[4] (one 16384x8192 pair in row bands), each with its own ms_per_step, e2e,
+roofline, cpu_baseline and parity.
 
-  value      W*H*D * B * N * K / t, inputs resident in HBM, device-timed (CUDA events, max over ranks)
-  e2e        the same metric through the reference-facing C ABI call `stepth_cuda_depth_dense_batch` with HOST
-             (pinned) buffers: host->device copies of every input and device->host copies of every depth map inside
-             the timed region
-  roofline   the dominant kernel (the ring search): algorithmic bytes per launch / its mean launch duration, measured
-             with CUDA events inside the timed region, against MEASURED_PEAKS.json's copy bandwidth
-  cpu_baseline  the CPU oracle (a C port of the reference path; the reference is Rust and cannot be built here) timed
-             on this box's cores on a bounded sample of the same workload (rank 0, N = 1 only)
+  value      W*H*D * pairs * K / t, inputs resident in HBM, device-timed (CUDA events, max over ranks)
+  e2e        the same metric through the reference-facing C ABI call with HOST buffers (pinned): host->device copies of
+             every input and device->host copies of every result inside the timed region; `e2e.pageable` = the same
+             call with ordinary (pageable) host memory, what a Rust Vec<u8> is
+  roofline   the dominant kernel stage (the ring search): algorithmic bytes per launch / its mean launch duration,
+             measured with CUDA events inside the timed region, against MEASURED_PEAKS.json's copy bandwidth; `issue` =
+             the instruction-issue ceiling that actually binds it (from the committed ncu capture); `int` = SURVEY 8(d)'s
+             integer half, probes counted on the device over the pairs that were timed
+  parity     after the timed region: sampled queries + whole finished planes of the results that were just timed,
+             against the CPU oracle (a port of the reference; upstream parity unpinned).  A
+             mismatch makes the run exit non-zero.
+  cpu_baseline  the CPU oracle timed on this box's cores on a bounded sample of the same workload (rank 0, N = 1 only)
 
-`--impl reference` times that CPU port alone (reference-faithful threading: the reference splits the query list in
-len/8-sized chunks -> 8-9 rayon tasks, depth_image.rs:111-112) and prints the same JSON line with "impl": "reference".
+`--impl reference` times that CPU port alone with the reference's own threading (len/8-sized chunks -> 8-9 rayon tasks,
+depth_image.rs:111-112) on a bounded sample per step and prints the same JSON line with "impl": "reference".
 """
 from __future__ import annotations
 
@@ -33,18 +40,21 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-W, H, D = 1920, 1080, 128          # BASELINE.json configs[1] (set per workload in main())
 PRECISION = [36, 36, 36]           # u8::MAX / 7 (Readme.md:15)
 METRIC = "Mpx*disparities/sec"
-FUSED = False                      # invert_depth + select_foreground + apply_mask fused into the step (configs[2..])
+SUB = 16                           # most pairs per launch sequence (bounds the scratch in HBM)
 
-# name -> (w, h, max_rings, pairs per step [per GPU | total], fused tail, scaling)
+# name -> shape of the workload.  pairs: per GPU when scaling == "weak", in total when "strong"
 WORKLOADS = {
-    "1080p": (1920, 1080, 128, 16, False, "weak"),        # configs[1]: the metric's configuration (default)
-    "4k_fused": (3840, 2160, 256, 4, True, "weak"),       # configs[2]
-    "batch4k": (3840, 2160, 256, 64, True, "strong"),     # configs[3]: 64 pairs in total, dealt to the ranks
-    "giant": (16384, 8192, 256, 1, False, "strong"),      # configs[4]: one pair, row-banded over the ranks
+    "batch4k": dict(w=3840, h=2160, d=256, pairs=64, fused=True, scaling="strong", mode="dense", data="synthetic"),   # configs[3]
+    "1080p": dict(w=1920, h=1080, d=128, pairs=16, fused=False, scaling="weak", mode="dense", data="synthetic"),     # configs[1]
+    "4k_fused": dict(w=3840, h=2160, d=256, pairs=4, fused=True, scaling="weak", mode="dense", data="synthetic"),    # configs[2]
+    "giant": dict(w=16384, h=8192, d=256, pairs=1, fused=False, scaling="strong", mode="bands", data="synthetic"),   # configs[4]
+    "readme_dense": dict(w=600, h=400, d=255, pairs=1, fused=False, scaling="weak", mode="dense", data="assets"),    # configs[0]
+    "readme_blocks": dict(w=600, h=400, d=255, pairs=1, fused=False, scaling="weak", mode="blocks", data="assets"),  # configs[0]
 }
+DEFAULT_WORKLOAD = "batch4k"
+OTHER_WORKLOADS = ["readme_blocks", "readme_dense", "1080p", "4k_fused", "giant"]
 
 
 def parse_args():
@@ -54,10 +64,12 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--kind", default="nat", choices=["nat", "geo", "worst"])
-    ap.add_argument("--workload", default="1080p", choices=sorted(WORKLOADS))
-    ap.add_argument("--pairs", type=int, default=0, help="pairs per step per GPU (default: the workload's)")
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--pairs", type=int, default=0, help="pairs per step (default: the workload's)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-others", action="store_true", help="only the named workload, no other_workloads")
     ap.add_argument("--extra-kinds", action="store_true", help="also time the geo and worst distributions (N=1)")
     return ap.parse_args()
 
@@ -80,21 +92,40 @@ def search_alg_bytes(w, h, d, pairs):
     return pairs * (4 * w * h + 3 * rw * rh + w * h)   # main RGBA read + reachable additional RGB read + d8 write
 
 
-def ncu_traffic(workload, kind):
-    """dram bytes (read + write) of the search-stage kernels per launch sequence, from the committed ncu capture"""
+def ncu_profile(workload, kind):
+    """what the committed `ncu --set full` capture of this workload's search stage says (profiles/traffic.json):
+    {"traffic": dram bytes read + written per launch sequence, "issue": {...}} or None"""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(p):
         with open(p) as f:
-            return json.load(f).get(f"{workload}_{kind}")
+            v = json.load(f).get(f"{workload}_{kind}")
+        if isinstance(v, (int, float)):
+            return {"traffic": int(v)}
+        return v
     return None
 
 
-class ClockSampler(threading.Thread):
-    """samples SM clock + throttle reasons of one GPU through NVML while the timed region runs"""
+def bind_to_gpu_numa(index: int):
+    """pins this process to the CPUs next to its GPU (NVML's ideal affinity) so that pinned host buffers and the threads that
+    fill them sit on the GPU's NUMA node; returns the number of CPUs in the set (None when NVML cannot say)"""
+    try:
+        import pynvml
 
-    def __init__(self, index: int):
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return None
+
+
+class ClockSampler(threading.Thread):
+    """samples SM clock + throttle reasons of one GPU through NVML while the timed regions run"""
+
+    def __init__(self, index: int, period_s: float = 0.004):
         super().__init__(daemon=True)
         self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self.period = period_s
         self._stop_evt = threading.Event()
         try:
             import pynvml
@@ -126,7 +157,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._stop_evt.wait(0.004)
+            self._stop_evt.wait(self.period)
 
     def stop(self):
         self._stop_evt.set()
@@ -139,71 +170,164 @@ class ClockSampler(threading.Thread):
 # ---------------------------------------------------------------------------------------------------------------
 # CPU arm: the oracle port of the reference path, timed on this box's cores (never the product path)
 # ---------------------------------------------------------------------------------------------------------------
-def cpu_pass(oracle, m, a, threads):
-    """one whole reference pass (depth_image.rs:96-136) over one pair on the CPU"""
-    return oracle.depth_dense(m, a, PRECISION, D, resample=oracle.RESAMPLE_U8, threads=threads)
+def load_assets():
+    """the reference's README pair as decoded pixels (tests/golden/assets.npz, made by tests/golden/make_golden.py)"""
+    import numpy as np
+
+    g = np.load(os.path.join(ROOT, "tests", "golden", "assets.npz"))
+    main, add = g["main"], g["additional"]
+    rgba = np.ascontiguousarray(np.concatenate([main, np.full(main.shape[:2] + (1,), 255, np.uint8)], axis=-1))
+    return rgba, np.ascontiguousarray(add)
 
 
-def cpu_baseline(kind: str, budget_s: float = 20.0):
-    """bounded sample: whole pairs of the bench workload, as many as fit ~budget_s (at least one)"""
-    from oracle import oracle
+def host_pair(wl, kind, seed):
+    """one pair of the workload as numpy arrays, generated on the CPU (the reference arm must not need a GPU)"""
+    if wl["data"] == "assets":
+        return load_assets()
     from stepth_b200 import synth
+
+    m, a = synth.make_pair(kind, wl["w"], wl["h"], seed=seed)
+    return m.numpy(), a.numpy()
+
+
+def cpu_pass_rows(oracle, wl, m, a, y0, rows, threads, blocks=None):
+    """the reference pass (depth_image.rs:96-136 [+ tail]) on the CPU over main rows [y0, y0+rows) of one pair; the whole
+    pair when rows >= h.  Returns the rows processed.  threads = 0: the reference's own len/8-sized chunks (8-9 tasks)."""
+    import numpy as np
+
+    w, h, d = wl["w"], wl["h"], wl["d"]
+    if blocks is not None:
+        oracle.depth_from_blocks(a, blocks, PRECISION, w, h, d, resample=oracle.RESAMPLE_U8, threads=threads)
+        return h
+    if rows >= h:
+        depth = oracle.depth_dense(m, a, PRECISION, d, resample=oracle.RESAMPLE_U8, threads=threads)
+    else:
+        idx = np.arange(y0 * w, (y0 + rows) * w, dtype=np.uint32)
+        sub, _ = oracle.search_dense_subset(m, a, PRECISION, idx, d, threads=threads)
+        try:
+            norm, _ = oracle.normalise(sub.reshape(rows, w))
+        except oracle.OracleError:      # a band whose distances are all 0: the whole image would still normalise
+            norm = sub.reshape(rows, w)
+        depth = oracle.gaussian_resample_unit(norm, oracle.RESAMPLE_U8)
+    if wl["fused"]:
+        depth = oracle.invert_depth(depth)
+        try:
+            mask, _ = oracle.select_foreground(depth)
+            oracle.apply_mask(m[y0:y0 + depth.shape[0]], mask)
+        except oracle.OracleError:
+            pass
+    return min(rows, h)
+
+
+def cpu_calibrate(oracle, wl, m, a, threads, target_s):
+    """rows of one pair the CPU port gets through in about target_s (a multiple of 8, at most the whole pair)"""
+    h = wl["h"]
+    probe = min(h, 16)
+    t0 = time.perf_counter()
+    cpu_pass_rows(oracle, wl, m, a, (h // 2) // 8 * 8, probe, threads)
+    dt = max(time.perf_counter() - t0, 1e-4)
+    rows = int(probe * target_s / dt) // 8 * 8
+    return h if rows >= h else max(8, rows)
+
+
+def cpu_baseline(wl, name, kind, pair=None, budget_s=12.0):
+    """bounded sample of the workload on all host cores: whole pairs when one fits the budget, else a row band"""
+    from oracle import oracle
 
     cores = os.cpu_count() or 1
-    threads = cores                      # all-cores variant (one chunk per hardware thread)
-    done, t_total = 0, 0.0
-    while done < 4 and t_total < budget_s:
-        m, a = synth.make_pair(kind, W, H, seed=done + 1)
-        m, a = m.numpy(), a.numpy()
+    m, a = pair if pair is not None else host_pair(wl, kind, 1)
+    w, h, d = wl["w"], wl["h"], wl["d"]
+    if wl["mode"] == "blocks":
+        import stepth_b200 as sb
+
+        blocks = sb.discretise_v0(m, PRECISION)
         t0 = time.perf_counter()
-        cpu_pass(oracle, m, a, threads)
-        t_total += time.perf_counter() - t0
-        done += 1
-    val = done * W * H * D / t_total / 1e6
-    return {"value": round(val, 3), "unit": METRIC, "cores": threads, "kind": "port",
-            "sample": f"{done} whole {W}x{H} '{kind}' pair(s), D={D}, oracle depth_dense with {threads} threads, {t_total:.1f} s"}
+        n = 0
+        while n < 3 and time.perf_counter() - t0 < budget_s:
+            cpu_pass_rows(oracle, wl, m, a, 0, h, cores, blocks=blocks)
+            n += 1
+        dt = time.perf_counter() - t0
+        return {"value": round(n * w * h * d / dt / 1e6, 3), "unit": METRIC, "cores": cores, "kind": "port",
+                "sample": f"{n} x the whole {w}x{h} pair, {len(blocks)} blocks (disc_v0 stand-in, not timed), D={d}, "
+                          f"oracle depth_from_blocks with {cores} threads, {dt:.1f} s"}
+    rows = cpu_calibrate(oracle, wl, m, a, cores, budget_s * 0.8)
+    y0 = 0 if rows >= h else ((h - rows) // 2) // 8 * 8
+    t0 = time.perf_counter()
+    done = cpu_pass_rows(oracle, wl, m, a, y0, rows, cores)
+    dt = time.perf_counter() - t0
+    what = f"one whole {w}x{h} '{kind}' pair" if rows >= h else f"main rows [{y0}, {y0 + rows}) of one {w}x{h} '{kind}' pair"
+    return {"value": round(done * w * d / dt / 1e6, 3), "unit": METRIC, "cores": cores, "kind": "port",
+            "sample": f"{what}, D={d}, oracle with {cores} threads, {dt:.1f} s"}
 
 
-def algorithmic_probes(kind: str):
-    """probes the reference's scan order needs per query (every pixel of a ring counted once), counted
-    by the oracle on pair seed 1 of the bench batch (the pairs of a batch are draws of the same distribution)"""
-    from oracle import oracle
-    from stepth_b200 import synth
+def workload_config(name, wl, kind, world, pairs_total, pairs_this_gpu, l2_note, parallelism):
+    return {"workload": f"{name}_d{wl['d']}_{kind if wl['data'] == 'synthetic' else 'assets'}", "w": wl["w"], "h": wl["h"],
+            "max_rings": wl["d"], "precision": PRECISION, "pairs_per_step_total": pairs_total,
+            "pairs_per_step_this_gpu": pairs_this_gpu, "mode": wl["mode"],
+            "flags": "RESAMPLE_U8" + ("|INVERT|FOREGROUND|APPLY" if wl["fused"] else ""), "l2": l2_note,
+            "parallelism": parallelism}
 
-    m, a = synth.make_pair(kind, W, H, seed=1)
-    oracle.search_dense(m.numpy(), a.numpy(), PRECISION, D, threads=os.cpu_count() or 1, want_probes=True)
-    return oracle.last_unique_probes() / float(W * H)
+
+def describe(name, wl, kind, world):
+    """the `config` object of a workload: the GPU arm and the reference arm print the same one"""
+    pairs = wl["pairs"]
+    w, h = wl["w"], wl["h"]
+    if wl["mode"] == "bands":
+        return workload_config(name, wl, kind, world, 1, 1, "inputs larger than L2",
+                               f"row bands x{world}: allreduce(MAX) + 3-row halo exchange + all-gather of depth bands")
+    total = pairs if wl["scaling"] == "strong" else pairs * world
+    mine = (pairs + world - 1) // world if wl["scaling"] == "strong" else pairs
+    in_mb = mine * 7 * w * h / 1e6
+    l2 = (f"inputs {in_mb:.0f} MB per step per GPU > 126 MB L2 (no flush needed)" if in_mb > 126
+          else "L2 flushed between timed iterations (256 MB memset, outside the per-iteration events)")
+    return workload_config(name, wl, kind, world, total, mine, l2, f"pair-batch x{world} (no collective)")
 
 
 def run_reference(args):
-    """--impl reference: the CPU port with the reference's own parallelism (8-9 chunks), each step one pair"""
+    """--impl reference: the CPU port with the reference's own parallelism (8-9 chunks).  Each step is a bounded sample of
+    the GPU arm's workload: main rows of one pair sized so that a step takes about 2 s (the whole pair when that fits)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     from oracle import oracle
-    from stepth_b200 import synth
 
+    name, wl = args.workload, WORKLOADS[args.workload]
+    w, h, d = wl["w"], wl["h"], wl["d"]
     cores = os.cpu_count() or 1
-    pairs = []
-    for i in range(min(args.steps + args.warmup, 4)):
-        m, a = synth.make_pair(args.kind, W, H, seed=i + 1)
-        pairs.append((m.numpy(), a.numpy()))
+    n_pairs = 1 if wl["data"] == "assets" or wl["mode"] == "bands" else min(4, max(1, args.steps))
+    pairs = [host_pair(wl, args.kind, i + 1) for i in range(n_pairs)]
+    blocks = None
+    if wl["mode"] == "blocks":
+        import stepth_b200 as sb
+
+        blocks = sb.discretise_v0(pairs[0][0], PRECISION)
+        rows = h
+    else:
+        rows = cpu_calibrate(oracle, wl, *pairs[0], 0, 1.5)
+    n_bands = max(1, h // rows)
+
+    def one(i):
+        m, a = pairs[i % n_pairs]
+        y0 = ((i // n_pairs) * 5 % n_bands) * rows if rows < h else 0     # bands spread over the image
+        return cpu_pass_rows(oracle, wl, m, a, y0, rows, 0, blocks=blocks)  # threads = 0 -> len/8-sized chunks = 8-9 threads
+
     for i in range(args.warmup):
-        cpu_pass(oracle, *pairs[i % len(pairs)], 0)
+        one(i)
     t0 = time.perf_counter()
+    done = 0
     for i in range(args.steps):
-        cpu_pass(oracle, *pairs[i % len(pairs)], 0)   # threads = 0 -> len/8-sized chunks = 8-9 threads (reference)
+        done += one(args.warmup + i)
     dt = time.perf_counter() - t0
-    val = args.steps * W * H * D / dt / 1e6
+    val = done * w * d / dt / 1e6
     used = min(9, cores)
+    sample = (f"{args.steps} steps x " + ("one whole pair" if rows >= h else f"{rows} main rows of one {w}x{h} pair (bands spread over the image, {n_pairs} pairs)")
+              + f", reference-faithful 8-9 chunk threads on {cores} cores")
     line = {
         "impl": "reference", "metric": METRIC, "value": round(val, 3), "unit": METRIC, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 3),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": f"{args.workload}_d{D}_{args.kind}", "w": W, "h": H, "max_rings": D, "precision": PRECISION,
-                   "pairs_per_step": 1, "note": "each step = one pair of the GPU arm's batch (bounded sample)"},
-        "cpu_baseline": {"value": round(val, 3), "unit": METRIC, "cores": used, "kind": "port",
-                         "sample": f"{args.steps} steps x 1 pair, reference-faithful 8-9 chunk threads on {cores} cores"},
+        "higher_is_better": True, "scaling": wl["scaling"], "vs_baseline": None, "dtype": "u8", "data": wl["data"],
+        "config": describe(name, wl, args.kind, max(1, args.gpus)),
+        "cpu_baseline": {"value": round(val, 3), "unit": METRIC, "cores": used, "kind": "port", "sample": sample},
         "e2e": {"value": round(val, 3), "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -211,98 +335,248 @@ def run_reference(args):
 
 
 # ---------------------------------------------------------------------------------------------------------------
-# GPU arm
+# GPU arm: timing
 # ---------------------------------------------------------------------------------------------------------------
-def time_resident(torch, dist, step, steps, warmup, world):
-    """K timed steps over HBM-resident inputs; `step(events)` enqueues one step and records (start, end) CUDA events
-    around its ring-search stage.  Returns (total ms [max over ranks], search-stage ms summed over the steps)."""
+class Env:
+    """what every workload runner needs: torch, the process group, this rank's context"""
+
+    def __init__(self, args):
+        import torch
+
+        self.args, self.torch = args, torch
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device -- stepth_b200 has no CPU fallback (use --impl reference for the CPU port)")
+        self.numa_cpus = bind_to_gpu_numa(self.local)   # before any pinned allocation
+        torch.cuda.set_device(self.local)
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist
+
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+            self.dist = dist
+        import stepth_b200 as sb
+
+        self.sb = sb
+        self.ctx = sb.Context(self.local)
+        self.dev = torch.device("cuda", self.local)
+        self.flush_buf = None
+
+    def flush_l2(self):
+        """writes a buffer twice the size of L2 (126 MB) so that nothing of the previous iteration is cache-resident"""
+        if self.flush_buf is None:
+            self.flush_buf = self.torch.empty(256 << 20, dtype=self.torch.uint8, device=self.dev)
+        self.flush_buf.zero_()
+
+    def max_over_ranks(self, x: float) -> float:
+        if self.world > 1:
+            t = self.torch.tensor([x], dtype=self.torch.float64, device=self.dev)
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+            return float(t.item())
+        return x
+
+    def sum_over_ranks(self, x: float) -> float:
+        if self.world > 1:
+            t = self.torch.tensor([x], dtype=self.torch.float64, device=self.dev)
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+            return float(t.item())
+        return x
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+
+def time_resident(env, step, steps, warmup, flush=False):
+    """K timed steps over HBM-resident inputs; `step(events)` enqueues one step and records (start, end) CUDA events around
+    its ring-search stage.  Returns (total ms [max over ranks], search-stage ms summed over the steps).  flush: the inputs
+    are smaller than L2 -> every iteration is timed by its own event pair with an L2 flush in between."""
+    torch = env.torch
     for _ in range(warmup):
         step(None)
     torch.cuda.synchronize()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
-    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    t0.record()
-    for i in range(steps):
-        step(ev[i])
-    t1.record()
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    total = t0.elapsed_time(t1)
+    env.barrier()
+    if flush:
+        it = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        for i in range(steps):
+            env.flush_l2()
+            it[i][0].record()
+            step(ev[i])
+            it[i][1].record()
+        torch.cuda.synchronize()
+        total = sum(a.elapsed_time(b) for a, b in it)
+    else:
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        for i in range(steps):
+            step(ev[i])
+        t1.record()
+        torch.cuda.synchronize()
+        total = t0.elapsed_time(t1)
+    env.barrier()
     search = sum(a.elapsed_time(b) for a, b in ev)
-    if world > 1:
-        t = torch.tensor([total], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total = float(t.item())
-    return total, search
+    return env.max_over_ranks(total), search
 
 
-def time_e2e(torch, dist, step, steps, warmup, world):
-    """`step()` = the C-ABI host-buffer call: H2D of all inputs + the whole path + D2H of the results (synchronous)"""
+def time_e2e(env, step, steps, warmup, flush=False):
+    """`step()` = the C-ABI host-buffer call: H2D of all inputs + the whole path + D2H of the results (synchronous);
+    wall clock around the calls, max over ranks"""
     for _ in range(max(1, min(warmup, 2))):
         step()
-    if world > 1:
-        dist.barrier()
+    env.barrier()
+    if flush:
+        dt = 0.0
+        for _ in range(steps):
+            env.flush_l2()
+            env.torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            step()
+            dt += (time.perf_counter() - t0) * 1e3
+    else:
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            step()
+        dt = (time.perf_counter() - t0) * 1e3
+    return env.max_over_ranks(dt)
+
+
+def build_roofline(name, kind, wl, alg_bytes, pairs_per_launch, search_launch_ms, share, kernel_desc):
+    hbm, which = peaks()
+    achieved = alg_bytes / (search_launch_ms * 1e-3) / 1e9
+    prof = ncu_profile(name, kind) or {}
+    r = {"bound": "hbm", "achieved": round(achieved, 2), "peak": hbm, "unit": "GB/s", "frac": round(achieved / hbm, 5),
+         "traffic": prof.get("traffic"), "peak_source": which, "kernel": kernel_desc,
+         "alg_bytes_per_launch": alg_bytes, "pairs_per_launch": pairs_per_launch, "launch_ms": round(search_launch_ms, 4),
+         "share_of_step": round(share, 4),
+         "note": "the stage is instruction-issue / latency bound, not HBM bound (DESIGN.md section 5): `issue` is the ceiling "
+                 "that binds it; frac is reported as the contract asks"}
+    if prof.get("issue"):
+        r["issue"] = prof["issue"]   # {"kernel", "frac", "lanes_active", "inst_executed", "duration_us", "source"} from profiles/
+    return r
+
+
+def int_roofline(env, wl, mains, adds, n_first, search_launch_ms, alg_bytes):
+    """SURVEY 8(d)'s other half: O_alg = 2 integer ops per probe of the reference order, the probes counted ON THE DEVICE
+    (in-order kernel with a counter) over the very pairs of the timed launch sequence; P_INT measured by a register-only kernel"""
+    from stepth_b200 import device
+
+    torch = env.torch
+    hbm, _ = peaks()
+    _, probes = device.count_probes(env.ctx, mains[:n_first], adds[:n_first], PRECISION, wl["d"])
     torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        step()
-    dt = (time.perf_counter() - t0) * 1e3
-    if world > 1:
-        t = torch.tensor([dt], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dt = float(t.item())
-    return dt
+    per_q = (probes.double() / float(wl["w"] * wl["h"])).cpu().tolist()
+    total = float(probes.sum().item())
+    p_mixed, p_logic = env.ctx.int_peak(False), env.ctx.int_peak(True)
+    ops = 2.0 * total
+    t_int_ms, t_hbm_ms = ops / p_mixed * 1e3, alg_bytes / (hbm * 1e9) * 1e3
+    return {
+        "bound": "int-alu", "unit": "Tiop/s", "ops_per_launch": round(ops),
+        "probes_per_query_min": round(min(per_q), 2), "probes_per_query_mean": round(sum(per_q) / len(per_q), 2),
+        "probes_per_query_max": round(max(per_q), 2), "pairs_counted": n_first,
+        "achieved": round(ops / (search_launch_ms * 1e-3) / 1e12, 3), "peak": round(p_mixed / 1e12, 3),
+        "frac": round(ops / (search_launch_ms * 1e-3) / p_mixed, 4), "peak_logic_only": round(p_logic / 1e12, 3),
+        "peak_source": "measured (stepth_cuda_int_peak: LOP3+IMAD.IADD on both integer pipes; logic_only = LOP3+SHF, alu pipe)",
+        "t_roof_ms": round(max(t_int_ms, t_hbm_ms), 4), "t_hbm_ms": round(t_hbm_ms, 4), "t_int_ms": round(t_int_ms, 4),
+        "frac_of_t_roof": round(max(t_int_ms, t_hbm_ms) / search_launch_ms, 4),
+        "note": "O_alg = 2 ops x the probes the reference order needs, counted by stepth_cuda_dev_count_probes over every pair of "
+                "the timed launch sequence; the tile search skips probes, so this is an equivalent-work figure, not a "
+                "utilisation, and may exceed 1 (SURVEY.md 8(d))"}
 
 
-def run_ours(args):
-    import torch
+# ---------------------------------------------------------------------------------------------------------------
+# GPU arm: parity of what was just timed, against the CPU oracle (test infrastructure; the checker, never the path)
+# ---------------------------------------------------------------------------------------------------------------
+ORACLE_NOTE = "port of the reference (oracle/stepth_oracle.c), upstream parity unpinned"
 
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device -- stepth_b200 has no CPU fallback (use --impl reference for the CPU port)")
-    torch.cuda.set_device(local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
 
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+def parity_dense(env, wl, m_t, a_t, raw_t, depth_t, mx, mask_t=None, rgba_t=None, from_to=None, host_depth=None,
+                 n_queries=2000, seed=0):
+    """one pair: sampled raw distances vs the oracle's search; the WHOLE finished plane (+ mask, + rgba) vs the oracle's
+    normalise / Gaussian / invert / select_foreground / apply_mask of those raw distances; the host-buffer call's plane too"""
+    import numpy as np
 
-    import stepth_b200 as sb
+    from oracle import oracle
+
+    w, h, d = wl["w"], wl["h"], wl["d"]
+    m, a, raw = m_t.cpu().numpy(), a_t.cpu().numpy(), raw_t.cpu().numpy()
+    rng = np.random.default_rng(1234 + seed)
+    idx = rng.choice(w * h, min(n_queries, w * h), replace=False).astype(np.uint32)
+    sub, _ = oracle.search_dense_subset(m, a, PRECISION, idx, d, threads=os.cpu_count() or 1)
+    ok = bool(np.array_equal(raw.reshape(-1)[idx], sub))
+    planes = 0
+    norm, mx_ref = oracle.normalise(raw)
+    ok = ok and mx_ref == int(mx)
+    depth = oracle.gaussian_resample_unit(norm, oracle.RESAMPLE_U8)
+    if wl["fused"]:
+        depth = oracle.invert_depth(depth)
+    ok = ok and bool(np.array_equal(depth_t.cpu().numpy(), depth))
+    planes += 1
+    if host_depth is not None:
+        ok = ok and bool(np.array_equal(np.asarray(host_depth), depth))
+        planes += 1
+    if wl["fused"]:
+        mask, ft = oracle.select_foreground(depth)
+        ok = ok and tuple(int(v) for v in from_to) == tuple(ft)
+        ok = ok and bool(np.array_equal(mask_t.cpu().numpy(), mask))
+        ok = ok and bool(np.array_equal(rgba_t.cpu().numpy(), oracle.apply_mask(m, mask)))
+        planes += 2
+    return {"bit_exact": ok, "checked_queries": int(len(idx)), "checked_planes": planes}
+
+
+def finish_parity(env, p):
+    """all ranks agree on the verdict; counts are summed"""
+    ok = env.sum_over_ranks(0.0 if p["bit_exact"] else 1.0) == 0.0
+    return {"bit_exact": ok, "checked_queries": int(env.sum_over_ranks(p["checked_queries"])),
+            "checked_planes": int(env.sum_over_ranks(p["checked_planes"])), "oracle": ORACLE_NOTE}
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# GPU arm: dense pair batches (configs[1], [2], [3] and the README pair in dense mode)
+# ---------------------------------------------------------------------------------------------------------------
+def run_dense(env, name, kind, steps, warmup, main_line):
+    """-> the JSON line of one dense workload (rank 0 uses it; every rank must call it)"""
+    import numpy as np
+
     from stepth_b200 import bands, device, synth
 
-    ctx = sb.Context(local)
-    dev = torch.device("cuda", local)
-    scaling = WORKLOADS[args.workload][5]
-    flags = sb.RESAMPLE_U8 | ((sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY) if FUSED else 0)
-    if args.workload == "giant":
-        return run_giant(args, torch, dist, ctx, dev, rank, world, flags)
-
-    # pairs this rank processes per step: weak scaling = a fixed batch per GPU; batch4k = 64 pairs dealt to the ranks
-    if scaling == "strong":
-        my_pairs = bands.shard_pairs(args.pairs, rank, world)
-        total_pairs = args.pairs
+    torch, args, sb, ctx, dev = env.torch, env.args, env.sb, env.ctx, env.dev
+    wl = dict(WORKLOADS[name])
+    if main_line and args.pairs:
+        wl["pairs"] = args.pairs
+    W, H, D = wl["w"], wl["h"], wl["d"]
+    rank, world = env.rank, env.world
+    flags = sb.RESAMPLE_U8 | ((sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY) if wl["fused"] else 0)
+    # pairs this rank processes per step: weak = a fixed batch per GPU; strong = the workload's pairs dealt to the ranks
+    if wl["scaling"] == "strong":
+        my_pairs = bands.shard_pairs(wl["pairs"], rank, world)
+        total_pairs = wl["pairs"]
     else:
-        my_pairs = [rank * args.pairs + i for i in range(args.pairs)]
-        total_pairs = args.pairs * world
+        my_pairs = [rank * wl["pairs"] + i for i in range(wl["pairs"])]
+        total_pairs = wl["pairs"] * world
     B = len(my_pairs)
-    SUB = min(B, 16)                                   # pairs per launch sequence (bounds the scratch in HBM)
+    sub = min(B, SUB)
+    in_mb = B * 7 * W * H / 1e6
+    flush = in_mb <= 126
+    if flush:
+        steps = max(steps, 20)   # a sub-millisecond step: more iterations, each with its own event pair and an L2 flush before it
 
-    def make_batch(kind):
+    def make_batch(k):
+        if wl["data"] == "assets":
+            m, a = load_assets()
+            return torch.from_numpy(m).to(dev)[None].contiguous(), torch.from_numpy(a).to(dev)[None].contiguous()
         ms, as_ = [], []
         for i in my_pairs:
-            m, a = synth.make_pair(kind, W, H, seed=i + 1, device=dev)
+            m, a = synth.make_pair(k, W, H, seed=i + 1, device=dev)
             ms.append(m)
             as_.append(a)
         return torch.stack(ms).contiguous(), torch.stack(as_).contiguous()
 
-    mains, adds = make_batch(args.kind)
+    mains, adds = make_batch(kind)
     pipes = {}
 
     def pipe_for(n):
@@ -312,14 +586,13 @@ def run_ours(args):
 
     def make_step(mains, adds):
         def step(events):
-            for j, i0 in enumerate(range(0, B, SUB)):
-                n = min(SUB, B - i0)
+            for j, i0 in enumerate(range(0, B, sub)):
+                n = min(sub, B - i0)
                 # the search-stage events bracket the first launch sequence of the step (all are alike)
                 pipe_for(n).run(mains[i0:i0 + n], adds[i0:i0 + n], search_events=events if j == 0 else None)
         return step
 
     step = make_step(mains, adds)
-    sampler = ClockSampler(local)
     l0 = ctx.launch_count()
     step(None)
     torch.cuda.synchronize()
@@ -327,118 +600,229 @@ def run_ours(args):
     for p in pipes.values():
         assert int(p.status.abs().sum()) == 0, "a pair of the bench batch failed (max == 0?)"
 
-    sampler.start()   # samples through the resident AND the end-to-end timed regions (stopped below)
-    total_ms, search_ms = time_resident(torch, dist, step, args.steps, args.warmup, world)
+    sampler = ClockSampler(env.local) if main_line else None
+    if sampler:
+        sampler.start()
+    total_ms, search_ms = time_resident(env, step, steps, warmup, flush=flush)
+    clocks = sampler.stop() if sampler else None
     px_disp = W * H * D
-    value = total_pairs * args.steps * px_disp / (total_ms * 1e-3) / 1e6
+    value = total_pairs * steps * px_disp / (total_ms * 1e-3) / 1e6
+    search_launch_ms = search_ms / steps
+    alg = search_alg_bytes(W, H, D, sub)
+    n_seq = (B + sub - 1) // sub
+    roofline = build_roofline(name, kind, wl, alg, sub, search_launch_ms, search_ms * n_seq / total_ms,
+                              "ring search stage (stepth_cuda_dev_search_dense: tile_planes + coarse_transpose + search_near + search_far)")
 
-    hbm, which = peaks()
-    search_launch_ms = search_ms / args.steps
-    alg = search_alg_bytes(W, H, D, SUB)
-    achieved = alg / (search_launch_ms * 1e-3) / 1e9
-    n_seq = (B + SUB - 1) // SUB
-    roofline = {"bound": "hbm", "achieved": round(achieved, 2), "peak": hbm, "unit": "GB/s",
-                "frac": round(achieved / hbm, 5), "traffic": ncu_traffic(args.workload, args.kind), "peak_source": which,
-                "kernel": "ring search stage (stepth_cuda_dev_search_dense: tile_planes + coarse_transpose + search_near + search_far)",
-                "alg_bytes_per_launch": alg, "pairs_per_launch": SUB, "launch_ms": round(search_launch_ms, 4),
-                "share_of_step": round(search_ms * n_seq / total_ms, 4),
-                "note": "the stage is issue/latency bound, not HBM bound (DESIGN.md section 5); frac is reported as the contract asks"}
+    # the results of the LAST pair of this rank's batch, as the resident pipeline left them (checked below)
+    last = B - 1
+    lp = pipe_for(B - (n_seq - 1) * sub)
+    lj = last - (n_seq - 1) * sub
+    keep = {"raw": lp.d8[lj].clone(), "depth": lp.depth[lj].clone(), "mx": int(lp.max[lj])}
+    if wl["fused"]:
+        keep.update(mask=lp.mask[lj].clone(), rgba=lp.rgba_out[lj].clone(), ft=lp.ranges[lj, :2].tolist())
 
-    e2e = None
+    e2e, host_last = None, None
     if not args.no_e2e:
         host_m = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(B)]
         host_a = [torch.empty((H, W, 3), dtype=torch.uint8).pin_memory() for _ in range(B)]
         out = {"depth": [torch.empty((H, W), dtype=torch.uint8).pin_memory() for _ in range(B)]}
-        if FUSED:
+        if wl["fused"]:
             out["mask"] = [torch.empty((H, W), dtype=torch.uint8).pin_memory() for _ in range(B)]
             out["rgba"] = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(B)]
         for i in range(B):
             host_m[i].copy_(mains[i])
             host_a[i].copy_(adds[i])
 
-        def e2e_step():
-            for i0 in range(0, B, SUB):
-                sl = slice(i0, min(B, i0 + SUB))
-                ctx.depth_dense_batch(host_m[sl], host_a[sl], PRECISION, D, flags, out={k: v[sl] for k, v in out.items()})
+        def e2e_step(hm=host_m, ha=host_a, ho=out, n=B):
+            for i0 in range(0, n, sub):
+                sl = slice(i0, min(n, i0 + sub))
+                ctx.depth_dense_batch(hm[sl], ha[sl], PRECISION, D, flags, out={k: v[sl] for k, v in ho.items()})
 
-        e2e_steps = max(2, min(args.steps, 5))
-        e2e_ms = time_e2e(torch, dist, e2e_step, e2e_steps, args.warmup, world)
+        e2e_steps = max(2, min(steps, 5)) if not flush else max(steps, 10)
+        e2e_ms = time_e2e(env, e2e_step, e2e_steps, warmup, flush=flush)
         rw, rh = reach(W, H, D)
+        h2d, d2h = B * (4 * W * H + 3 * rw * rh), B * W * H * (6 if wl["fused"] else 1)
         e2e = {"value": round(total_pairs * e2e_steps * px_disp / (e2e_ms * 1e-3) / 1e6, 3), "unit": METRIC,
-               "h2d_bytes_per_step": B * (4 * W * H + 3 * rw * rh), "d2h_bytes_per_step": B * W * H * (6 if FUSED else 1),
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                "ms_per_step": round(e2e_ms / e2e_steps, 3), "steps": e2e_steps,
+               "link_gbs_this_gpu": round((h2d + d2h) / (e2e_ms / e2e_steps * 1e-3) / 1e9, 2),
                "api": "stepth_cuda_depth_dense_batch (host buffers, pinned; chunks pipelined over copy/compute/copy streams)"}
-        # the resident pipeline and the host-buffer call must agree bit for bit
-        assert torch.equal(out["depth"][0], pipe_for(min(SUB, B)).depth[0].cpu()) or B > SUB, "host-buffer path and device-resident path disagree"
+        host_last = out["depth"][last].numpy().copy()
+        # the same call with ordinary pageable memory (what a Rust Vec<u8> is): the library stages it through its own
+        # pinned ring.  Bounded to one launch sequence of pairs.
+        nb = min(B, sub)
+        pg_m = [np.array(host_m[i].numpy(), copy=True) for i in range(nb)]
+        pg_a = [np.array(host_a[i].numpy(), copy=True) for i in range(nb)]
+        pg_out = {k: [np.empty(tuple(v[0].shape), np.uint8) for _ in range(nb)] for k, v in out.items()}
+        pg_steps = max(2, min(steps, 4)) if not flush else max(steps, 10)
+        pg_ms = time_e2e(env, lambda: e2e_step(pg_m, pg_a, pg_out, nb), pg_steps, warmup, flush=flush)
+        pg_total = nb * world if wl["scaling"] == "weak" or world == 1 else int(env.sum_over_ranks(nb))
+        e2e["pageable"] = {"value": round(pg_total * pg_steps * px_disp / (pg_ms * 1e-3) / 1e6, 3),
+                           "ms_per_step": round(pg_ms / pg_steps, 3), "pairs_per_step_this_gpu": nb, "steps": pg_steps,
+                           "note": "numpy (malloc) buffers in and out; staged through the library's pinned ring by its copy threads"}
+        e2e["pageable"]["vs_pinned"] = round(e2e["pageable"]["value"] / e2e["value"], 3)   # both are pairs/s x px_disp
+        same = all(np.array_equal(pg_out["depth"][i], out["depth"][i].numpy()) for i in range(nb))
+        assert same, "pageable and pinned host-buffer calls disagree"
+        del host_m, host_a, out, pg_m, pg_a, pg_out
 
-    clocks = sampler.stop()
+    parity = None
+    if not args.no_parity:
+        p = parity_dense(env, wl, mains[last], adds[last], keep["raw"], keep["depth"], keep["mx"], keep.get("mask"),
+                         keep.get("rgba"), keep.get("ft"), host_depth=host_last, seed=rank)
+        parity = finish_parity(env, p)
+        parity["what"] = f"pair {my_pairs[last]} (the last of each rank's batch): sampled raw distances + whole finished planes, resident and host-buffer results"
+
     extra = {}
-    if args.extra_kinds and world == 1:
-        for kind in ("geo", "worst"):
-            if kind == args.kind:
+    if main_line and args.extra_kinds and world == 1:
+        for k2 in ("geo", "worst"):
+            if k2 == kind:
                 continue
-            m2, a2 = make_batch(kind)
-            steps2 = max(1, min(args.steps, 3))
-            t_ms, s_ms = time_resident(torch, dist, make_step(m2, a2), steps2, 1, world)
-            extra[kind] = {"value": round(total_pairs * steps2 * px_disp / (t_ms * 1e-3) / 1e6, 3), "ms_per_step": round(t_ms / steps2, 3),
-                           "search_ms_per_launch": round(s_ms / steps2, 3)}
+            m2, a2 = make_batch(k2)
+            steps2 = max(1, min(steps, 3))
+            t_ms, s_ms = time_resident(env, make_step(m2, a2), steps2, 1)
+            extra[k2] = {"value": round(total_pairs * steps2 * px_disp / (t_ms * 1e-3) / 1e6, 3), "ms_per_step": round(t_ms / steps2, 3),
+                         "search_ms_per_launch": round(s_ms / steps2, 3)}
             del m2, a2
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu = cpu_baseline(args.kind)
-        # the other half of SURVEY 8(d)'s roofline, t_roof = max(B_alg / BW_HBM, O_alg / P_INT): O_alg = 2 integer ops
-        # per probe of the reference order (oracle-counted), P_INT measured on this GPU by a register-only kernel
-        probes_q = algorithmic_probes(args.kind)
-        p_mixed, p_logic = ctx.int_peak(False), ctx.int_peak(True)
-        ops = 2.0 * probes_q * W * H * SUB
-        t_int_ms, t_hbm_ms = ops / p_mixed * 1e3, alg / (hbm * 1e9) * 1e3
-        roofline["int"] = {
-            "bound": "int-alu", "unit": "Tiop/s", "ops_per_launch": round(ops), "probes_per_query": round(probes_q, 2),
-            "achieved": round(ops / (search_launch_ms * 1e-3) / 1e12, 3), "peak": round(p_mixed / 1e12, 3),
-            "frac": round(ops / (search_launch_ms * 1e-3) / p_mixed, 4), "peak_logic_only": round(p_logic / 1e12, 3),
-            "peak_source": "measured (stepth_cuda_int_peak: LOP3+IMAD.IADD on both integer pipes; logic_only = LOP3+SHF, alu pipe)",
-            "t_roof_ms": round(max(t_int_ms, t_hbm_ms), 4), "t_hbm_ms": round(t_hbm_ms, 4), "t_int_ms": round(t_int_ms, 4),
-            "frac_of_t_roof": round(max(t_int_ms, t_hbm_ms) / search_launch_ms, 4),
-            "note": "O_alg = 2 ops x probes the reference order needs (oracle count, seed-1 pair x pairs per launch); "
-                    "the tile search skips probes, so frac may exceed 1 (SURVEY.md 8(d))"}
+        cpu = cpu_baseline(wl, name, kind, pair=(mains[0].cpu().numpy(), adds[0].cpu().numpy()))
+        if wl["data"] == "synthetic":
+            roofline["int"] = int_roofline(env, wl, mains, adds, sub, search_launch_ms, alg)
 
-    if rank == 0:
-        line = {
-            "metric": METRIC, "value": round(value, 3), "unit": METRIC, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": round(total_ms / args.steps, 4), "higher_is_better": True,
-            "scaling": scaling, "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": f"{args.workload}_d{D}_{args.kind}", "w": W, "h": H, "max_rings": D, "precision": PRECISION,
-                       "pairs_per_step_total": total_pairs, "pairs_per_step_this_gpu": B,
-                       "flags": "RESAMPLE_U8" + ("|INVERT|FOREGROUND|APPLY" if FUSED else ""),
-                       "l2": f"inputs {B * (4 + 3) * W * H / 1e6:.0f} MB per step per GPU > 126 MB L2 (no flush needed)",
-                       "parallelism": f"pair-batch x{world} (no collective)"},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
-            "clocks": clocks,
-        }
-        if extra:
-            line["other_distributions"] = extra
-        print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    line = {
+        "metric": METRIC, "value": round(value, 3), "unit": METRIC, "n_gpus": world, "steps": steps,
+        "warmup": warmup, "ms_per_step": round(total_ms / steps, 4), "higher_is_better": True,
+        "scaling": wl["scaling"], "vs_baseline": None, "dtype": "u8", "data": wl["data"],
+        "config": describe(name, wl, kind, world),
+        "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "parity": parity, "gpu_launches": launches_per_step * steps,
+    }
+    if clocks is not None:
+        line["clocks"] = clocks
+    if extra:
+        line["other_distributions"] = extra
+    del mains, adds, pipes, keep
+    torch.cuda.empty_cache()
+    return line
 
 
-def run_giant(args, torch, dist, ctx, dev, rank, world, flags):
-    """configs[4]: ONE pair, main rows banded over the ranks (bands.BandRunner): MAX all-reduce of the normaliser, 3-row
-    halo exchange, and an NCCL all-gather of the depth bands so that every GPU ends with the assembled map."""
-    import stepth_b200 as sb
+# ---------------------------------------------------------------------------------------------------------------
+# GPU arm: the README pair in block mode (configs[0]: the reference's actual call shape, depth_image.rs:104-122)
+# ---------------------------------------------------------------------------------------------------------------
+def run_blocks(env, name, kind, steps, warmup, main_line):
+    import numpy as np
+
+    from stepth_b200 import device
+
+    torch, args, sb, ctx, dev = env.torch, env.args, env.sb, env.ctx, env.dev
+    wl = WORKLOADS[name]
+    W, H, D = wl["w"], wl["h"], wl["d"]
+    m, a = load_assets()
+    # the disage discretiser stays on the host in the drop-in (blocks are an INPUT of the boundary); disc_v0 is the
+    # documented stand-in.  It is outside both the GPU and the CPU timed regions.
+    blocks = sb.discretise_v0(m, PRECISION)
+    nb = len(blocks)
+    blocks_t = torch.from_numpy(blocks.view(np.uint8).reshape(nb, 20)).to(dev).contiguous()
+    add_t = torch.from_numpy(a).to(dev).contiguous()
+    pipe = device.BlockPipeline(ctx, nb, W, H, a.shape[1], a.shape[0], PRECISION, D, sb.RESAMPLE_U8)
+
+    def step(events):
+        pipe.run(blocks_t, add_t, search_events=events)
+
+    l0 = ctx.launch_count()
+    step(None)
+    torch.cuda.synchronize()
+    launches_per_step = ctx.launch_count() - l0
+    assert int(pipe.status[0]) == 0
+    steps_r = max(steps, 20)
+    total_ms, search_ms = time_resident(env, step, steps_r, warmup, flush=True)
+    px_disp = W * H * D
+    value = env.world * steps_r * px_disp / (total_ms * 1e-3) / 1e6
+    # algorithmic bytes of the block search: 20 B per block read + the reachable additional image + 1 B per block written
+    rw, rh = min(a.shape[1], (W + 1) // 2 + D + 1), min(a.shape[0], (H + 1) // 2 + D + 1)
+    alg = nb * 21 + 3 * rw * rh
+    roofline = build_roofline(name, "assets", wl, alg, 1, search_ms / steps_r, search_ms / total_ms,
+                              "ring search stage, block mode (stepth_cuda_dev_search_blocks: tile_planes + coarse_transpose + search_near<blocks> + search_far<blocks>)")
+    raw_gpu, depth_gpu = pipe.d8.cpu().numpy(), pipe.depth[0].cpu().numpy()
+
+    e2e, host_depth = None, None
+    if not args.no_e2e:
+        pin_a = torch.from_numpy(a).pin_memory()
+        pin_b = torch.from_numpy(blocks.view(np.uint8).reshape(nb, 20).copy()).pin_memory()
+        blocks_pinned = pin_b.numpy().reshape(-1).view(sb.BLOCK_DTYPE)
+        res = {}
+
+        def call(add_host, blocks_host):
+            res["out"] = ctx.depth_from_blocks(add_host, blocks_host, W, H, PRECISION, D, sb.RESAMPLE_U8)
+
+        e2e_steps = max(steps, 20)
+        ms = time_e2e(env, lambda: call(pin_a.numpy(), blocks_pinned), e2e_steps, warmup, flush=True)
+        host_depth = res["out"]["depth"].copy()
+        ms_pg = time_e2e(env, lambda: call(a, blocks), e2e_steps, warmup, flush=True)
+        e2e = {"value": round(env.world * e2e_steps * px_disp / (ms * 1e-3) / 1e6, 3), "unit": METRIC,
+               "h2d_bytes_per_step": nb * 20 + 3 * rw * rh, "d2h_bytes_per_step": W * H,
+               "ms_per_step": round(ms / e2e_steps, 4), "steps": e2e_steps,
+               "api": "stepth_cuda_depth_from_blocks (host buffers; inputs pinned, the depth plane lands in a numpy array)",
+               "pageable": {"value": round(env.world * e2e_steps * px_disp / (ms_pg * 1e-3) / 1e6, 3),
+                            "ms_per_step": round(ms_pg / e2e_steps, 4), "steps": e2e_steps}}
+
+    parity = None
+    if not args.no_parity:
+        from oracle import oracle
+
+        ref_depth, ref_raw = oracle.depth_from_blocks(a, blocks, PRECISION, W, H, D, resample=oracle.RESAMPLE_U8,
+                                                      threads=os.cpu_count() or 1, want_raw=True)
+        ok = bool(np.array_equal(raw_gpu, ref_raw)) and bool(np.array_equal(depth_gpu, ref_depth))
+        planes = 1
+        if host_depth is not None:
+            ok = ok and bool(np.array_equal(host_depth, ref_depth))
+            planes += 1
+        parity = finish_parity(env, {"bit_exact": ok, "checked_queries": nb, "checked_planes": planes})
+        parity["what"] = "every block's raw distance + the whole finished plane, resident and host-buffer results"
+
+    cpu = None
+    if env.rank == 0 and env.world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline(wl, name, kind, pair=(m, a), budget_s=4.0)
+    line = {
+        "metric": METRIC, "value": round(value, 3), "unit": METRIC, "n_gpus": env.world, "steps": steps_r, "warmup": warmup,
+        "ms_per_step": round(total_ms / steps_r, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "assets", "config": dict(describe(name, wl, kind, env.world), n_blocks=nb,
+                                                      discretiser="disc_v0 stand-in on the host, outside the timed regions (disage source absent)"),
+        "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "parity": parity, "gpu_launches": launches_per_step * steps_r,
+    }
+    del pipe, blocks_t, add_t
+    torch.cuda.empty_cache()
+    return line
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# GPU arm: one giant pair in row bands (configs[4])
+# ---------------------------------------------------------------------------------------------------------------
+def run_giant(env, name, kind, steps, warmup, main_line):
+    """ONE pair, main rows banded over the ranks (bands.BandRunner): MAX all-reduce of the normaliser, 3-row halo exchange,
+    and an all-gather of the depth bands so that every GPU ends with the assembled map."""
+    import numpy as np
+
     from stepth_b200 import bands, synth
 
+    torch, args, sb, ctx, dev, dist = env.torch, env.args, env.sb, env.ctx, env.dev, env.dist
+    wl = WORKLOADS[name]
+    W, H, D = wl["w"], wl["h"], wl["d"]
+    rank, world = env.rank, env.world
+    flags = sb.RESAMPLE_U8
     runner = bands.BandRunner(bands.DeviceStages(ctx), W, H, H, PRECISION, D, flags)
     b = runner.band
     # every rank generates the same pair from the same seed and keeps only its rows (synthetic data; no scatter timed)
-    m, a = synth.make_pair(args.kind, W, H, seed=1, device=dev)
+    m, a = synth.make_pair(kind, W, H, seed=1, device=dev)
     mb, ab = m[None, b.y0:b.y1].contiguous(), a[None, b.ay0:b.ay1].contiguous()
+    want_cpu_copy = not args.no_parity or (rank == 0 and world == 1 and not args.no_cpu_baseline)
+    m_np = m.cpu().numpy() if want_cpu_copy else None
+    a_np = a.cpu().numpy() if want_cpu_copy else None
     del m, a
     torch.cuda.empty_cache()
-    sampler = ClockSampler(int(os.environ.get("LOCAL_RANK", "0")))
+    gather = world > 1
     l0 = ctx.launch_count()
-    out = runner.run(mb, ab, gather_depth=world > 1)
+    out = runner.run(mb, ab, gather_depth=gather)
     torch.cuda.synchronize()
     launches = ctx.launch_count() - l0
     assert out["status"] == 0
@@ -446,46 +830,145 @@ def run_giant(args, torch, dist, ctx, dev, rank, world, flags):
     def step(events):
         if events is not None:
             events[0].record()
-        runner.run(mb, ab, gather_depth=world > 1)
+        runner.run(mb, ab, gather_depth=gather)
         if events is not None:
             events[1].record()
 
-    sampler.start()
-    total_ms, _ = time_resident(torch, dist, step, args.steps, args.warmup, world)
-    clocks = sampler.stop()
-    value = args.steps * W * H * D / (total_ms * 1e-3) / 1e6
+    sampler = ClockSampler(env.local) if main_line else None
+    if sampler:
+        sampler.start()
+    total_ms, _ = time_resident(env, step, steps, warmup)
+    clocks = sampler.stop() if sampler else None
+    value = steps * W * H * D / (total_ms * 1e-3) / 1e6
     # one more (untimed) run with CUDA events between the stages: where each rank's time goes
     runner.profile = True
-    runner.run(mb, ab, gather_depth=world > 1)
+    out = runner.run(mb, ab, gather_depth=gather)
     runner.profile = False
     stage_ms = [runner.stage_ms]
     if world > 1:
         stage_ms = [None] * world
         dist.all_gather_object(stage_ms, runner.stage_ms)
-    if rank == 0:
-        line = {
-            "metric": METRIC, "value": round(value, 3), "unit": METRIC, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": round(total_ms / args.steps, 4), "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": f"giant_d{D}_{args.kind}", "w": W, "h": H, "max_rings": D, "precision": PRECISION,
-                       "bands": [[p.y0, p.y1, p.ay0, p.ay1] for p in runner.plan],
-                       "l2": "inputs larger than L2",
-                       "parallelism": f"row bands x{world}: allreduce(MAX) + 3-row halo all-gather + NCCL all-gather of depth bands"},
-            "roofline": None, "cpu_baseline": None, "e2e": None, "gpu_launches": launches * args.steps, "clocks": clocks,
-            "stage_ms_per_rank": stage_ms,
-        }
+    # roofline of the search stage on the slowest band: this rank's main rows + the additional rows it can reach
+    rw = min(W, W // 2 + D)
+    my_alg = 4 * W * (b.y1 - b.y0) + 3 * rw * (b.ay1 - b.ay0) + W * (b.y1 - b.y0)
+    my_search = runner.stage_ms.get("search", 0.0)
+    slow = env.max_over_ranks(my_search)
+    alg_all = int(env.sum_over_ranks(my_alg))
+    roofline = build_roofline(name, kind, wl, alg_all // world, 1, slow, slow / (total_ms / steps),
+                              "ring search stage of one band (tile_planes + coarse_transpose + search_near + search_far), the slowest rank's time, mean band bytes")
+
+    e2e = None
+    if not args.no_e2e:
+        hm, ha = mb.cpu().pin_memory(), ab.cpu().pin_memory()
+        hd = torch.empty((1, b.y1 - b.y0, W), dtype=torch.uint8).pin_memory()
+        dm, da = torch.empty_like(mb), torch.empty_like(ab)
+
+        def e2e_step():
+            dm.copy_(hm, non_blocking=True)
+            da.copy_(ha, non_blocking=True)
+            o = runner.run(dm, da, gather_depth=False)     # bands go straight back to pinned host memory (no gather)
+            hd.copy_(o["depth_band"], non_blocking=True)
+            torch.cuda.synchronize()
+
+        e2e_steps = max(2, min(steps, 5))
+        ms = time_e2e(env, e2e_step, e2e_steps, warmup)
+        e2e = {"value": round(e2e_steps * W * H * D / (ms * 1e-3) / 1e6, 3), "unit": METRIC,
+               "h2d_bytes_per_step": int(env.sum_over_ranks(hm.numel() + ha.numel())),
+               "d2h_bytes_per_step": int(env.sum_over_ranks(hd.numel())),
+               "ms_per_step": round(ms / e2e_steps, 3), "steps": e2e_steps,
+               "api": "bands.BandRunner over the stage API: each rank uploads its band (+ reachable additional rows) from pinned "
+                      "memory, MAX all-reduce + halo exchange, its depth band returns to pinned memory"}
+        del hm, ha, hd, dm, da
+
+    parity = None
+    if not args.no_parity:
+        from oracle import oracle
+
+        rows = b.y1 - b.y0
+        raw_band = out["d8_band"][0].cpu().numpy()
+        rng = np.random.default_rng(77 + rank)
+        n_q = min(2000, rows * W)
+        local = rng.choice(rows * W, n_q, replace=False).astype(np.int64)
+        local[: min(200, n_q)] %= min(rows, 3) * W                      # some right under the upper seam
+        idx = (local + b.y0 * W).astype(np.uint32)
+        sub, _ = oracle.search_dense_subset(m_np, a_np, PRECISION, idx, D, threads=max(1, (os.cpu_count() or 1) // world))
+        ok = bool(np.array_equal(raw_band.reshape(-1)[local], sub))
+        planes = 0
+        # the finished plane, whole: rank 0 assembles the raw bands and runs the oracle's normalise + Gaussian over them
+        raw_t = out["d8_band"].contiguous()
+        depth_t = out["depth_band"].contiguous()
+        if world > 1:
+            assert len({p.y1 - p.y0 for p in runner.plan}) == 1, "equal bands expected for the parity gather"
+            raws = torch.empty((world,) + tuple(raw_t.shape), dtype=torch.uint8, device=dev)
+            deps = torch.empty_like(raws)
+            dist.all_gather_into_tensor(raws, raw_t)
+            dist.all_gather_into_tensor(deps, depth_t)
+            if rank == 0:
+                ok = ok and bool(torch.equal(deps.reshape(H, W), out["depth"].reshape(H, W)))   # the timed all-gather's result
+            raw_full, depth_full = raws.reshape(H, W), deps.reshape(H, W)
+        else:
+            raw_full, depth_full = raw_t.reshape(H, W), depth_t.reshape(H, W)
+        if rank == 0:
+            norm, _ = oracle.normalise(raw_full.cpu().numpy())
+            ok = ok and bool(np.array_equal(depth_full.cpu().numpy(), oracle.gaussian_resample_unit(norm, oracle.RESAMPLE_U8)))
+            planes = 1
+        parity = finish_parity(env, {"bit_exact": ok, "checked_queries": n_q, "checked_planes": planes})
+        parity["what"] = "every band: sampled raw distances (some at the seams) vs the oracle on the whole pair; the assembled finished plane, whole"
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline(wl, name, kind, pair=(m_np, a_np), budget_s=8.0)
+    line = {
+        "metric": METRIC, "value": round(value, 3), "unit": METRIC, "n_gpus": world, "steps": steps,
+        "warmup": warmup, "ms_per_step": round(total_ms / steps, 4), "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": dict(describe(name, wl, kind, world), bands=[[p.y0, p.y1, p.ay0, p.ay1] for p in runner.plan]),
+        "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "parity": parity, "gpu_launches": launches * steps,
+        "stage_ms_per_rank": stage_ms,
+    }
+    if clocks is not None:
+        line["clocks"] = clocks
+    del mb, ab, out, runner
+    torch.cuda.empty_cache()
+    return line
+
+
+RUNNERS = {"dense": run_dense, "blocks": run_blocks, "bands": run_giant}
+
+
+def compact(line):
+    """an other_workloads entry: the same keys as a line, minus what only the main line needs"""
+    return {k: line[k] for k in ("value", "ms_per_step", "steps", "scaling", "config", "roofline", "cpu_baseline", "e2e", "parity",
+                                 "gpu_launches", "stage_ms_per_rank") if k in line}
+
+
+def run_ours(args):
+    env = Env(args)
+    wl = WORKLOADS[args.workload]
+    line = RUNNERS[wl["mode"]](env, args.workload, args.kind, args.steps, args.warmup, True)
+    line["host"] = {"cpus": os.cpu_count(), "cpus_bound_to_this_gpu": env.numa_cpus}
+    bad = [args.workload] if line.get("parity") and not line["parity"]["bit_exact"] else []
+    if not args.no_others:
+        others = {}
+        for name in OTHER_WORKLOADS:
+            if name == args.workload:
+                continue
+            sub_line = RUNNERS[WORKLOADS[name]["mode"]](env, name, args.kind, max(3, min(args.steps, 10)), 3, False)
+            others[name] = compact(sub_line)
+            if sub_line.get("parity") and not sub_line["parity"]["bit_exact"]:
+                bad.append(name)
+        line["other_workloads"] = others
+    if env.rank == 0:
         print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    if env.world > 1:
+        env.dist.destroy_process_group()
+    if bad:
+        sys.stderr.write(f"bench.py: PARITY FAILURE against the oracle in {bad}\n")
+        raise SystemExit(3)
 
 
 def main():
-    global W, H, D, FUSED
     args = parse_args()
-    w, h, d, pairs, fused, _ = WORKLOADS[args.workload]
-    W, H, D, FUSED = w, h, d, fused
-    if not args.pairs:
-        args.pairs = pairs
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -207,6 +207,14 @@ uint64_t stepth_cuda_launch_count(const stepth_ctx *ctx);
  * integer work (2 ops per probe of the reference order, src/helpers.rs:26-47) by it. */
 int32_t stepth_cuda_int_peak(stepth_ctx *ctx, int32_t logic_only, double *ops_per_second_out);
 
+/* Measurement aid (no reference counterpart): runs the in-order kernel (one thread per query, the probe order of
+ * src/helpers.rs:26-47 with the duplicate probes dropped) and counts, per pair, the in-bounds pixels that order visits up to
+ * and including the first match -- the "probes the reference order needs" of SURVEY.md 8(d).  d8_out / max_out as
+ * stepth_cuda_dev_search_dense; probes_out [n_pairs] u64 (device). */
+int32_t stepth_cuda_dev_count_probes(stepth_ctx *ctx, void *stream, const stepth_dev_shape *shape,
+                                     const stepth_params *params, const uint8_t *main_rgba, const uint8_t *add_rgb,
+                                     uint8_t *d8_out, uint32_t *max_out, uint64_t *probes_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -92,6 +92,7 @@ SIGNATURES = {
     "stepth_cuda_dev_histogram": (_i32, [_vp, _vp, _u8p, _sz, _u32p]),
     "stepth_cuda_launch_count": (C.c_uint64, [_vp]),
     "stepth_cuda_int_peak": (_i32, [_vp, _i32, C.POINTER(C.c_double)]),
+    "stepth_cuda_dev_count_probes": (_i32, [_vp, _vp, _SP, _PP, _u8p, _u8p, _u8p, _u32p, _vp]),
 }
 
 _lib = None

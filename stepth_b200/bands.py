@@ -199,6 +199,7 @@ class BandRunner:
             return _ffi.ERR_DIV_BY_ZERO_MAX if int(mx[0]) == 0 else int(status[0]) if rows > 0 else 0
 
         out["depth_band"] = depth
+        out["d8_band"] = d8          # raw distances of this band (parity checks read them; nothing else does)
         self._mark("finish")
         if want_fg:
             out["status"] = read_status()

@@ -131,11 +131,12 @@ inline int32_t get_taps(stepth_ctx *ctx, cudaStream_t st, uint32_t n, const TapR
         stepth_ctx::Taps t;
         build_taps(n, t.host);
         STEPTH_CUDA_TRY(ctx, cudaMalloc((void **)&t.dev, sizeof(TapRow) * (n ? n : 1)));
-        // synchronous copy: the table is immutable afterwards and shared by every later launch
-        STEPTH_CUDA_TRY(ctx, cudaMemcpy(t.dev, t.host.data(), sizeof(TapRow) * n, cudaMemcpyHostToDevice));
+        // the table is immutable afterwards and shared by every later launch on any stream: the copy is ordered on the
+        // caller's (non-blocking) stream and waited for, so the DMA itself -- not just its staging -- is over when this returns
+        STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(t.dev, t.host.data(), sizeof(TapRow) * n, cudaMemcpyHostToDevice, st));
+        STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(st));
         it = ctx->taps.emplace(n, std::move(t)).first;
     }
-    (void)st;
     for (int k = 0; k < 7; ++k) interior_out[k] = n >= 7 ? it->second.host[3].w[k] : 0.0f;
     *dev_out = it->second.dev;
     return STEPTH_OK;

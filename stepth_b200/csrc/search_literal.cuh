@@ -23,6 +23,7 @@ struct SearchArgs {
     uint32_t sat;
     uint8_t *d8;                 // [n_pairs, n_queries]
     uint32_t *max_out;           // [n_pairs]
+    unsigned long long *probes_out;  // [n_pairs] or null (literal kernel only): in-bounds pixels the reference order visits, each once
 };
 
 // origin + colour box of query q (depth_image.rs:114-118)
@@ -57,6 +58,7 @@ __global__ void __launch_bounds__(256) search_literal_kernel(SearchArgs a) {
     const uint32_t pair = blockIdx.y;
     const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t d = 0;
+    unsigned long long n_probes = 0;
     if (q < a.n_queries) {
         int ox, oy;
         ColourBox box;
@@ -70,6 +72,7 @@ __global__ void __launch_bounds__(256) search_literal_kernel(SearchArgs a) {
             auto probe = [&](int dx, int dy) -> bool {
                 int x = ox + dx, yl = oyl + dy;
                 if (x < 0 || x >= wa || yl < 0 || yl >= (int)a.ha) return false;
+                ++n_probes;
                 const uint8_t *v = add + ((size_t)yl * wa + x) * 3;
                 return box_contains(box, v[0], v[1], v[2]);
             };
@@ -90,6 +93,10 @@ __global__ void __launch_bounds__(256) search_literal_kernel(SearchArgs a) {
         a.d8[(size_t)pair * a.n_queries + q] = (uint8_t)d;
     }
     publish_max(d, a.max_out + pair);
+    if (a.probes_out) {   // measurement aid (bench.py's algorithmic-work figure): one atomic per warp
+        for (int o = 16; o; o >>= 1) n_probes += __shfl_xor_sync(0xffffffffu, n_probes, o);
+        if ((threadIdx.x & 31) == 0 && n_probes) atomicAdd(a.probes_out + pair, n_probes);
+    }
 }
 
 }  // namespace stepth

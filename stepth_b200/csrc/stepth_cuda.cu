@@ -153,12 +153,24 @@ extern "C" int32_t stepth_cuda_dev_search_dense(stepth_ctx *ctx, void *stream, c
                                                 const stepth_params *params, const uint8_t *main_rgba,
                                                 const uint8_t *add_rgb, uint8_t *d8_out, uint32_t *max_out) {
     if (!ctx) return STEPTH_ERR_INVALID_ARG;
-    if (!s || !params_ok(params) || !main_rgba || !add_rgb || !d8_out || !max_out)
+    if (!s || !params_ok(params) || !main_rgba || (!add_rgb && s->ha) || !d8_out || !max_out)
         return set_err(ctx, STEPTH_ERR_INVALID_ARG, "dev_search_dense: null or invalid argument");
-    if (s->n_pairs == 0 || s->w == 0 || s->h == 0 || s->wa == 0 || s->ha == 0 ||
+    if (s->n_pairs == 0 || s->w == 0 || s->h == 0 || s->wa == 0 || (s->ha == 0 && s->add_img_h == 0) ||
         (uint64_t)s->w * s->h > 0xffffffffull || ((uintptr_t)main_rgba & 3))
         return set_err(ctx, STEPTH_ERR_INVALID_ARG, "dev_search_dense: bad shape or unaligned RGBA plane");
     cudaStream_t st = (cudaStream_t)stream;
+    if (s->ha == 0) {
+        // a row band whose reachable additional rows lie below the additional image: every origin is out of bounds, ring 0
+        // has no in-bounds probe -> None -> 0 (helpers.rs:49-51, depth_image.rs:120), as the unbanded call answers
+        if (ctx->main_ready) {
+            cudaEvent_t ev = ctx->main_ready;
+            ctx->main_ready = nullptr;
+            STEPTH_CUDA_TRY(ctx, cudaStreamWaitEvent(st, ev, 0));
+        }
+        STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(max_out, 0, sizeof(uint32_t) * s->n_pairs, st));
+        STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(d8_out, 0, (size_t)s->n_pairs * s->w * s->h, st));
+        return STEPTH_OK;
+    }
     const bool hier = !(params->flags & STEPTH_FLAG_LITERAL_SEARCH) && params->precision[0] && params->precision[1] && params->precision[2];
     if (ctx->main_ready && !hier) {   // only the tile search has work to do before it needs the main images
         cudaEvent_t ev = ctx->main_ready;
@@ -192,6 +204,37 @@ extern "C" int32_t stepth_cuda_dev_search_dense(stepth_ctx *ctx, void *stream, c
         ctx->main_ready = nullptr;
     }
     return rc;
+}
+
+// measurement aid: the in-order kernel with a counter of the probes the reference's scan order needs (every in-bounds pixel
+// of a ring once, up to and including the first match) -- what orc_last_unique_probes counts on the CPU
+extern "C" int32_t stepth_cuda_dev_count_probes(stepth_ctx *ctx, void *stream, const stepth_dev_shape *s,
+                                                const stepth_params *params, const uint8_t *main_rgba,
+                                                const uint8_t *add_rgb, uint8_t *d8_out, uint32_t *max_out,
+                                                uint64_t *probes_out) {
+    if (!ctx) return STEPTH_ERR_INVALID_ARG;
+    if (!s || !params_ok(params) || !main_rgba || !add_rgb || !d8_out || !max_out || !probes_out || s->n_pairs == 0 ||
+        s->w == 0 || s->h == 0 || s->wa == 0 || s->ha == 0 || (uint64_t)s->w * s->h > 0xffffffffull || ((uintptr_t)main_rgba & 3))
+        return set_err(ctx, STEPTH_ERR_INVALID_ARG, "dev_count_probes: null or invalid argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(max_out, 0, sizeof(uint32_t) * s->n_pairs, st));
+    STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(probes_out, 0, sizeof(uint64_t) * s->n_pairs, st));
+    if (params->precision[0] == 0 || params->precision[1] == 0 || params->precision[2] == 0)
+        return set_err(ctx, STEPTH_ERR_INVALID_ARG, "dev_count_probes: a zero precision has no probes to count here");
+    SearchArgs a = make_search_args(params);
+    a.main_rgba = main_rgba;
+    a.n_queries = s->w * s->h;
+    a.w = s->w; a.h = s->h; a.y0 = s->y0;
+    a.add_rgb = add_rgb;
+    a.wa = s->wa; a.ha = s->ha; a.add_y0 = s->add_y0;
+    a.add_img_h = s->add_img_h ? s->add_img_h : s->ha;
+    a.d8 = d8_out;
+    a.max_out = max_out;
+    a.probes_out = reinterpret_cast<unsigned long long *>(probes_out);
+    dim3 grid((a.n_queries + 255) / 256, s->n_pairs);
+    search_literal_kernel<<<grid, 256, 0, st>>>(a);
+    LAUNCH_CHECK(ctx);
+    return STEPTH_OK;
 }
 
 extern "C" int32_t stepth_cuda_dev_search_blocks(stepth_ctx *ctx, void *stream, const stepth_params *params,
@@ -369,16 +412,20 @@ int32_t ensure_host_small(stepth_ctx *ctx, size_t bytes) {
     } while (0)
 
 // depth_image.rs:110-134 (+ tail) for n pairs of one shape; `blocks` selects block mode (n == 1 only).
-int32_t run_pairs(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_rgba, uint32_t w, uint32_t h,
-                  const uint8_t *const *add_rgb, uint32_t wa, uint32_t ha, const stepth_block *blocks,
-                  size_t n_blocks, const stepth_params *params, uint8_t *const *depth_out, uint8_t *raw_d8_out,
-                  const uint8_t *const *rgba_in, uint8_t *const *rgba_out, uint8_t *const *mask_out,
-                  uint8_t *from_to_out, int32_t *status_out) {
+int32_t run_pairs_impl(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_rgba, uint32_t w, uint32_t h,
+                       const uint8_t *const *add_rgb, uint32_t wa, uint32_t ha, const stepth_block *blocks,
+                       size_t n_blocks, const stepth_params *params, uint8_t *const *depth_out, uint8_t *raw_d8_out,
+                       const uint8_t *const *rgba_in, uint8_t *const *rgba_out, uint8_t *const *mask_out,
+                       uint8_t *from_to_out, int32_t *status_out, std::vector<cudaEvent_t> &t_out) {
     const uint32_t flags = params->flags;
     const bool want_fg = (flags & STEPTH_FLAG_FOREGROUND) != 0;
     const bool want_apply = (flags & STEPTH_FLAG_APPLY) != 0;
     if (want_apply && (!want_fg || !rgba_out || !rgba_in))
         return set_err(ctx, STEPTH_ERR_INVALID_ARG, "APPLY needs FOREGROUND, rgba_in and rgba_out");
+    if (want_apply)   // per element: the single-pair entry points hand in the addresses of their own arguments
+        for (uint32_t i = 0; i < n; ++i)
+            if (!rgba_out[i] || !rgba_in[i])
+                return set_err(ctx, STEPTH_ERR_INVALID_ARG, "APPLY: pair %u has no rgba_in or no rgba_out buffer", i);
     STEPTH_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
     const size_t px = (size_t)w * h;
@@ -425,7 +472,7 @@ int32_t run_pairs(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_rgba, 
     // images follow (`split`)
     const bool split = !blocks;
     const bool piped = n_chunks > 1 || split;
-    std::vector<cudaEvent_t> t_out;  // trace only: end of each chunk's copy-out
+    // t_out (trace only): end of each chunk's copy-out; owned and destroyed by run_pairs
     if (ctx->trace && piped)
         for (uint32_t k = 0; k < n_chunks; ++k) {
             cudaEvent_t e;
@@ -539,7 +586,6 @@ int32_t run_pairs(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_rgba, 
             cudaEventElapsedTime(&b, ctx->events[2 * n_chunks], ctx->events[2 * k + 1]);
             cudaEventElapsedTime(&c, ctx->events[2 * n_chunks], t_out[k]);
             fprintf(stderr, "  chunk %u [%u,%u): %.3f %.3f %.3f\n", k, bounds[k], bounds[k + 1], a, b, c);
-            cudaEventDestroy(t_out[k]);
         }
     }
 
@@ -560,6 +606,29 @@ int32_t run_pairs(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_rgba, 
         return set_err(ctx, first_bad, "%s", why);
     }
     return STEPTH_OK;
+}
+
+// Every exit of the batch path goes through here: an error inside the chunk loop returns at once, possibly with device->host
+// copies into the caller's buffers still in flight and the context's chunk state (slot, main_ready) mid-batch.  The caller
+// owns those buffers again the moment this returns, so all four streams are drained and the state reset first.
+int32_t run_pairs(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_rgba, uint32_t w, uint32_t h,
+                  const uint8_t *const *add_rgb, uint32_t wa, uint32_t ha, const stepth_block *blocks,
+                  size_t n_blocks, const stepth_params *params, uint8_t *const *depth_out, uint8_t *raw_d8_out,
+                  const uint8_t *const *rgba_in, uint8_t *const *rgba_out, uint8_t *const *mask_out,
+                  uint8_t *from_to_out, int32_t *status_out) {
+    std::vector<cudaEvent_t> t_out;
+    const int32_t rc = run_pairs_impl(ctx, n, main_rgba, w, h, add_rgb, wa, ha, blocks, n_blocks, params, depth_out, raw_d8_out,
+                                      rgba_in, rgba_out, mask_out, from_to_out, status_out, t_out);
+    if (rc != STEPTH_OK) {
+        const std::string why = ctx->err;   // the drain must not replace the first error's text
+        for (cudaStream_t s : {ctx->copy_in, ctx->stream, ctx->stream2, ctx->copy_out})
+            if (s) cudaStreamSynchronize(s);
+        ctx->err = why;
+    }
+    ctx->slot = 0;
+    ctx->main_ready = nullptr;
+    for (cudaEvent_t e : t_out) cudaEventDestroy(e);
+    return rc;
 }
 
 }  // namespace

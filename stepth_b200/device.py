@@ -73,6 +73,42 @@ class DensePipeline:
                                                          _ffi.ptr(self.mask), _ffi.ptr(self.rgba_out)))
 
 
+class BlockPipeline:
+    """depth_image.rs:110-134 from a DiscretePixel list that already sits in HBM (block mode, one pair):
+    blocks [n_blocks] (20-byte records, as a u8 tensor [n_blocks, 20]), add_rgb [ha, wa, 3]."""
+
+    def __init__(self, ctx: Context, n_blocks: int, w: int, h: int, wa: int, ha: int, precision, max_rings: int = 255,
+                 flags: int = _ffi.RESAMPLE_U8):
+        self.ctx, self.nb, self.w, self.h, self.wa, self.ha = ctx, int(n_blocks), int(w), int(h), int(wa), int(ha)
+        self.flags = int(flags)
+        self.params = _ffi.make_params(precision, max_rings, flags)
+        dev = torch.device("cuda", ctx.device)
+        u8 = dict(dtype=torch.uint8, device=dev)
+        self.d8 = torch.empty(self.nb, **u8)
+        self.plane = torch.empty((1, h, w), **u8)
+        self.depth = torch.empty((1, h, w), **u8)
+        self.max = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.status = torch.zeros(1, dtype=torch.int32, device=dev)
+
+    def run(self, blocks: torch.Tensor, add_rgb: torch.Tensor, search_events=None) -> None:
+        assert blocks.is_cuda and blocks.dtype == torch.uint8 and tuple(blocks.shape) == (self.nb, 20)
+        assert tuple(add_rgb.shape) == (self.ha, self.wa, 3)
+        lib, ctx, st = self.ctx._lib, self.ctx, _stream_handle()
+        p = C.byref(self.params)
+        self.status.zero_()
+        if search_events is not None:
+            search_events[0].record()
+        ctx.check(lib.stepth_cuda_dev_search_blocks(ctx.handle, st, p, _ffi.ptr(add_rgb), self.wa, self.ha, _ffi.ptr(blocks),
+                                                    self.nb, _ffi.ptr(self.d8), _ffi.ptr(self.max)))
+        if search_events is not None:
+            search_events[1].record()
+        ctx.check(lib.stepth_cuda_dev_paint_blocks(ctx.handle, st, _ffi.ptr(blocks), _ffi.ptr(self.d8), self.nb, self.w, self.h,
+                                                   _ffi.ptr(self.plane)))
+        ctx.check(lib.stepth_cuda_dev_finish(ctx.handle, st, 1, self.w, self.h, _ffi.ptr(self.plane), 0, self.h,
+                                             _ffi.ptr(self.max), self.flags, _ffi.ptr(self.depth), 0, self.h, None,
+                                             _ffi.ptr(self.status)))
+
+
 def search_dense(ctx: Context, main_rgba: torch.Tensor, add_rgb: torch.Tensor, precision, max_rings=255, flags=0,
                  y0: int = 0, add_y0: int = 0, add_img_h: int | None = None, img_h: int | None = None):
     """K1 only: -> (d8 [n,h,w] u8, max [n] i32).  Band geometry (y0 / add_y0 / add_img_h) is for row-banded runs."""
@@ -126,3 +162,18 @@ def histogram(ctx: Context, data: torch.Tensor) -> torch.Tensor:
     hist = torch.zeros(256, dtype=torch.int32, device=data.device)
     ctx.check(ctx._lib.stepth_cuda_dev_histogram(ctx.handle, _stream_handle(), _ffi.ptr(data), data.numel(), _ffi.ptr(hist)))
     return hist
+
+
+def count_probes(ctx: Context, main_rgba: torch.Tensor, add_rgb: torch.Tensor, precision, max_rings=255, flags=0):
+    """Measurement aid: the in-order kernel with a probe counter -> (d8 [n,h,w], probes [n] i64): per pair, the in-bounds
+    pixels the reference's scan order (helpers.rs:26-47) visits up to and including each query's first match."""
+    n, h, w, _ = main_rgba.shape
+    _, ha, wa, _ = add_rgb.shape
+    d8 = torch.empty((n, h, w), dtype=torch.uint8, device=main_rgba.device)
+    mx = torch.zeros(n, dtype=torch.int32, device=main_rgba.device)
+    probes = torch.zeros(n, dtype=torch.int64, device=main_rgba.device)
+    shape = _ffi.DevShape(n, w, h, h, 0, wa, ha, 0, ha)
+    p = _ffi.make_params(precision, max_rings, flags)
+    ctx.check(ctx._lib.stepth_cuda_dev_count_probes(ctx.handle, _stream_handle(), C.byref(shape), C.byref(p), _ffi.ptr(main_rgba),
+                                                    _ffi.ptr(add_rgb), _ffi.ptr(d8), _ffi.ptr(mx), _ffi.ptr(probes)))
+    return d8, probes

@@ -155,6 +155,20 @@ def test_search_precision_edges(ctx, orc, prec):
         assert np.array_equal(gpu_raw(ctx, m, a, prec, 64, flags), ref), (prec, flags)
 
 
+def test_probe_counter_equals_the_oracle_count(ctx, orc):
+    """bench.py's algorithmic-work figure: the device-side count of the probes the reference order needs == the oracle's"""
+    from stepth_b200 import device
+
+    pairs = [synth_pair(k, 150, 90, seed=3 + i) for i, k in enumerate(("nat", "geo", "worst"))]
+    m = torch.from_numpy(np.stack([p[0] for p in pairs])).cuda()
+    a = torch.from_numpy(np.stack([p[1] for p in pairs])).cuda()
+    d8, probes = device.count_probes(ctx, m, a, P36, 64)
+    for i, (mi, ai) in enumerate(pairs):
+        ref, _ = orc.search_dense(mi, ai, P36, 64, threads=4, want_probes=True)
+        assert np.array_equal(d8[i].cpu().numpy(), ref)
+        assert int(probes[i]) == orc.last_unique_probes(), i
+
+
 def test_origin_outside_additional(ctx, orc):
     # additional much smaller than main/2: origins beyond it give None -> 0 (helpers.rs:49-51)
     m, a = rand_pair(64, 48, 10, 6, seed=5, levels=3)
@@ -446,7 +460,9 @@ def test_normalize_brightness_vs_oracle(ctx, orc):
 
 
 # ---- BASELINE.json's full sizes: size-independent properties + sampled oracle checks -----------------------------
-@pytest.mark.parametrize("kind,w,h,rings", [("nat", 1920, 1080, 128), ("geo", 1920, 1080, 128), ("nat", 3840, 2160, 256)])
+@pytest.mark.parametrize("kind,w,h,rings", [("nat", 1920, 1080, 128), ("geo", 1920, 1080, 128), ("nat", 3840, 2160, 256),
+                                            # 256 rings: coarse rings 16..32 take the per-lane window loop (S > 15)
+                                            ("geo", 3840, 2160, 256), ("worst", 3840, 2160, 256)])
 def test_full_size_production_equals_in_order_kernel(ctx, orc, kind, w, h, rings):
     import stepth_b200 as sb
     from stepth_b200 import device, synth
@@ -458,9 +474,21 @@ def test_full_size_production_equals_in_order_kernel(ctx, orc, kind, w, h, rings
     assert int(mx[0]) == int(d8.max())
     # sampled oracle check on the same bytes
     rng = np.random.default_rng(1)
-    idx = rng.choice(w * h, 3000, replace=False).astype(np.uint32)
+    idx = rng.choice(w * h, 3000 if kind == "nat" else 1600, replace=False).astype(np.uint32)
+    if kind == "worst":   # the queries that can see the planted pixel at (w/4, h/4) are the only non-zero ones
+        ys, xs = np.mgrid[h // 2 - 120:h // 2 + 120:11, w // 2 - 120:w // 2 + 120:11]
+        idx = np.concatenate([idx, (ys * w + xs).reshape(-1).astype(np.uint32)])
     sub, _ = orc.search_dense_subset(m.cpu().numpy(), a.cpu().numpy(), P36, idx, rings, threads=8)
     assert np.array_equal(d8[0].reshape(-1).cpu().numpy()[idx], sub)
+    assert (sub != 0).any()
+    # the FINISHED plane, whole, against the oracle's normalise + unit-scale Gaussian of the same raw distances
+    # (depth_image.rs:124-134): the streaming finish_vert / finish_horz path at 1920 / 3840 columns
+    norm, mx_ref = orc.normalise(d8[0].cpu().numpy())
+    assert mx_ref == int(mx[0])
+    want_depth = orc.gaussian_resample_unit(norm, orc.RESAMPLE_U8)
+    for mode_g, mode_o in ((sb.RESAMPLE_F32, orc.RESAMPLE_F32), (sb.RESAMPLE_OFF, orc.RESAMPLE_OFF)):
+        got, st = device.finish(ctx, d8, mx, h, mode_g)
+        assert int(st[0]) == 0 and np.array_equal(got[0].cpu().numpy(), orc.gaussian_resample_unit(norm, mode_o)), mode_g
     # the fused tail's invariants: invert is an involution, the mask is a pure function of depth and (from,to),
     # apply only ever clears, and clears exactly the masked-out pixels
     flags = sb.RESAMPLE_U8 | sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY
@@ -470,6 +498,7 @@ def test_full_size_production_equals_in_order_kernel(ctx, orc, kind, w, h, rings
     plain.run(m[None], a[None])
     torch.cuda.synchronize()
     assert int(pipe.status[0]) == 0
+    assert np.array_equal(plain.depth[0].cpu().numpy(), want_depth)
     assert torch.equal(pipe.depth, 255 - plain.depth)
     hist = torch.bincount(pipe.depth.reshape(-1).int(), minlength=256).int()
     assert torch.equal(hist, pipe.hist[0])
@@ -516,6 +545,81 @@ def test_full_size_worst_case_sampled(ctx, orc):
     got = d8[0].reshape(-1).cpu().numpy()[idx]
     assert np.array_equal(got, sub)
     assert (sub != 0).any() and int(mx[0]) > 0
+
+
+def test_batch_of_4k_pairs_sliced_like_the_bench(ctx, orc):
+    """configs[3]'s shape: 4K pairs, 256 rings, fused tail, more pairs than one launch sequence holds (the bench cuts a
+    rank's pairs into sequences of 16): pairs of the first and of the second sequence against the oracle."""
+    import stepth_b200 as sb
+    from stepth_b200 import device, synth
+
+    w, h, rings, n, sub = 3840, 2160, 256, 18, 16
+    flags = sb.RESAMPLE_U8 | sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY
+    pairs = [synth.make_pair("nat", w, h, 100 + i, device="cuda") for i in range(n)]
+    m = torch.stack([p[0] for p in pairs])
+    a = torch.stack([p[1] for p in pairs])
+    del pairs
+    pipes = {k: device.DensePipeline(ctx, k, w, h, w, h, P36, rings, flags) for k in (sub, n - sub)}
+    rng = np.random.default_rng(18)
+    for i0 in range(0, n, sub):
+        k = min(sub, n - i0)
+        pipe = pipes[k]
+        pipe.run(m[i0:i0 + k], a[i0:i0 + k])
+        torch.cuda.synchronize()
+        assert int(pipe.status.abs().sum()) == 0
+        for j in sorted({0, k - 1}):
+            mi, ai = m[i0 + j].cpu().numpy(), a[i0 + j].cpu().numpy()
+            idx = rng.choice(w * h, 1500, replace=False).astype(np.uint32)
+            subset, _ = orc.search_dense_subset(mi, ai, P36, idx, rings, threads=8)
+            raw = pipe.d8[j].cpu().numpy()
+            assert np.array_equal(raw.reshape(-1)[idx], subset), (i0, j)
+            norm, mx = orc.normalise(raw)
+            assert mx == int(pipe.max[j])
+            depth = orc.invert_depth(orc.gaussian_resample_unit(norm, orc.RESAMPLE_U8))
+            assert np.array_equal(pipe.depth[j].cpu().numpy(), depth), (i0, j)
+            mask, ft = orc.select_foreground(depth)
+            assert tuple(pipe.ranges[j, :2].tolist()) == ft
+            assert np.array_equal(pipe.mask[j].cpu().numpy(), mask)
+            assert np.array_equal(pipe.rgba_out[j].cpu().numpy(), orc.apply_mask(mi, mask))
+
+
+def test_giant_pair_in_row_bands_vs_oracle(ctx, orc):
+    """configs[4]'s shape on ONE GPU: the 16384x8192 pair cut into the 8 row bands the 8-GPU run uses (add_y0 != 0, halo
+    rows of the neighbours), band after band; raw distances sampled against the oracle on the whole image, the finished
+    plane compared whole."""
+    import stepth_b200 as sb
+    from stepth_b200 import bands, device, synth
+
+    w, h, rings = 16384, 8192, 256
+    m, a = synth.make_pair("nat", w, h, 1, device="cuda")
+    plan = bands.band_plan(h, h, rings, 8)
+    d8 = torch.empty((1, h, w), dtype=torch.uint8, device="cuda")
+    mx_all = torch.zeros(1, dtype=torch.int32, device="cuda")
+    for b in plan:
+        band_d8, mx = device.search_dense(ctx, m[None, b.y0:b.y1].contiguous(), a[None, b.ay0:b.ay1].contiguous(), P36, rings,
+                                          y0=b.y0, add_y0=b.ay0, add_img_h=h, img_h=h)
+        d8[0, b.y0:b.y1] = band_d8[0]
+        mx_all = torch.maximum(mx_all, mx.to(torch.int32))
+    rng = np.random.default_rng(5)
+    idx = rng.choice(w * h, 4000, replace=False).astype(np.uint32)
+    seam = np.concatenate([np.arange(b.y0 - 2, b.y0 + 2) for b in plan[1:]])           # rows either side of every seam
+    idx = np.concatenate([idx, (seam[:, None].astype(np.int64) * w + rng.integers(0, w, (len(seam), 40))).reshape(-1).astype(np.uint32)])
+    m_np, a_np = m.cpu().numpy(), a.cpu().numpy()
+    del m, a
+    subset, _ = orc.search_dense_subset(m_np, a_np, P36, idx, rings, threads=8)
+    raw = d8[0].cpu().numpy()
+    assert np.array_equal(raw.reshape(-1)[idx], subset)
+    del m_np, a_np
+    out = torch.empty((h, w), dtype=torch.uint8, device="cuda")
+    for b in plan:
+        s0, s1 = max(0, b.y0 - 3), min(h, b.y1 + 3)
+        depth, status = device.finish(ctx, d8[:, s0:s1].contiguous(), mx_all, h, sb.RESAMPLE_U8, src_y0=s0, out_y0=b.y0,
+                                      out_rows=b.y1 - b.y0)
+        assert int(status[0]) == 0
+        out[b.y0:b.y1] = depth[0]
+    norm, mx_ref = orc.normalise(raw)
+    assert mx_ref == int(mx_all[0])
+    assert np.array_equal(out.cpu().numpy(), orc.gaussian_resample_unit(norm, orc.RESAMPLE_U8))
 
 
 # ---- multi-GPU orchestration (stepth_b200/bands.py) on the CUDA stage API ---------------------------------------------
