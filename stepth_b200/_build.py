@@ -39,7 +39,7 @@ def is_stale() -> bool:
 
 
 def build(force: bool = False, verbose: bool = False, out: str | None = None, defs=()) -> str:
-    """`out` / `defs` build a tuning variant next to the product library (scratch/ sweeps; see _ffi.lib)."""
+    """`out` / `defs` build a tuning variant next to the product library (kernel sweeps; see _ffi.lib)."""
     if out is None and not force and not is_stale():
         return LIB_PATH
     out = out or LIB_PATH
