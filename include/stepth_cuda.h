@@ -19,6 +19,8 @@
  * Threading: one call at a time per context; different contexts may be used from different threads.
  * All `stepth_cuda_*` host-buffer calls are synchronous (they return after the device->host copies finish),
  * like the reference.  `stepth_cuda_dev_*` calls take DEVICE pointers and a CUDA stream and only enqueue work.
+ * Host buffers may be ordinary pageable memory (a Rust Vec<u8>): the batch path stages them through a page-locked ring of
+ * its own with a few copy threads (STEPTH_STAGE_THREADS, default 4); page-locked buffers are used in place.
  *
  * There is NO CPU fallback: every entry point fails with STEPTH_ERR_CUDA when no sm_100 device is usable.
  */
@@ -105,6 +107,13 @@ int32_t stepth_cuda_depth_dense_batch(stepth_ctx *ctx, uint32_t n_pairs, const u
                                       uint8_t *const *rgba_out, uint8_t *const *mask_out, uint8_t *from_to_out,
                                       int32_t *status_out);
 
+/* the same for main images held as RGB8 -- what `self.image.clone()...to_rgb8()` holds at depth_image.rs:105; the search never
+ * reads alpha, so depth-only calls (no STEPTH_FLAG_APPLY: that one returns RGBA pixels) upload 3 instead of 4 bytes per pixel. */
+int32_t stepth_cuda_depth_dense_batch_rgb(stepth_ctx *ctx, uint32_t n_pairs, const uint8_t *const *main_rgb,
+                                          uint32_t w, uint32_t h, const uint8_t *const *add_rgb, uint32_t wa,
+                                          uint32_t ha, const stepth_params *params, uint8_t *const *depth_out,
+                                          uint8_t *const *mask_out, uint8_t *from_to_out, int32_t *status_out);
+
 /* ---- tail operations, host buffers ----------------------------------------------------------------------- */
 int32_t stepth_cuda_invert_depth(stepth_ctx *ctx, uint8_t *depth_inout, size_t n);             /* :225-227 */
 /* ranges_out: 2*256 bytes, (min,max) per cluster; has_values_out = 0 for the zones<2 answer [(None,None)] */
@@ -145,7 +154,10 @@ size_t stepth_host_discretise_v0(const uint8_t *main_px, uint32_t stride, uint32
                                  stepth_block *blocks_out, size_t cap);
 
 /* ---- device-resident stage API (device pointers; work is enqueued on `stream`, a cudaStream_t) ------------ */
-/* Used by the batch / row-band orchestration (one process per GPU) and by the device-resident benchmark. */
+/* Used by the batch / row-band orchestration (one process per GPU) and by the device-resident benchmark.
+ * ONE stream in flight per context: the stages keep scratch in the context (match planes, work lists, the plane between the
+ * two finish passes), so calls on one context must be ordered -- the same stream, or streams the caller orders with events.
+ * Use one context per concurrent stream. */
 
 typedef struct {
     uint32_t n_pairs;  /* images in the batch (contiguous, identical shape)                          */

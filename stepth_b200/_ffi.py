@@ -69,6 +69,7 @@ SIGNATURES = {
     "stepth_cuda_depth_from_blocks": (_i32, [_vp, _u8p, _u32, _u32, _vp, _sz, _u32, _u32, _PP, _u8p, _u8p, _u8p, _u8p, _u8p, _u8p]),
     "stepth_cuda_depth_dense": (_i32, [_vp, _u8p, _u32, _u32, _u8p, _u32, _u32, _PP, _u8p, _u8p, _u8p, _u8p, _u8p]),
     "stepth_cuda_depth_dense_batch": (_i32, [_vp, _u32, _vp, _u32, _u32, _vp, _u32, _u32, _PP, _vp, _vp, _vp, _u8p, _i32p]),
+    "stepth_cuda_depth_dense_batch_rgb": (_i32, [_vp, _u32, _vp, _u32, _u32, _vp, _u32, _u32, _PP, _vp, _vp, _u8p, _i32p]),
     "stepth_cuda_invert_depth": (_i32, [_vp, _u8p, _sz]),
     "stepth_cuda_depth_split": (_i32, [_vp, _u8p, _sz, _u8, _u8p, C.POINTER(_u32), C.POINTER(_i32)]),
     "stepth_cuda_slice": (_i32, [_vp, _u8p, _sz, _i32, _i32, _u8p]),

@@ -170,16 +170,22 @@ class Context:
         return out
 
     def depth_dense_batch(self, mains, adds, precision, max_rings=255, flags=_ffi.RESAMPLE_U8, out=None):
-        """A batch of same-shape pairs.  `mains`/`adds` are sequences of host arrays (numpy or pinned torch).
+        """A batch of same-shape pairs.  `mains`/`adds` are sequences of host arrays (numpy or pinned torch); the main
+        images are RGBA8 [h,w,4] or -- for calls without FLAG_APPLY -- RGB8 [h,w,3] (depth_image.rs:105 holds RGB).
         Returns dict(depth=[...], mask=[...], rgba=[...], from_to=ndarray[n,2], status=ndarray[n])."""
         n = len(mains)
         if n == 0 or len(adds) != n:
             raise StepthIOError("Sizes don't match")
         h, w = mains[0].shape[:2]
         ha, wa = adds[0].shape[:2]
+        stride = int(mains[0].shape[2]) if len(mains[0].shape) == 3 else 0
+        if stride not in (3, 4):
+            raise StepthIOError("main images must be RGB8 or RGBA8")
         for m, a in zip(mains, adds):
-            if tuple(m.shape) != (h, w, 4) or tuple(a.shape) != (ha, wa, 3):
+            if tuple(m.shape) != (h, w, stride) or tuple(a.shape) != (ha, wa, 3):
                 raise StepthIOError("Sizes don't match")
+        if stride == 3 and flags & _ffi.FLAG_APPLY:
+            raise StepthIOError("FLAG_APPLY returns RGBA pixels: pass RGBA main images")
         p = _ffi.make_params(precision, max_rings, flags)
         out = out or {}
         depth = out.get("depth") or [np.empty((h, w), np.uint8) for _ in range(n)]
@@ -195,8 +201,12 @@ class Context:
 
         pm, pa, pd, pr, pk = parr(mains), parr(adds), parr(depth), parr(rgba), parr(mask)
         with self._lock:
-            rc = self._lib.stepth_cuda_depth_dense_batch(self._h, n, pm, w, h, pa, wa, ha, C.byref(p), pd, pr, pk,
-                                                         _ffi.ptr(ft), _ffi.ptr(status))
+            if stride == 3:
+                rc = self._lib.stepth_cuda_depth_dense_batch_rgb(self._h, n, pm, w, h, pa, wa, ha, C.byref(p), pd, pk,
+                                                                 _ffi.ptr(ft), _ffi.ptr(status))
+            else:
+                rc = self._lib.stepth_cuda_depth_dense_batch(self._h, n, pm, w, h, pa, wa, ha, C.byref(p), pd, pr, pk,
+                                                             _ffi.ptr(ft), _ffi.ptr(status))
             self.check(rc)
         return {"depth": depth, "mask": mask, "rgba": rgba, "from_to": ft, "status": status}
 

@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "finish.cuh"
+#include "staging.cuh"
 
 struct stepth_ctx {
     int device = 0;
@@ -43,6 +44,9 @@ struct stepth_ctx {
     Buf planes2, worklist2, work2;  // scratch set of slot 1 (work / work2: the plane between the two streaming finish passes)
     int finish_streaming = 1;       // STEPTH_FINISH_STREAMING: 0 = always the tiled finish kernel
     int two_streams = 1;     // STEPTH_TWO_STREAMS
+    stepth::Stager stager;   // pinned rings + copy threads for pageable caller buffers (batch path; created on first use)
+    int stage_threads = 4;   // STEPTH_STAGE_THREADS: copy threads (the caller included); 0 = hand pageable pointers to the driver
+    Buf main_rgb;            // RGB8 main images as uploaded by the *_rgb entry point, expanded to main_rgba on the device
     Buf planes;  // two-level match bit-planes of the additional image(s) (tiles.cuh), rebuilt by every search
     // small per-pair state: [max u32][hist 256 u32][status i32][n_out u32][ranges 512 B] per pair
     void *h_small = nullptr;  // pinned mirror

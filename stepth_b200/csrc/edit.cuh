@@ -15,6 +15,27 @@ __device__ __forceinline__ uint32_t scale_u8(uint32_t v, float mul) {
     return (uint32_t)t;                                                    // as u8: truncation
 }
 
+// RGB8 -> RGBA8 (alpha 255) for n pixels: the *_rgb entry points upload 3 bytes per main pixel (what to_rgb8() holds,
+// depth_image.rs:105) and the search reads whole words.  Four pixels per thread (three words in, four out) when the run
+// starts on a word; the rest byte-wise.
+__global__ void __launch_bounds__(256) rgb_to_rgba_kernel(const uint8_t *rgb, uint32_t *rgba, size_t n) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x, t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool words = (reinterpret_cast<uintptr_t>(rgb) & 3) == 0 && (reinterpret_cast<uintptr_t>(rgba) & 15) == 0;
+    const size_t quads = words ? n / 4 : 0;
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(rgb);
+    for (size_t q = t; q < quads; q += stride) {
+        const uint32_t w0 = src[3 * q], w1 = src[3 * q + 1], w2 = src[3 * q + 2];
+        uint4 o;
+        o.x = w0 | 0xff000000u;
+        o.y = __funnelshift_r(w0, w1, 24) | 0xff000000u;
+        o.z = __funnelshift_r(w1, w2, 16) | 0xff000000u;
+        o.w = (w2 >> 8) | 0xff000000u;
+        reinterpret_cast<uint4 *>(rgba)[q] = o;
+    }
+    for (size_t i = quads * 4 + t; i < n; i += stride)
+        rgba[i] = (uint32_t)rgb[3 * i] | ((uint32_t)rgb[3 * i + 1] << 8) | ((uint32_t)rgb[3 * i + 2] << 16) | 0xff000000u;
+}
+
 // mode 0: highlight_depth (plane = depth), mode 1: highlight_mask (plane = mask)
 __global__ void __launch_bounds__(256) highlight_kernel(const uint32_t *rgba_in, const uint8_t *plane, size_t n, uint32_t *rgba_out,
                                                         int mode) {

@@ -84,6 +84,7 @@ extern "C" int32_t stepth_cuda_ctx_create(int32_t device, stepth_ctx **ctx_out) 
     if (const char *ev = getenv("STEPTH_FINISH_STREAMING")) ctx->finish_streaming = atoi(ev);
     if (const char *ev = getenv("STEPTH_TRACE")) ctx->trace = atoi(ev);
     if (const char *ev = getenv("STEPTH_UPLOAD_FULL_ROWS")) ctx->upload_full_rows = atoi(ev);
+    if (const char *ev = getenv("STEPTH_STAGE_THREADS")) ctx->stage_threads = std::max(0, std::min(64, atoi(ev)));
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
         g_create_err = std::string("cudaStreamCreate failed: ") + cudaGetErrorString(e);
         delete ctx;
@@ -106,12 +107,14 @@ extern "C" void stepth_cuda_ctx_destroy(stepth_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     stepth_ctx::Buf *bufs[] = {&ctx->main_rgba, &ctx->add_rgb, &ctx->d8,   &ctx->depth, &ctx->mask, &ctx->rgba_out,
                                &ctx->blocks,    &ctx->plane,   &ctx->small, &ctx->u16a,  &ctx->u16b, &ctx->u16o,
-                               &ctx->work,      &ctx->planes, &ctx->worklist, &ctx->planes2, &ctx->worklist2, &ctx->work2};
+                               &ctx->work,      &ctx->planes, &ctx->worklist, &ctx->planes2, &ctx->worklist2, &ctx->work2,
+                               &ctx->main_rgb};
     for (auto *b : bufs)
         if (b->p) cudaFree(b->p);
     for (auto &kv : ctx->taps)
         if (kv.second.dev) cudaFree(kv.second.dev);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
+    ctx->stager.destroy();
     for (cudaEvent_t e : ctx->events) cudaEventDestroy(e);
     if (ctx->copy_in) cudaStreamDestroy(ctx->copy_in);
     if (ctx->copy_out) cudaStreamDestroy(ctx->copy_out);
@@ -416,7 +419,7 @@ int32_t run_pairs_impl(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_r
                        const uint8_t *const *add_rgb, uint32_t wa, uint32_t ha, const stepth_block *blocks,
                        size_t n_blocks, const stepth_params *params, uint8_t *const *depth_out, uint8_t *raw_d8_out,
                        const uint8_t *const *rgba_in, uint8_t *const *rgba_out, uint8_t *const *mask_out,
-                       uint8_t *from_to_out, int32_t *status_out, std::vector<cudaEvent_t> &t_out) {
+                       uint8_t *from_to_out, int32_t *status_out, std::vector<cudaEvent_t> &t_out, uint32_t main_stride) {
     const uint32_t flags = params->flags;
     const bool want_fg = (flags & STEPTH_FLAG_FOREGROUND) != 0;
     const bool want_apply = (flags & STEPTH_FLAG_APPLY) != 0;
@@ -450,6 +453,30 @@ int32_t run_pairs_impl(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_r
         TRY_RC(ensure(ctx, ctx->plane, px));
     }
     if (!blocks || want_apply) TRY_RC(ensure(ctx, ctx->main_rgba, px * 4 * n));
+    if (main_stride == 3) TRY_RC(ensure(ctx, ctx->main_rgb, px * 3 * n));
+    // Host buffers that are not page-locked (a Rust Vec<u8>, a numpy array) go through the library's pinned ring, filled and
+    // emptied by its copy threads (staging.cuh); page-locked ones are read and written by the DMA engines directly.
+    auto upload = [&](void *dev, const void *host, size_t src_pitch, size_t row_bytes, size_t rows, cudaStream_t s) -> int32_t {
+        if (ctx->stage_threads > 0 && row_bytes * rows >= (64u << 10) && (src_pitch == row_bytes || row_bytes <= STAGE_IN_RING / 2) &&
+            host_ptr_is_pageable(host)) {
+            STEPTH_CUDA_TRY(ctx, ctx->stager.ensure(ctx->stage_threads));
+            STEPTH_CUDA_TRY(ctx, ctx->stager.h2d(dev, host, src_pitch, row_bytes, rows, s));
+        } else if (src_pitch == row_bytes || rows == 1) {
+            STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(dev, host, row_bytes * rows, cudaMemcpyHostToDevice, s));
+        } else {
+            STEPTH_CUDA_TRY(ctx, cudaMemcpy2DAsync(dev, row_bytes, host, src_pitch, row_bytes, rows, cudaMemcpyHostToDevice, s));
+        }
+        return STEPTH_OK;
+    };
+    auto download = [&](void *host, const void *dev, size_t bytes, cudaStream_t s) -> int32_t {
+        if (ctx->stage_threads > 0 && bytes >= (64u << 10) && host_ptr_is_pageable(host)) {
+            STEPTH_CUDA_TRY(ctx, ctx->stager.ensure(ctx->stage_threads));
+            STEPTH_CUDA_TRY(ctx, ctx->stager.d2h(host, dev, bytes, s));
+        } else {
+            STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, s));
+        }
+        return STEPTH_OK;
+    };
     if (want_fg && mask_out) TRY_RC(ensure(ctx, ctx->mask, px * n));
     if (want_apply) TRY_RC(ensure(ctx, ctx->rgba_out, px * 4 * n));
 
@@ -497,21 +524,24 @@ int32_t run_pairs_impl(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_r
         const uint32_t i0 = bounds[k], i1 = bounds[k + 1], nc = i1 - i0;
         ctx->slot = two ? (int)(k & 1) : 0;   // chunks alternate between two compute streams, each with its own scratch
         st = ctx->slot ? ctx->stream2 : st0;
-        for (uint32_t i = i0; i < i1; ++i) {
-            if (wa_d == wa)
-                STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(d_add + add_bytes * i, add_rgb[i], add_bytes, cudaMemcpyHostToDevice, s_in));
-            else
-                STEPTH_CUDA_TRY(ctx, cudaMemcpy2DAsync(d_add + add_bytes * i, (size_t)wa_d * 3, add_rgb[i], (size_t)wa * 3,
-                                                       (size_t)wa_d * 3, ha_d, cudaMemcpyHostToDevice, s_in));
-        }
+        for (uint32_t i = i0; i < i1; ++i)   // the reachable window of each additional image (whole rows when it spans them)
+            TRY_RC(upload(d_add + add_bytes * i, add_rgb[i], (size_t)wa * 3, (size_t)wa_d * 3, ha_d, s_in));
         if (split) {   // the compute stream may start K0 now; K1 waits for the second event (ctx->main_ready)
             STEPTH_CUDA_TRY(ctx, cudaEventRecord(ctx->events[2 * n_chunks + 2 + k], s_in));
             STEPTH_CUDA_TRY(ctx, cudaStreamWaitEvent(st, ctx->events[2 * n_chunks + 2 + k], 0));
         }
         for (uint32_t i = i0; i < i1; ++i) {
             const uint8_t *rgba_src = blocks ? (want_apply ? rgba_in[i] : nullptr) : main_rgba[i];
-            if (rgba_src)
-                STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(d_main + px * 4 * i, rgba_src, px * 4, cudaMemcpyHostToDevice, s_in));
+            if (!rgba_src) continue;
+            if (main_stride == 3) TRY_RC(upload((uint8_t *)ctx->main_rgb.p + px * 3 * i, rgba_src, px * 3, px * 3, 1, s_in));
+            else TRY_RC(upload(d_main + px * 4 * i, rgba_src, px * 4, px * 4, 1, s_in));
+        }
+        if (main_stride == 3 && !blocks) {   // RGB8 mains: widened to the RGBA words the search reads, behind their upload
+            const size_t n_px = px * (size_t)nc;
+            const uint32_t grid = (uint32_t)std::min<size_t>((n_px / 4 + 255) / 256 + 1, (size_t)ctx->sm_count * 8);
+            rgb_to_rgba_kernel<<<grid, 256, 0, s_in>>>((const uint8_t *)ctx->main_rgb.p + px * 3 * i0,
+                                                       (uint32_t *)(d_main + px * 4 * i0), n_px);
+            LAUNCH_CHECK(ctx);
         }
         if (piped) {
             STEPTH_CUDA_TRY(ctx, cudaEventRecord(ctx->events[2 * k], s_in));
@@ -555,11 +585,9 @@ int32_t run_pairs_impl(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_r
             STEPTH_CUDA_TRY(ctx, cudaStreamWaitEvent(s_out, ctx->events[2 * k + 1], 0));
         }
         for (uint32_t i = i0; i < i1; ++i) {
-            STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(depth_out[i], d_depth + px * i, px, cudaMemcpyDeviceToHost, s_out));
-            if (want_fg && mask_out && mask_out[i])
-                STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(mask_out[i], d_mask + px * i, px, cudaMemcpyDeviceToHost, s_out));
-            if (want_apply && rgba_out[i])
-                STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(rgba_out[i], d_rgba + px * 4 * i, px * 4, cudaMemcpyDeviceToHost, s_out));
+            TRY_RC(download(depth_out[i], d_depth + px * i, px, s_out));
+            if (want_fg && mask_out && mask_out[i]) TRY_RC(download(mask_out[i], d_mask + px * i, px, s_out));
+            if (want_apply && rgba_out[i]) TRY_RC(download(rgba_out[i], d_rgba + px * 4 * i, px * 4, s_out));
         }
         if (!t_out.empty()) STEPTH_CUDA_TRY(ctx, cudaEventRecord(t_out[k], s_out));
     }
@@ -576,6 +604,11 @@ int32_t run_pairs_impl(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_r
     if (piped) {
         STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(s_in));
         STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(s_out));
+    }
+    if (ctx->stager.pool) {   // the staged results that are still in the ring reach the caller's buffers now
+        STEPTH_CUDA_TRY(ctx, ctx->stager.drain_out(true, true));
+        STEPTH_CUDA_TRY(ctx, ctx->stager.reap_in(true));
+        while (!ctx->stager.in.live.empty()) STEPTH_CUDA_TRY(ctx, ctx->stager.reap_in(true));
     }
     if (!t_out.empty()) {
         fprintf(stderr, "stepth trace: %u pairs in %u chunks%s (ms after the start: copy-in, compute, copy-out)\n", n, n_chunks,
@@ -615,14 +648,15 @@ int32_t run_pairs(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_rgba, 
                   const uint8_t *const *add_rgb, uint32_t wa, uint32_t ha, const stepth_block *blocks,
                   size_t n_blocks, const stepth_params *params, uint8_t *const *depth_out, uint8_t *raw_d8_out,
                   const uint8_t *const *rgba_in, uint8_t *const *rgba_out, uint8_t *const *mask_out,
-                  uint8_t *from_to_out, int32_t *status_out) {
+                  uint8_t *from_to_out, int32_t *status_out, uint32_t main_stride = 4) {
     std::vector<cudaEvent_t> t_out;
     const int32_t rc = run_pairs_impl(ctx, n, main_rgba, w, h, add_rgb, wa, ha, blocks, n_blocks, params, depth_out, raw_d8_out,
-                                      rgba_in, rgba_out, mask_out, from_to_out, status_out, t_out);
+                                      rgba_in, rgba_out, mask_out, from_to_out, status_out, t_out, main_stride);
     if (rc != STEPTH_OK) {
         const std::string why = ctx->err;   // the drain must not replace the first error's text
         for (cudaStream_t s : {ctx->copy_in, ctx->stream, ctx->stream2, ctx->copy_out})
             if (s) cudaStreamSynchronize(s);
+        ctx->stager.abandon();
         ctx->err = why;
     }
     ctx->slot = 0;
@@ -676,6 +710,24 @@ extern "C" int32_t stepth_cuda_depth_dense_batch(stepth_ctx *ctx, uint32_t n_pai
             return set_err(ctx, STEPTH_ERR_INVALID_ARG, "depth_dense_batch: pair %u has a null buffer", i);
     return run_pairs(ctx, n_pairs, main_rgba, w, h, add_rgb, wa, ha, nullptr, 0, params, depth_out, nullptr, main_rgba,
                      rgba_out, mask_out, from_to_out, status_out);
+}
+
+extern "C" int32_t stepth_cuda_depth_dense_batch_rgb(stepth_ctx *ctx, uint32_t n_pairs, const uint8_t *const *main_rgb,
+                                                     uint32_t w, uint32_t h, const uint8_t *const *add_rgb, uint32_t wa,
+                                                     uint32_t ha, const stepth_params *params, uint8_t *const *depth_out,
+                                                     uint8_t *const *mask_out, uint8_t *from_to_out, int32_t *status_out) {
+    if (!ctx) return STEPTH_ERR_INVALID_ARG;
+    if (!main_rgb || !add_rgb || !depth_out || !status_out || !params_ok(params) || n_pairs == 0 || w == 0 || h == 0 ||
+        wa == 0 || ha == 0)
+        return set_err(ctx, STEPTH_ERR_INVALID_ARG, "depth_dense_batch_rgb: null or invalid argument");
+    if (params->flags & STEPTH_FLAG_APPLY)
+        return set_err(ctx, STEPTH_ERR_INVALID_ARG, "depth_dense_batch_rgb: APPLY returns RGBA pixels and needs the RGBA entry point");
+    if ((uint64_t)w * h < 8) return set_err(ctx, STEPTH_ERR_TOO_FEW_BLOCKS, "fewer than 8 pixels: par_chunks_mut(0) panics");
+    for (uint32_t i = 0; i < n_pairs; ++i)
+        if (!main_rgb[i] || !add_rgb[i] || !depth_out[i])
+            return set_err(ctx, STEPTH_ERR_INVALID_ARG, "depth_dense_batch_rgb: pair %u has a null buffer", i);
+    return run_pairs(ctx, n_pairs, main_rgb, w, h, add_rgb, wa, ha, nullptr, 0, params, depth_out, nullptr, main_rgb, nullptr,
+                     mask_out, from_to_out, status_out, 3);
 }
 
 // ---- tail operations on host buffers -----------------------------------------------------------------------

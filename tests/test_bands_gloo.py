@@ -74,7 +74,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, w, h, rings, seed, q):
+def _worker(rank, world, port, w, h, rings, seed, q, add_h=None):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -83,9 +83,9 @@ def _worker(rank, world, port, w, h, rings, seed, q):
         from stepth_b200 import bands, synth
 
         m, a = synth.make_pair("nat", w, h, seed)
-        m, a = m.numpy(), a.numpy()
+        m, a = m.numpy(), a.numpy()[: add_h or h].copy()
         flags = sb.RESAMPLE_U8 | sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY
-        runner = bands.BandRunner(OracleStages(m, a, P36, rings), w, h, h, P36, rings, flags)
+        runner = bands.BandRunner(OracleStages(m, a, P36, rings), w, h, a.shape[0], P36, rings, flags)
         b = runner.band
         mb = torch.from_numpy(m[b.y0:b.y1].copy())[None]
         ab = torch.from_numpy(a[b.ay0:b.ay1].copy())[None]
@@ -100,8 +100,10 @@ def _worker(rank, world, port, w, h, rings, seed, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,w,h,rings", [(2, 64, 46, 12), (3, 40, 10, 6), (2, 64, 48, 12)])  # the last: equal bands (direct gather)
-def test_row_bands_over_gloo_equal_the_whole_image(orc, world, w, h, rings):
+@pytest.mark.parametrize("world,w,h,rings,add_h", [(2, 64, 46, 12, None), (3, 40, 10, 6, None),
+                                                   (2, 64, 48, 12, None),    # equal bands (direct gather)
+                                                   (2, 64, 80, 6, 10)])      # rank 1 can reach no additional row at all
+def test_row_bands_over_gloo_equal_the_whole_image(orc, world, w, h, rings, add_h):
     import stepth_b200 as sb  # noqa: F401
     from stepth_b200 import synth
 
@@ -109,7 +111,7 @@ def test_row_bands_over_gloo_equal_the_whole_image(orc, world, w, h, rings):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, w, h, rings, seed, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, w, h, rings, seed, q, add_h)) for r in range(world)]
     for p in procs:
         p.start()
     results = [q.get(timeout=300) for _ in range(world)]
@@ -117,7 +119,11 @@ def test_row_bands_over_gloo_equal_the_whole_image(orc, world, w, h, rings):
         p.join(timeout=60)
         assert p.exitcode == 0
     m, a = synth.make_pair("nat", w, h, seed)
-    m, a = m.numpy(), a.numpy()
+    m, a = m.numpy(), a.numpy()[: add_h or h].copy()
+    if add_h:
+        from stepth_b200.bands import band_plan
+
+        assert any(b.ay1 <= b.ay0 and b.y1 > b.y0 for b in band_plan(h, add_h, rings, world))
     whole = orc.invert_depth(orc.depth_dense(m, a, P36, rings, resample=orc.RESAMPLE_U8, threads=2))
     mask_ref, ft_ref = orc.select_foreground(whole)
     rgba_ref = orc.apply_mask(m, mask_ref)

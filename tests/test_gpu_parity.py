@@ -400,6 +400,88 @@ def test_batch_and_per_pair_status(ctx, orc):
         assert np.array_equal(out["rgba"][i], orc.apply_mask(m, mask))
 
 
+@pytest.mark.parametrize("threads", ["4", "1", "0"])
+def test_pageable_and_pinned_host_buffers_agree(orc, threads, monkeypatch):
+    """Ordinary (malloc) host memory goes through the library's pinned ring and copy threads, page-locked memory is used in
+    place: same bytes out, for every output, with images larger than a staged piece and more outputs than the ring holds."""
+    import stepth_b200 as sb
+
+    monkeypatch.setenv("STEPTH_STAGE_THREADS", threads)
+    monkeypatch.setenv("STEPTH_BATCH_CHUNKS", "3")
+    c = sb.Context(0)
+    n, w, h, rings = 7, 1536, 1100, 40          # main RGBA 6.8 MB (two pieces), additional window pitched
+    flags = sb.RESAMPLE_U8 | sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY
+    pairs = [synth_pair("nat", w, h, seed=40 + i) for i in range(n)]
+    pg = c.depth_dense_batch([p[0] for p in pairs], [p[1] for p in pairs], P36, rings, flags)
+    pin_m = [torch.from_numpy(p[0]).pin_memory() for p in pairs]
+    pin_a = [torch.from_numpy(p[1]).pin_memory() for p in pairs]
+    out = {"depth": [torch.empty((h, w), dtype=torch.uint8).pin_memory() for _ in range(n)],
+           "mask": [torch.empty((h, w), dtype=torch.uint8).pin_memory() for _ in range(n)],
+           "rgba": [torch.empty((h, w, 4), dtype=torch.uint8).pin_memory() for _ in range(n)]}
+    pn = c.depth_dense_batch(pin_m, pin_a, P36, rings, flags, out=out)
+    assert pg["status"].tolist() == [0] * n and pn["status"].tolist() == [0] * n
+    assert np.array_equal(pg["from_to"], pn["from_to"])
+    for i in range(n):
+        for k in ("depth", "mask", "rgba"):
+            assert np.array_equal(pg[k][i], pn[k][i].numpy()), (k, i)
+    m, a = pairs[n - 1]
+    depth = orc.invert_depth(orc.depth_dense(m, a, P36, rings, resample=orc.RESAMPLE_U8, threads=8))
+    mask, ft = orc.select_foreground(depth)
+    assert np.array_equal(pg["depth"][n - 1], depth) and np.array_equal(pg["mask"][n - 1], mask)
+    assert np.array_equal(pg["rgba"][n - 1], orc.apply_mask(m, mask))
+    # a failing call (the batch is rejected before any work) leaves the context usable
+    with pytest.raises(sb.StepthIOError):
+        c.depth_dense_batch([p[0] for p in pairs], [p[1][:-1] for p in pairs] , P36, rings, flags)
+    again = c.depth_dense_batch([pairs[0][0]], [pairs[0][1]], P36, rings, flags)
+    assert np.array_equal(again["depth"][0], pg["depth"][0])
+
+
+@pytest.mark.parametrize("w,h", [(232, 120), (233, 121), (1920, 1080)])
+def test_rgb_main_entry_point_equals_rgba(ctx, orc, w, h):
+    """depth_image.rs:105 holds the main image as RGB8: the *_rgb entry point uploads 3 bytes per pixel"""
+    import stepth_b200 as sb
+
+    n = 3
+    pairs = [synth_pair("nat" if i % 2 else "geo", w, h, seed=90 + i) for i in range(n)]
+    flags = sb.RESAMPLE_U8 | sb.FLAG_INVERT | sb.FLAG_FOREGROUND
+    a4 = ctx.depth_dense_batch([p[0] for p in pairs], [p[1] for p in pairs], P36, 64, flags)
+    a3 = ctx.depth_dense_batch([np.ascontiguousarray(p[0][..., :3]) for p in pairs], [p[1] for p in pairs], P36, 64, flags)
+    assert a3["status"].tolist() == a4["status"].tolist() == [0] * n
+    assert np.array_equal(a3["from_to"], a4["from_to"])
+    for i in range(n):
+        assert np.array_equal(a3["depth"][i], a4["depth"][i]) and np.array_equal(a3["mask"][i], a4["mask"][i])
+    want = orc.invert_depth(orc.depth_dense(pairs[0][0], pairs[0][1], P36, 64, resample=orc.RESAMPLE_U8, threads=8))
+    assert np.array_equal(a3["depth"][0], want)
+    with pytest.raises(sb.StepthIOError):
+        ctx.depth_dense_batch([np.ascontiguousarray(p[0][..., :3]) for p in pairs], [p[1] for p in pairs], P36, 64, flags | sb.FLAG_APPLY)
+
+
+def test_apply_needs_both_rgba_buffers(ctx):
+    """APPLY with a NULL rgba_in (block mode) or a NULL rgba_out is rejected, not silently dropped (C callers)"""
+    import ctypes as C
+
+    import stepth_b200 as sb
+    from stepth_b200 import _ffi
+
+    m, a = synth_pair("nat", 64, 48, seed=2)
+    blocks = sb.discretise_v0(m, P36, min_splits=6)
+    p = _ffi.make_params(P36, 32, sb.RESAMPLE_U8 | sb.FLAG_FOREGROUND | sb.FLAG_APPLY)
+    depth, rgba, mask, ft = np.empty((48, 64), np.uint8), np.empty((48, 64, 4), np.uint8), np.empty((48, 64), np.uint8), np.zeros(2, np.uint8)
+    lib = ctx._lib
+    rc = lib.stepth_cuda_depth_from_blocks(ctx.handle, _ffi.ptr(a), 64, 48, blocks.ctypes.data, len(blocks), 64, 48, C.byref(p),
+                                           _ffi.ptr(depth), None, None, _ffi.ptr(rgba), _ffi.ptr(mask), _ffi.ptr(ft))
+    assert rc == _ffi.ERR_INVALID_ARG
+    rc = lib.stepth_cuda_depth_from_blocks(ctx.handle, _ffi.ptr(a), 64, 48, blocks.ctypes.data, len(blocks), 64, 48, C.byref(p),
+                                           _ffi.ptr(depth), None, _ffi.ptr(m), None, _ffi.ptr(mask), _ffi.ptr(ft))
+    assert rc == _ffi.ERR_INVALID_ARG
+    rc = lib.stepth_cuda_depth_dense(ctx.handle, _ffi.ptr(m), 64, 48, _ffi.ptr(a), 64, 48, C.byref(p), _ffi.ptr(depth), None, None,
+                                     _ffi.ptr(mask), _ffi.ptr(ft))
+    assert rc == _ffi.ERR_INVALID_ARG
+    rc = lib.stepth_cuda_depth_dense(ctx.handle, _ffi.ptr(m), 64, 48, _ffi.ptr(a), 64, 48, C.byref(p), _ffi.ptr(depth), None,
+                                     _ffi.ptr(rgba), _ffi.ptr(mask), _ffi.ptr(ft))
+    assert rc == 0
+
+
 def test_device_pipeline_matches_host_api(ctx, orc):
     import stepth_b200 as sb
     from stepth_b200 import device
@@ -444,6 +526,25 @@ def test_row_bands_equal_whole_image(ctx, orc):
         depth, status = device.finish(ctx, d8[:, s0:s1].contiguous(), mx_all, h, 1, src_y0=s0, out_y0=y0, out_rows=y1 - y0)
         out[y0:y1] = depth[0]
     assert np.array_equal(out.cpu().numpy(), whole)
+
+
+def test_row_band_without_reachable_additional_rows(ctx, orc):
+    """a band whose origins all lie below the additional image: every query is None -> 0, as in the unbanded call"""
+    import stepth_b200 as sb
+    from stepth_b200 import bands
+
+    m, a = synth_pair("nat", 64, 80, seed=4)
+    a = a[:10].copy()
+    whole = gpu_raw(ctx, m, a, P36, 6)
+    assert np.array_equal(whole, orc.search_dense(m, a, P36, 6, threads=4))
+    plan = bands.band_plan(80, 10, 6, 2)
+    assert plan[1].ay1 <= plan[1].ay0
+    st = bands.DeviceStages(ctx)
+    mt, at = torch.from_numpy(m).cuda(), torch.from_numpy(a).cuda()
+    for b in plan:
+        d8, mx = st.search(mt[None, b.y0:b.y1].contiguous(), at[None, b.ay0:b.ay1].contiguous(), P36, 6, 0, b.y0, b.ay0, 10, 80)
+        assert np.array_equal(d8[0].cpu().numpy(), whole[b.y0:b.y1])
+    assert (whole[plan[1].y0:] == 0).all()
 
 
 def test_normalize_brightness_vs_oracle(ctx, orc):
