@@ -445,6 +445,37 @@ def time_e2e(env, step, steps, warmup, flush=False):
     return env.max_over_ranks(dt)
 
 
+def link_ceiling(env, h2d_bytes, d2h_bytes):
+    """the end-to-end roofline: ms this rank's share of one step's host<->device traffic takes with NO kernels -- page-locked
+    memory, uploads and downloads on two streams at once, every rank at the same time (max over ranks, best of 3)"""
+    torch = env.torch
+    piece = 32 << 20
+    cap = 768 << 20
+    h_in = torch.empty(max(1, min(h2d_bytes, cap)), dtype=torch.uint8).pin_memory()
+    h_out = torch.empty(max(1, min(d2h_bytes, cap)), dtype=torch.uint8).pin_memory()
+    d_in, d_out = torch.empty_like(h_in, device=env.dev), torch.empty_like(h_out, device=env.dev)
+    s_up, s_down = torch.cuda.Stream(), torch.cuda.Stream()
+
+    def run():
+        env.barrier()
+        t0 = time.perf_counter()
+        with torch.cuda.stream(s_up):
+            for o in range(0, h2d_bytes, piece):
+                a = o % h_in.numel()
+                n = min(piece, h_in.numel() - a, h2d_bytes - o)
+                d_in[a:a + n].copy_(h_in[a:a + n], non_blocking=True)
+        with torch.cuda.stream(s_down):
+            for o in range(0, d2h_bytes, piece):
+                a = o % h_out.numel()
+                n = min(piece, h_out.numel() - a, d2h_bytes - o)
+                h_out[a:a + n].copy_(d_out[a:a + n], non_blocking=True)
+        torch.cuda.synchronize()
+        return env.max_over_ranks((time.perf_counter() - t0) * 1e3)
+
+    run()
+    return min(run() for _ in range(3))
+
+
 def build_roofline(name, kind, wl, alg_bytes, pairs_per_launch, search_launch_ms, share, kernel_desc):
     hbm, which = peaks()
     achieved = alg_bytes / (search_launch_ms * 1e-3) / 1e9
@@ -647,6 +678,12 @@ def run_dense(env, name, kind, steps, warmup, main_line):
                "ms_per_step": round(e2e_ms / e2e_steps, 3), "steps": e2e_steps,
                "link_gbs_this_gpu": round((h2d + d2h) / (e2e_ms / e2e_steps * 1e-3) / 1e9, 2),
                "api": "stepth_cuda_depth_dense_batch (host buffers, pinned; chunks pipelined over copy/compute/copy streams)"}
+        if main_line:
+            floor_ms = link_ceiling(env, h2d, d2h)
+            tot = env.sum_over_ranks(h2d + d2h)
+            e2e["link_floor_ms"] = round(floor_ms, 3)
+            e2e["link_ceiling_gbs"] = round(tot / (floor_ms * 1e-3) / 1e9, 2)        # all ranks together, no kernels
+            e2e["frac_of_link_ceiling"] = round(floor_ms / (e2e_ms / e2e_steps), 4)
         host_last = out["depth"][last].numpy().copy()
         # the same call with ordinary pageable memory (what a Rust Vec<u8> is): the library stages it through its own
         # pinned ring.  Bounded to one launch sequence of pairs.

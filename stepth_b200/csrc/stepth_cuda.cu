@@ -457,7 +457,7 @@ int32_t run_pairs_impl(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_r
     // Host buffers that are not page-locked (a Rust Vec<u8>, a numpy array) go through the library's pinned ring, filled and
     // emptied by its copy threads (staging.cuh); page-locked ones are read and written by the DMA engines directly.
     auto upload = [&](void *dev, const void *host, size_t src_pitch, size_t row_bytes, size_t rows, cudaStream_t s) -> int32_t {
-        if (ctx->stage_threads > 0 && row_bytes * rows >= (64u << 10) && (src_pitch == row_bytes || row_bytes <= STAGE_IN_RING / 2) &&
+        if (ctx->stage_threads > 0 && row_bytes * rows >= (64u << 10) && (src_pitch == row_bytes || row_bytes <= STAGE_IN_RING / 4) &&
             host_ptr_is_pageable(host)) {
             STEPTH_CUDA_TRY(ctx, ctx->stager.ensure(ctx->stage_threads));
             STEPTH_CUDA_TRY(ctx, ctx->stager.h2d(dev, host, src_pitch, row_bytes, rows, s));
@@ -526,6 +526,7 @@ int32_t run_pairs_impl(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_r
         st = ctx->slot ? ctx->stream2 : st0;
         for (uint32_t i = i0; i < i1; ++i)   // the reachable window of each additional image (whole rows when it spans them)
             TRY_RC(upload(d_add + add_bytes * i, add_rgb[i], (size_t)wa * 3, (size_t)wa_d * 3, ha_d, s_in));
+        if (ctx->stager.pool) STEPTH_CUDA_TRY(ctx, ctx->stager.flush_in());   // staged pieces still filling: their DMAs go first
         if (split) {   // the compute stream may start K0 now; K1 waits for the second event (ctx->main_ready)
             STEPTH_CUDA_TRY(ctx, cudaEventRecord(ctx->events[2 * n_chunks + 2 + k], s_in));
             STEPTH_CUDA_TRY(ctx, cudaStreamWaitEvent(st, ctx->events[2 * n_chunks + 2 + k], 0));
@@ -536,6 +537,7 @@ int32_t run_pairs_impl(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_r
             if (main_stride == 3) TRY_RC(upload((uint8_t *)ctx->main_rgb.p + px * 3 * i, rgba_src, px * 3, px * 3, 1, s_in));
             else TRY_RC(upload(d_main + px * 4 * i, rgba_src, px * 4, px * 4, 1, s_in));
         }
+        if (ctx->stager.pool) STEPTH_CUDA_TRY(ctx, ctx->stager.flush_in());
         if (main_stride == 3 && !blocks) {   // RGB8 mains: widened to the RGBA words the search reads, behind their upload
             const size_t n_px = px * (size_t)nc;
             const uint32_t grid = (uint32_t)std::min<size_t>((n_px / 4 + 255) / 256 + 1, (size_t)ctx->sm_count * 8);
@@ -600,15 +602,12 @@ int32_t run_pairs_impl(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_r
     }
     STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_small, ctx->small.p, sm.bytes, cudaMemcpyDeviceToHost, st));
     if (raw_d8_out) STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(raw_d8_out, ctx->d8.p, n_q * n, cudaMemcpyDeviceToHost, st));
+    // everything is enqueued: the staged results reach the caller's buffers piece by piece as their DMAs complete
+    if (ctx->stager.pool) STEPTH_CUDA_TRY(ctx, ctx->stager.finish());
     STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(st));
     if (piped) {
         STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(s_in));
         STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(s_out));
-    }
-    if (ctx->stager.pool) {   // the staged results that are still in the ring reach the caller's buffers now
-        STEPTH_CUDA_TRY(ctx, ctx->stager.drain_out(true, true));
-        STEPTH_CUDA_TRY(ctx, ctx->stager.reap_in(true));
-        while (!ctx->stager.in.live.empty()) STEPTH_CUDA_TRY(ctx, ctx->stager.reap_in(true));
     }
     if (!t_out.empty()) {
         fprintf(stderr, "stepth trace: %u pairs in %u chunks%s (ms after the start: copy-in, compute, copy-out)\n", n, n_chunks,
