@@ -20,7 +20,7 @@
  * All `stepth_cuda_*` host-buffer calls are synchronous (they return after the device->host copies finish),
  * like the reference.  `stepth_cuda_dev_*` calls take DEVICE pointers and a CUDA stream and only enqueue work.
  * Host buffers may be ordinary pageable memory (a Rust Vec<u8>): the batch path stages them through a page-locked ring of
- * its own with a few copy threads (STEPTH_STAGE_THREADS, default 4); page-locked buffers are used in place.
+ * its own with a few copy threads (STEPTH_STAGE_THREADS, default min(8, cores / 2)); page-locked buffers are used in place.
  *
  * There is NO CPU fallback: every entry point fails with STEPTH_ERR_CUDA when no sm_100 device is usable.
  */

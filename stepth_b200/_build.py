@@ -26,7 +26,7 @@ def _nvcc() -> str:
 
 
 def sources():
-    return sorted(glob.glob(os.path.join(CSRC, "*.cu")) + glob.glob(os.path.join(CSRC, "*.cuh"))) + [
+    return sorted(glob.glob(os.path.join(CSRC, "*.cu")) + glob.glob(os.path.join(CSRC, "*.cuh")) + glob.glob(os.path.join(CSRC, "*.cpp"))) + [
         os.path.join(os.path.dirname(_HERE), "include", "stepth_cuda.h")
     ]
 
@@ -43,7 +43,8 @@ def build(force: bool = False, verbose: bool = False, out: str | None = None, de
     if out is None and not force and not is_stale():
         return LIB_PATH
     out = out or LIB_PATH
-    cmd = [_nvcc(), *NVCC_FLAGS, *[f"-D{d}" for d in defs], "-o", out, os.path.join(CSRC, "stepth_cuda.cu")]
+    cmd = [_nvcc(), *NVCC_FLAGS, *[f"-D{d}" for d in defs], "-o", out, os.path.join(CSRC, "stepth_cuda.cu"),
+           os.path.join(CSRC, "hostcopy.cpp")]
     if verbose:
         cmd += ["-Xptxas", "-v"]
     r = subprocess.run(cmd, capture_output=True, text=True)

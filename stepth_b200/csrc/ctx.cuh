@@ -45,7 +45,7 @@ struct stepth_ctx {
     int finish_streaming = 1;       // STEPTH_FINISH_STREAMING: 0 = always the tiled finish kernel
     int two_streams = 1;     // STEPTH_TWO_STREAMS
     stepth::Stager stager;   // pinned rings + copy threads for pageable caller buffers (batch path; created on first use)
-    int stage_threads = 4;   // STEPTH_STAGE_THREADS: copy threads (the caller included); 0 = hand pageable pointers to the driver
+    int stage_threads = 8;   // STEPTH_STAGE_THREADS: copy threads (the caller included; default min(8, cores / 2)); 0 = hand pageable pointers to the driver
     Buf main_rgb;            // RGB8 main images as uploaded by the *_rgb entry point, expanded to main_rgba on the device
     Buf planes;  // two-level match bit-planes of the additional image(s) (tiles.cuh), rebuilt by every search
     // small per-pair state: [max u32][hist 256 u32][status i32][n_out u32][ranges 512 B] per pair

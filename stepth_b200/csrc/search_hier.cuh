@@ -198,6 +198,42 @@ STEPTH_HD unsigned long long side_flags(const unsigned long long *plane, int wpl
     return m;
 }
 
+// ---- the first step: coarse rings 0 and 1 together -------------------------------------------------------------------
+// The 3x3 tile block around the origin's tile is three runs of (at most) three tiles in three consecutive tile rows: THREE
+// row-major windows give all nine occupancy flags -- the origin's own tile included, which ring 0 alone would test blind
+// (on a natural pair two out of three own tiles hold no match), and the two column sides of ring 1, which are single
+// tiles of the middle row -- where rings 0 and 1 walked separately cost one un-flagged tile test and four windows.
+struct Block3 {
+    uint32_t fa, fb, fc;  // flags of tile rows T0y-1, T0y, T0y+1; bit i <-> tile rlo + i
+    int rlo, rhi;         // the tile run, clipped to the grid
+};
+
+STEPTH_HD uint32_t row_flags3(const unsigned long long *plane, int wpl, int line, int n_lines, int lo, int hi, const HierQuery &q) {
+    if ((unsigned)line >= (unsigned)n_lines || lo > hi) return 0u;
+    const unsigned long long w = coarse_window(plane, (uint32_t)(line * wpl + (lo >> 5)), q);
+    return (uint32_t)(w >> (lo & 31)) & ((2u << (hi - lo)) - 1u);   // hi - lo <= 2
+}
+
+STEPTH_HD Block3 block3_flags(const HierView &v, const HierQuery &q, int T0x, int T0y) {
+    Block3 b;
+    b.rlo = T0x - 1 < 0 ? 0 : T0x - 1;
+    b.rhi = T0x + 1 > v.ntx - 1 ? v.ntx - 1 : T0x + 1;
+    b.fa = row_flags3(v.crp, v.nxw, T0y - 1, v.nty, b.rlo, b.rhi, q);
+    b.fb = row_flags3(v.crp, v.nxw, T0y, v.nty, b.rlo, b.rhi, q);
+    b.fc = row_flags3(v.crp, v.nxw, T0y + 1, v.nty, b.rlo, b.rhi, q);
+    return b;
+}
+// flag of tile TX of the middle row (0 when TX lies outside the run)
+STEPTH_HD uint32_t block3_mid(const Block3 &b, int TX) { return (TX < b.rlo || TX > b.rhi) ? 0u : (b.fb >> (TX - b.rlo)) & 1u; }
+
+// Every pixel outside the (2S+1)^2 tile block around the origin's tile lies at ring >= 8S + slack + 1, slack = the distance
+// from the origin to the nearest border of its own tile: after coarse ring S the walk is over once the best ring <= 8S + slack.
+STEPTH_HD int stop_slack(const HierQuery &q) {
+    const int lx = q.ox & 7, ly = q.oy & 7;
+    const int mx = lx < 7 - lx ? lx : 7 - lx, my = ly < 7 - ly ? ly : 7 - ly;
+    return mx < my ? mx : my;
+}
+
 // coarse rings [S0, S1): true when the answer is final, false when rings >= S1 still have to be walked.
 // Ring S: side 0 = tile row T0y+S, 1 = row T0y-S (tiles T0x-S .. T0x+S), 2 = tile column T0x+S, 3 = column T0x-S
 // (tiles T0y-S+1 .. T0y+S-1), all clipped to the grid.
@@ -207,10 +243,28 @@ STEPTH_HD bool hier_rings(const HierView &v, const HierQuery &q, int D, int S0, 
     const int Smax = (D + 6) >> 3;               // tiles of coarse ring S start at ring >= 8S - 7
     const int S_end = S1 < Smax + 1 ? S1 : Smax + 1;
     const int xmax = v.ntx - 1, ymax = v.nty - 1;
+    const int slack = stop_slack(q);
     for (int S = S0; S < S_end; ++S) {
         // the coarse square has left the tile grid on all four sides: nothing further out exists
         if (T0x - S < 0 && T0x + S > xmax && T0y - S < 0 && T0y + S > ymax) return true;
-        if (S == 0) {
+        if (S == 0 && S_end >= 2) {
+            // rings 0 and 1 from three row windows (see Block3)
+            const Block3 b = block3_flags(v, q, T0x, T0y);
+            if (block3_mid(b, T0x)) fine_test(v, q, T0x, T0y, D, tab_le, tab_ge, best);
+            if (best != KEY_NONE && (int)(best >> 12) <= slack) return true;
+            S = 1;
+            if (T0x - 1 < 0 && T0x + 1 > xmax && T0y - 1 < 0 && T0y + 1 > ymax) return true;
+            for (int side = 0; side < 2; ++side) {            // rows T0y+1, T0y-1
+                uint32_t m = side == 0 ? b.fc : b.fa;
+                while (m) {
+                    const int p = b.rlo + ffs32(m) - 1;
+                    m &= m - 1;
+                    fine_test(v, q, p, side == 0 ? T0y + 1 : T0y - 1, D, tab_le, tab_ge, best);
+                }
+            }
+            if (block3_mid(b, T0x + 1)) fine_test(v, q, T0x + 1, T0y, D, tab_le, tab_ge, best);
+            if (block3_mid(b, T0x - 1)) fine_test(v, q, T0x - 1, T0y, D, tab_le, tab_ge, best);
+        } else if (S == 0) {
             if ((unsigned)T0x < (unsigned)v.ntx && (unsigned)T0y < (unsigned)v.nty)
                 fine_test(v, q, T0x, T0y, D, tab_le, tab_ge, best);
         } else {
@@ -256,7 +310,7 @@ STEPTH_HD bool hier_rings(const HierView &v, const HierQuery &q, int D, int S0, 
                 }
             }
         }
-        if (best != KEY_NONE && (int)(best >> 12) <= 8 * S) return true;
+        if (best != KEY_NONE && (int)(best >> 12) <= 8 * S + slack) return true;
     }
     return S1 > Smax;
 }
@@ -419,12 +473,32 @@ __device__ __forceinline__ bool hier_rings_warp(bool walking, const uint8_t *pla
     const int Smax = (D + 6) >> 3;
     const int S_end = S1 < Smax + 1 ? S1 : Smax + 1;
     const int xmax = v.ntx - 1, ymax = v.nty - 1;
+    const int slack = walking ? stop_slack(q) : 0;
     bool final_ = !walking;
     for (int S = S0; S < S_end; ++S) {
         uint32_t f0 = 0, f1 = 0, f2 = 0, f3 = 0;
         int rlo = 0, clo = 0;
-        const bool go = walking && !final_;
-        if (go) {
+        bool go = walking && !final_;
+        if (S == 0 && S_end >= 2) {   // warp-uniform: rings 0 and 1 from three row windows (see Block3)
+            if (go) {
+                const Block3 b = block3_flags(v, q, T0x, T0y);
+                // the origin's own tile: every walking lane has at most this one test, nothing to pool
+                if (block3_mid(b, T0x)) fine_test(v, q, T0x, T0y, D, tab_le, tab_ge, best);
+                if ((best != KEY_NONE && (int)(best >> 12) <= slack) ||
+                    (T0x - 1 < 0 && T0x + 1 > xmax && T0y - 1 < 0 && T0y + 1 > ymax)) {
+                    final_ = true;
+                    go = false;
+                } else {
+                    rlo = b.rlo;
+                    clo = T0y;
+                    f0 = b.fc;
+                    f1 = b.fa;
+                    f2 = block3_mid(b, T0x + 1);
+                    f3 = block3_mid(b, T0x - 1);
+                }
+            }
+            S = 1;
+        } else if (go) {
             if (T0x - S < 0 && T0x + S > xmax && T0y - S < 0 && T0y + S > ymax) {
                 final_ = true;  // the coarse square has left the tile grid on all four sides
             } else if (S == 0) {
@@ -502,7 +576,7 @@ __device__ __forceinline__ bool hier_rings_warp(bool walking, const uint8_t *pla
             __syncwarp();
             best = ws->best[lane];
         }
-        if (go && best != KEY_NONE && (int)(best >> 12) <= 8 * S) final_ = true;
+        if (go && best != KEY_NONE && (int)(best >> 12) <= 8 * S + slack) final_ = true;
         if (__all_sync(0xffffffffu, final_)) return true;
     }
     return final_ || S1 > Smax;

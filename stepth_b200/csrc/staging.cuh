@@ -27,6 +27,8 @@
 
 #include <cuda_runtime.h>
 
+extern "C" void stepth_stream_copy(void *dst, const void *src, size_t n);   // hostcopy.cpp: non-temporal stores
+
 namespace stepth {
 
 // ---- a small pool of threads that run memcpy slices ----------------------------------------------------------------
@@ -103,9 +105,9 @@ class CopyPool {
         JobPtr job;
     };
     static void run(const Task &t) {
-        if (t.rows == 1) memcpy(t.dst, t.src, t.row_bytes);
+        if (t.rows == 1) stepth_stream_copy(t.dst, t.src, t.row_bytes);
         else
-            for (size_t r = 0; r < t.rows; ++r) memcpy(t.dst + r * t.dst_pitch, t.src + r * t.src_pitch, t.row_bytes);
+            for (size_t r = 0; r < t.rows; ++r) stepth_stream_copy(t.dst + r * t.dst_pitch, t.src + r * t.src_pitch, t.row_bytes);
         t.job->left.fetch_sub(1, std::memory_order_acq_rel);
     }
     bool pop(Task &t) {

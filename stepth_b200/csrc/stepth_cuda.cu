@@ -84,6 +84,7 @@ extern "C" int32_t stepth_cuda_ctx_create(int32_t device, stepth_ctx **ctx_out) 
     if (const char *ev = getenv("STEPTH_FINISH_STREAMING")) ctx->finish_streaming = atoi(ev);
     if (const char *ev = getenv("STEPTH_TRACE")) ctx->trace = atoi(ev);
     if (const char *ev = getenv("STEPTH_UPLOAD_FULL_ROWS")) ctx->upload_full_rows = atoi(ev);
+    ctx->stage_threads = (int)std::max(2u, std::min(8u, std::thread::hardware_concurrency() / 2));
     if (const char *ev = getenv("STEPTH_STAGE_THREADS")) ctx->stage_threads = std::max(0, std::min(64, atoi(ev)));
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
         g_create_err = std::string("cudaStreamCreate failed: ") + cudaGetErrorString(e);

@@ -462,21 +462,21 @@ def test_apply_needs_both_rgba_buffers(ctx):
     import stepth_b200 as sb
     from stepth_b200 import _ffi
 
-    m, a = synth_pair("nat", 64, 48, seed=2)
+    m, a = synth_pair("nat", 120, 80, seed=5)
     blocks = sb.discretise_v0(m, P36, min_splits=6)
     p = _ffi.make_params(P36, 32, sb.RESAMPLE_U8 | sb.FLAG_FOREGROUND | sb.FLAG_APPLY)
-    depth, rgba, mask, ft = np.empty((48, 64), np.uint8), np.empty((48, 64, 4), np.uint8), np.empty((48, 64), np.uint8), np.zeros(2, np.uint8)
+    depth, rgba, mask, ft = np.empty((80, 120), np.uint8), np.empty((80, 120, 4), np.uint8), np.empty((80, 120), np.uint8), np.zeros(2, np.uint8)
     lib = ctx._lib
-    rc = lib.stepth_cuda_depth_from_blocks(ctx.handle, _ffi.ptr(a), 64, 48, blocks.ctypes.data, len(blocks), 64, 48, C.byref(p),
+    rc = lib.stepth_cuda_depth_from_blocks(ctx.handle, _ffi.ptr(a), 120, 80, blocks.ctypes.data, len(blocks), 120, 80, C.byref(p),
                                            _ffi.ptr(depth), None, None, _ffi.ptr(rgba), _ffi.ptr(mask), _ffi.ptr(ft))
     assert rc == _ffi.ERR_INVALID_ARG
-    rc = lib.stepth_cuda_depth_from_blocks(ctx.handle, _ffi.ptr(a), 64, 48, blocks.ctypes.data, len(blocks), 64, 48, C.byref(p),
+    rc = lib.stepth_cuda_depth_from_blocks(ctx.handle, _ffi.ptr(a), 120, 80, blocks.ctypes.data, len(blocks), 120, 80, C.byref(p),
                                            _ffi.ptr(depth), None, _ffi.ptr(m), None, _ffi.ptr(mask), _ffi.ptr(ft))
     assert rc == _ffi.ERR_INVALID_ARG
-    rc = lib.stepth_cuda_depth_dense(ctx.handle, _ffi.ptr(m), 64, 48, _ffi.ptr(a), 64, 48, C.byref(p), _ffi.ptr(depth), None, None,
+    rc = lib.stepth_cuda_depth_dense(ctx.handle, _ffi.ptr(m), 120, 80, _ffi.ptr(a), 120, 80, C.byref(p), _ffi.ptr(depth), None, None,
                                      _ffi.ptr(mask), _ffi.ptr(ft))
     assert rc == _ffi.ERR_INVALID_ARG
-    rc = lib.stepth_cuda_depth_dense(ctx.handle, _ffi.ptr(m), 64, 48, _ffi.ptr(a), 64, 48, C.byref(p), _ffi.ptr(depth), None,
+    rc = lib.stepth_cuda_depth_dense(ctx.handle, _ffi.ptr(m), 120, 80, _ffi.ptr(a), 120, 80, C.byref(p), _ffi.ptr(depth), None,
                                      _ffi.ptr(rgba), _ffi.ptr(mask), _ffi.ptr(ft))
     assert rc == 0
 
