@@ -42,7 +42,7 @@ if ROOT not in sys.path:
 
 PRECISION = [36, 36, 36]           # u8::MAX / 7 (Readme.md:15)
 METRIC = "Mpx*disparities/sec"
-SUB = 16                           # most pairs per launch sequence (bounds the scratch in HBM)
+SUB = int(os.environ.get("STEPTH_BENCH_SUB", "16"))   # most pairs per launch sequence (bounds the scratch in HBM)
 
 # name -> shape of the workload.  pairs: per GPU when scaling == "weak", in total when "strong"
 WORKLOADS = {

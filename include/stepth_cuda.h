@@ -219,6 +219,50 @@ uint64_t stepth_cuda_launch_count(const stepth_ctx *ctx);
  * integer work (2 ops per probe of the reference order, src/helpers.rs:26-47) by it. */
 int32_t stepth_cuda_int_peak(stepth_ctx *ctx, int32_t logic_only, double *ops_per_second_out);
 
+/* ---- multi-GPU: pair batches dealt to the devices, or ONE giant pair in row bands ------------------------ */
+#define STEPTH_ERR_NCCL 101 /* NCCL missing or a collective failed; text in the owner's last_error()                 */
+
+/* main rows [out[0], out[1]) of rank `rank` of `n_ranks` for an image of h rows, and the additional rows [out[2], out[3]) those
+ * rows can reach: origins are half-coordinates (depth_image.rs:114-117), widened by max_rings - 1 (helpers.rs:26). */
+void stepth_host_band_plan(uint32_t h, uint32_t add_h, uint32_t max_rings, uint32_t n_ranks, uint32_t rank, uint32_t out[4]);
+
+/* One rank of a row-band group: a context + an NCCL communicator (one process per GPU; rank 0 makes the 128-byte id and hands
+ * it to the others by whatever channel the host has).  n_ranks == 1 needs no id and no NCCL. */
+typedef struct stepth_comm stepth_comm;
+int32_t stepth_cuda_comm_unique_id(uint8_t id_out[128]);
+int32_t stepth_cuda_comm_create(stepth_ctx *ctx, int32_t n_ranks, int32_t rank, const uint8_t id[128], stepth_comm **comm_out);
+void stepth_cuda_comm_destroy(stepth_comm *comm);
+
+/* This rank's share of depth_image.rs:110-134 (+ fused tail) for ONE pair whose main rows are banded over the group (device
+ * pointers, enqueued on `stream`; every rank of the group must make the same call).  w, h: the whole main image; wa: width of
+ * the additional rows held here; add_h: rows of the whole additional image.  main_band [rows, w, 4] and add_band [arows, wa, 3]
+ * are the rows stepth_host_band_plan gives this rank.  Exchanges (NCCL): all-reduce MAX of the normaliser (:124), 3-row halos
+ * of the raw distance plane for the Gaussian (:133), all-reduce SUM of the histogram for depth_split (:162-218), and -- when
+ * depth_full_out [h, w] is given -- an all-gather of the depth bands.  depth_band_out [rows, w]; mask_band_out / rgba_band_out
+ * optional (fused tail). */
+int32_t stepth_cuda_dev_depth_dense_band(stepth_comm *comm, void *stream, uint32_t w, uint32_t h, uint32_t wa, uint32_t add_h,
+                                         const stepth_params *params, const uint8_t *main_band, const uint8_t *add_band,
+                                         uint8_t *depth_band_out, uint8_t *depth_full_out, uint8_t *mask_band_out,
+                                         uint8_t *rgba_band_out);
+/* waits for `stream` and reports the last band call's status (0, 3 = max == 0, 5 / 6 = depth_split) and cluster 0's (from, to) */
+int32_t stepth_cuda_comm_band_result(stepth_comm *comm, void *stream, int32_t *status_out, uint8_t from_to_out[2]);
+
+/* One process driving several GPUs (what a Rust host links): a context per device, a host thread per device per call. */
+typedef struct stepth_multi stepth_multi;
+int32_t stepth_cuda_multi_create(const int32_t *devices, uint32_t n_devices, stepth_multi **multi_out);
+void stepth_cuda_multi_destroy(stepth_multi *multi);
+const char *stepth_cuda_multi_last_error(const stepth_multi *multi); /* multi may be NULL: last create() error */
+uint64_t stepth_cuda_multi_launch_count(const stepth_multi *multi);
+/* stepth_cuda_depth_dense_batch with pair i on device i mod n_devices; no collective on the data path */
+int32_t stepth_cuda_multi_depth_dense_batch(stepth_multi *multi, uint32_t n_pairs, const uint8_t *const *main_rgba, uint32_t w,
+                                            uint32_t h, const uint8_t *const *add_rgb, uint32_t wa, uint32_t ha,
+                                            const stepth_params *params, uint8_t *const *depth_out, uint8_t *const *rgba_out,
+                                            uint8_t *const *mask_out, uint8_t *from_to_out, int32_t *status_out);
+/* stepth_cuda_depth_dense for ONE pair too large (or too slow) for one GPU: row bands over the devices, host buffers */
+int32_t stepth_cuda_multi_depth_dense_banded(stepth_multi *multi, const uint8_t *main_rgba, uint32_t w, uint32_t h,
+                                             const uint8_t *add_rgb, uint32_t wa, uint32_t ha, const stepth_params *params,
+                                             uint8_t *depth_out, uint8_t *rgba_out, uint8_t *mask_out, uint8_t *from_to_out);
+
 /* Measurement aid (no reference counterpart): runs the in-order kernel (one thread per query, the probe order of
  * src/helpers.rs:26-47 with the duplicate probes dropped) and counts, per pair, the in-bounds pixels that order visits up to
  * and including the first match -- the "probes the reference order needs" of SURVEY.md 8(d).  d8_out / max_out as

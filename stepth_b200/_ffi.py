@@ -22,6 +22,7 @@ ERR_DEGENERATE_DEPTH = 5
 ERR_NO_CONVERGENCE = 6
 ERR_OUT_OF_BOUNDS = 7
 ERR_CUDA = 100
+ERR_NCCL = 101
 
 RESAMPLE_OFF, RESAMPLE_U8, RESAMPLE_F32 = 0, 1, 2
 FLAG_INVERT = 1 << 2
@@ -93,6 +94,18 @@ SIGNATURES = {
     "stepth_cuda_dev_histogram": (_i32, [_vp, _vp, _u8p, _sz, _u32p]),
     "stepth_cuda_launch_count": (C.c_uint64, [_vp]),
     "stepth_cuda_int_peak": (_i32, [_vp, _i32, C.POINTER(C.c_double)]),
+    "stepth_host_band_plan": (None, [_u32, _u32, _u32, _u32, _u32, C.POINTER(_u32 * 4)]),
+    "stepth_cuda_comm_unique_id": (_i32, [_u8p]),
+    "stepth_cuda_comm_create": (_i32, [_vp, _i32, _i32, _u8p, C.POINTER(_vp)]),
+    "stepth_cuda_comm_destroy": (None, [_vp]),
+    "stepth_cuda_dev_depth_dense_band": (_i32, [_vp, _vp, _u32, _u32, _u32, _u32, _PP, _u8p, _u8p, _u8p, _u8p, _u8p, _u8p]),
+    "stepth_cuda_comm_band_result": (_i32, [_vp, _vp, C.POINTER(_i32), _u8p]),
+    "stepth_cuda_multi_create": (_i32, [C.POINTER(_i32), _u32, C.POINTER(_vp)]),
+    "stepth_cuda_multi_destroy": (None, [_vp]),
+    "stepth_cuda_multi_last_error": (C.c_char_p, [_vp]),
+    "stepth_cuda_multi_launch_count": (C.c_uint64, [_vp]),
+    "stepth_cuda_multi_depth_dense_batch": (_i32, [_vp, _u32, _vp, _u32, _u32, _vp, _u32, _u32, _PP, _vp, _vp, _vp, _u8p, _i32p]),
+    "stepth_cuda_multi_depth_dense_banded": (_i32, [_vp, _u8p, _u32, _u32, _u8p, _u32, _u32, _PP, _u8p, _u8p, _u8p, _u8p]),
     "stepth_cuda_dev_count_probes": (_i32, [_vp, _vp, _SP, _PP, _u8p, _u8p, _u8p, _u32p, _vp]),
 }
 

@@ -44,24 +44,21 @@ class Band:
     ay1: int     # one past the last
 
 
-def band_plan(h: int, add_h: int, max_rings: int, world: int, align: int = 2) -> list[Band]:
-    """Cuts main rows [0, h) into `world` contiguous bands (multiples of `align` rows so that the two main rows that
-    share an origin row stay together where possible) and gives each the additional rows it can reach:
-    origin rows (y+1)/2 for y in [y0, y1) -> [(y0+1)/2, y1/2], widened by max_rings - 1 on both sides."""
+def band_plan(h: int, add_h: int, max_rings: int, world: int) -> list[Band]:
+    """Cuts main rows [0, h) into `world` contiguous bands (multiples of 2 rows so that the two main rows that share an
+    origin row stay together) and gives each the additional rows it can reach: origin rows (y+1)/2 for y in [y0, y1)
+    -> [(y0+1)/2, y1/2], widened by max_rings - 1 on both sides.  ONE implementation: the library's
+    `stepth_host_band_plan` (csrc/multi.cuh), which the C++ band path uses too."""
     if world < 1 or h < 1:
         raise ValueError("need at least one rank and one row")
-    units = (h + align - 1) // align
+    import ctypes as C
+
+    lib = _ffi.lib()
     bands = []
+    out = (C.c_uint32 * 4)()
     for r in range(world):
-        u0, u1 = units * r // world, units * (r + 1) // world
-        y0, y1 = min(h, u0 * align), min(h, u1 * align)
-        if y1 <= y0:
-            bands.append(Band(r, y0, y0, 0, 0))
-            continue
-        o0, o1 = (y0 + 1) // 2, y1 // 2          # first / last origin row (inclusive)
-        ay0 = max(0, o0 - (max_rings - 1))
-        ay1 = min(add_h, o1 + (max_rings - 1) + 1)
-        bands.append(Band(r, y0, y1, ay0, max(ay0, ay1)))
+        lib.stepth_host_band_plan(h, add_h, max_rings, world, r, C.byref(out))
+        bands.append(Band(r, int(out[0]), int(out[1]), int(out[2]), int(out[3])))
     return bands
 
 
@@ -238,3 +235,87 @@ class BandRunner:
         parts = [torch.empty_like(padded) for _ in range(self.world)]
         dist.all_gather(parts, padded, group=self.group)
         return torch.cat([parts[p.rank][:, : p.y1 - p.y0] for p in self.plan], dim=1).contiguous()
+
+
+class CommBandRunner:
+    """The row-band path below the C ABI (csrc/multi_api.cuh): this rank's `stepth_comm` (context + NCCL communicator created
+    from a 128-byte id that rank 0 makes and torch.distributed broadcasts) and `stepth_cuda_dev_depth_dense_band`, which
+    enqueues the search, the MAX all-reduce, the halo exchange, finish, the histogram all-reduce + tail and the band
+    all-gather on torch's current stream.  Python only allocates the tensors."""
+
+    def __init__(self, ctx, w: int, h: int, add_h: int, precision, max_rings: int, flags: int, wa: int | None = None, group=None):
+        import ctypes as C
+
+        self.ctx, self.C = ctx, C
+        self.w, self.h, self.add_h, self.wa = int(w), int(h), int(add_h), int(wa or w)
+        self.flags = int(flags)
+        self.params = _ffi.make_params(precision, max_rings, flags)
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.plan = band_plan(self.h, self.add_h, int(max_rings), self.world)
+        self.band = self.plan[self.rank]
+        lib = ctx._lib
+        uid = torch.zeros(128, dtype=torch.uint8)
+        if self.world > 1:
+            if self.rank == 0:
+                buf = (C.c_uint8 * 128)()
+                rc = lib.stepth_cuda_comm_unique_id(C.addressof(buf))
+                if rc:
+                    raise _ffi.StepthError(rc, lib.stepth_cuda_last_error(None).decode())
+                uid = torch.frombuffer(bytearray(buf), dtype=torch.uint8).clone()
+            dev = torch.device("cuda", ctx.device)
+            t = uid.to(dev)
+            dist.broadcast(t, src=0, group=group)
+            uid = t.cpu()
+        self._uid = uid.numpy().copy()
+        handle = C.c_void_p()
+        ctx.check(lib.stepth_cuda_comm_create(ctx.handle, self.world, self.rank, self._uid.ctypes.data, C.byref(handle)))
+        self._h = handle
+        dev = torch.device("cuda", ctx.device)
+        rows = self.band.y1 - self.band.y0
+        u8 = dict(dtype=torch.uint8, device=dev)
+        self.depth_band = torch.empty((1, rows, self.w), **u8)
+        self.fg, self.apply = bool(flags & _ffi.FLAG_FOREGROUND), bool(flags & _ffi.FLAG_APPLY)
+        self.mask_band = torch.empty((1, rows, self.w), **u8) if self.fg else None
+        self.rgba_band = torch.empty((1, rows, self.w, 4), **u8) if self.apply else None
+        self.depth_full = None
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.ctx._lib.stepth_cuda_comm_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def enqueue(self, main_band: torch.Tensor, add_band: torch.Tensor, gather_depth: bool = False) -> None:
+        """main_band [1, rows, w, 4], add_band [1, arows, wa, 3] of THIS rank (device tensors); asynchronous"""
+        b = self.band
+        assert tuple(main_band.shape) == (1, b.y1 - b.y0, self.w, 4) and tuple(add_band.shape) == (1, b.ay1 - b.ay0, self.wa, 3)
+        if gather_depth and self.depth_full is None:
+            self.depth_full = torch.empty((1, self.h, self.w), dtype=torch.uint8, device=main_band.device)
+        st = torch.cuda.current_stream().cuda_stream
+        self.ctx.check(self.ctx._lib.stepth_cuda_dev_depth_dense_band(
+            self._h, st, self.w, self.h, self.wa, self.add_h, self.C.byref(self.params), _ffi.ptr(main_band), _ffi.ptr(add_band),
+            _ffi.ptr(self.depth_band), _ffi.ptr(self.depth_full) if gather_depth else None, _ffi.ptr(self.mask_band),
+            _ffi.ptr(self.rgba_band)))
+
+    def result(self) -> dict:
+        """waits for the stream; -> status (+ from_to when the tail is fused)"""
+        C = self.C
+        status, ft = C.c_int32(0), (C.c_uint8 * 2)()
+        st = torch.cuda.current_stream().cuda_stream
+        self.ctx.check(self.ctx._lib.stepth_cuda_comm_band_result(self._h, st, C.byref(status), C.addressof(ft)))
+        out = {"status": int(status.value), "depth_band": self.depth_band}
+        if self.fg and out["status"] == 0:
+            out.update(from_to=(int(ft[0]), int(ft[1])), mask_band=self.mask_band, rgba_band=self.rgba_band)
+        if self.depth_full is not None:
+            out["depth"] = self.depth_full
+        return out
+
+    def run(self, main_band, add_band, gather_depth: bool = False) -> dict:
+        self.enqueue(main_band, add_band, gather_depth)
+        return self.result()

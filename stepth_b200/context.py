@@ -321,6 +321,90 @@ class Context:
         return out
 
 
+class Multi:
+    """One process driving several GPUs through the C ABI (`stepth_multi`: a context and a host thread per device; what a Rust
+    host links).  Pair batches are dealt to the devices without any collective; one giant pair runs in row bands."""
+
+    def __init__(self, devices):
+        self._lib = _ffi.lib()
+        self.devices = [int(d) for d in devices]
+        arr = (C.c_int32 * len(self.devices))(*self.devices)
+        h = C.c_void_p()
+        rc = self._lib.stepth_cuda_multi_create(arr, len(self.devices), C.byref(h))
+        if rc != _ffi.OK:
+            raise _ffi.StepthError(rc, (self._lib.stepth_cuda_multi_last_error(None) or b"").decode())
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.stepth_cuda_multi_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def launch_count(self) -> int:
+        return int(self._lib.stepth_cuda_multi_launch_count(self._h))
+
+    def _check(self, rc: int):
+        if rc == _ffi.OK:
+            return
+        msg = (self._lib.stepth_cuda_multi_last_error(self._h) or b"").decode()
+        if rc in _PANIC_TEXT:
+            raise StepthPanic(rc, _PANIC_TEXT[rc])
+        if rc in (_ffi.ERR_INVALID_ARG, _ffi.ERR_SIZE_MISMATCH):
+            raise StepthIOError(msg or "invalid argument")
+        raise _ffi.StepthError(rc, msg)
+
+    def depth_dense_batch(self, mains, adds, precision, max_rings=255, flags=_ffi.RESAMPLE_U8, out=None):
+        """Context.depth_dense_batch over all the devices: pair i runs on device i mod n"""
+        n = len(mains)
+        if n == 0 or len(adds) != n:
+            raise StepthIOError("Sizes don't match")
+        h, w = mains[0].shape[:2]
+        ha, wa = adds[0].shape[:2]
+        for m, a in zip(mains, adds):
+            if tuple(m.shape) != (h, w, 4) or tuple(a.shape) != (ha, wa, 3):
+                raise StepthIOError("Sizes don't match")
+        p = _ffi.make_params(precision, max_rings, flags)
+        out = out or {}
+        depth = out.get("depth") or [np.empty((h, w), np.uint8) for _ in range(n)]
+        mask = (out.get("mask") or [np.empty((h, w), np.uint8) for _ in range(n)]) if flags & _ffi.FLAG_FOREGROUND else None
+        rgba = (out.get("rgba") or [np.empty((h, w, 4), np.uint8) for _ in range(n)]) if flags & _ffi.FLAG_APPLY else None
+        ft = np.zeros((n, 2), np.uint8)
+        status = np.zeros(n, np.int32)
+
+        def parr(seq):
+            return None if seq is None else (C.c_void_p * n)(*[_ffi.ptr(x) for x in seq])
+
+        self._check(self._lib.stepth_cuda_multi_depth_dense_batch(self._h, n, parr(mains), w, h, parr(adds), wa, ha, C.byref(p),
+                                                                  parr(depth), parr(rgba), parr(mask), _ffi.ptr(ft), _ffi.ptr(status)))
+        return {"depth": depth, "mask": mask, "rgba": rgba, "from_to": ft, "status": status}
+
+    def depth_dense_banded(self, main_rgba, add_rgb, precision, max_rings=255, flags=_ffi.RESAMPLE_U8, out=None):
+        """Context.depth_dense for ONE pair in row bands over the devices (host buffers in and out)"""
+        main_rgba, add_rgb = _u8c(main_rgba, (4,)), _u8c(add_rgb, (3,))
+        h, w = main_rgba.shape[:2]
+        ha, wa = add_rgb.shape[:2]
+        p = _ffi.make_params(precision, max_rings, flags)
+        out = out or {}
+        res = {"depth": out.get("depth") if out.get("depth") is not None else np.empty((h, w), np.uint8)}
+        mask = (out.get("mask") if out.get("mask") is not None else np.empty((h, w), np.uint8)) if flags & _ffi.FLAG_FOREGROUND else None
+        rgba = (out.get("rgba") if out.get("rgba") is not None else np.empty((h, w, 4), np.uint8)) if flags & _ffi.FLAG_APPLY else None
+        ft = np.zeros(2, np.uint8)
+        self._check(self._lib.stepth_cuda_multi_depth_dense_banded(self._h, _ffi.ptr(main_rgba), w, h, _ffi.ptr(add_rgb), wa, ha,
+                                                                   C.byref(p), _ffi.ptr(res["depth"]), _ffi.ptr(rgba), _ffi.ptr(mask),
+                                                                   _ffi.ptr(ft)))
+        if mask is not None:
+            res["mask"], res["from_to"] = mask, (int(ft[0]), int(ft[1]))
+        if rgba is not None:
+            res["rgba"] = rgba
+        return res
+
+
 def discretise_v0(main_px, precision, min_splits: int = 16, max_splits: int | None = None) -> np.ndarray:
     """Host stand-in for disage::open::rgb_discrete (depth_image.rs:104-109); NOT disage (source absent)."""
     main_px = _u8c(main_px)

@@ -39,6 +39,8 @@ struct stepth_ctx {
                                        // main images are still on their way up while the planes of the additional ones are built)
     int trace = 0;  // STEPTH_TRACE=1: the batch entry point prints each chunk's copy-in / compute / copy-out end times to stderr
     int upload_full_rows = 0;  // host-buffer entry points upload whole rows of the additional image (STEPTH_UPLOAD_FULL_ROWS)
+    int near_tile = 0;     // 1: dense mode runs ring 0 + coarse rings 0..1 from TMA-staged tile records (search_tile.cuh) and resumes the walk at ring 2
+                           // (STEPTH_NEAR_TILE; measured slower than the walking near kernel so far: 2.59 vs 2.26 ms per 16 pairs 1080p)
     int near_compact = 1;  // the near kernel packs the queries that survive ring 0 into full warps (STEPTH_NEAR_COMPACT)
     int mid_rings = 0;   // > near_rings: a second resumption point (FAR-1 walks rings [near_rings, mid_rings)); 0 = the far stage runs once (STEPTH_MID_RINGS)
     Buf planes2, worklist2, work2;  // scratch set of slot 1 (work / work2: the plane between the two streaming finish passes)

@@ -177,3 +177,222 @@ extern "C" int32_t stepth_cuda_comm_band_result(stepth_comm *c, void *stream, in
     }
     return STEPTH_OK;
 }
+
+// ============================================================================================================
+// stepth_multi: one process, several GPUs (a context per device, a host thread per device per call)
+// ============================================================================================================
+struct stepth_multi {
+    std::vector<int> devices;
+    std::vector<stepth_ctx *> ctxs;
+    std::vector<stepth_comm *> comms;   // row-band group over all the devices
+    std::string err;
+};
+
+static thread_local std::string g_multi_err;
+
+extern "C" void stepth_cuda_multi_destroy(stepth_multi *m) {
+    if (!m) return;
+    for (auto *c : m->comms) stepth_cuda_comm_destroy(c);
+    for (auto *c : m->ctxs) stepth_cuda_ctx_destroy(c);
+    delete m;
+}
+
+extern "C" const char *stepth_cuda_multi_last_error(const stepth_multi *m) { return m ? m->err.c_str() : g_multi_err.c_str(); }
+
+extern "C" int32_t stepth_cuda_multi_create(const int32_t *devices, uint32_t n_devices, stepth_multi **multi_out) {
+    if (!multi_out) return STEPTH_ERR_INVALID_ARG;
+    *multi_out = nullptr;
+    if (!devices || n_devices == 0 || n_devices > 64) {
+        g_multi_err = "multi_create: null or empty device list";
+        return STEPTH_ERR_INVALID_ARG;
+    }
+    for (uint32_t i = 0; i < n_devices; ++i)
+        for (uint32_t j = 0; j < i; ++j)
+            if (devices[i] == devices[j]) {
+                g_multi_err = "multi_create: a device is listed twice";
+                return STEPTH_ERR_INVALID_ARG;
+            }
+    stepth_multi *m = new stepth_multi();
+    for (uint32_t i = 0; i < n_devices; ++i) {
+        stepth_ctx *c = nullptr;
+        const int32_t rc = stepth_cuda_ctx_create(devices[i], &c);
+        if (rc != STEPTH_OK) {
+            g_multi_err = stepth_cuda_last_error(nullptr);
+            stepth_cuda_multi_destroy(m);
+            return rc;
+        }
+        m->devices.push_back(devices[i]);
+        m->ctxs.push_back(c);
+    }
+    std::vector<ncclComm_t> nc(n_devices, nullptr);
+    if (n_devices > 1) {
+        NcclApi &n = nccl_api();
+        if (!n.lib) {
+            g_multi_err = n.why;
+            stepth_cuda_multi_destroy(m);
+            return STEPTH_ERR_NCCL;
+        }
+        const ncclResult_t r = n.CommInitAll(nc.data(), (int)n_devices, m->devices.data());
+        if (r != ncclSuccess) {
+            g_multi_err = std::string("ncclCommInitAll failed: ") + n.GetErrorString(r);
+            stepth_cuda_multi_destroy(m);
+            return STEPTH_ERR_NCCL;
+        }
+    }
+    for (uint32_t i = 0; i < n_devices; ++i) {
+        stepth_comm *c = nullptr;
+        comm_alloc(m->ctxs[i], (int32_t)n_devices, (int32_t)i, nc[i], &c);
+        m->comms.push_back(c);
+    }
+    *multi_out = m;
+    return STEPTH_OK;
+}
+
+extern "C" uint64_t stepth_cuda_multi_launch_count(const stepth_multi *m) {
+    uint64_t n = 0;
+    if (m)
+        for (auto *c : m->ctxs) n += c->launches;
+    return n;
+}
+
+// configs[3]: independent pairs dealt to the devices (pair i -> device i mod n), each device's share through the single-GPU
+// batch call on its own context and host thread: no collective anywhere on the data path
+extern "C" int32_t stepth_cuda_multi_depth_dense_batch(stepth_multi *m, uint32_t n_pairs, const uint8_t *const *main_rgba,
+                                                       uint32_t w, uint32_t h, const uint8_t *const *add_rgb, uint32_t wa,
+                                                       uint32_t ha, const stepth_params *params, uint8_t *const *depth_out,
+                                                       uint8_t *const *rgba_out, uint8_t *const *mask_out, uint8_t *from_to_out,
+                                                       int32_t *status_out) {
+    if (!m) return STEPTH_ERR_INVALID_ARG;
+    if (!main_rgba || !add_rgb || !depth_out || !status_out || n_pairs == 0) {
+        m->err = "multi_depth_dense_batch: null or invalid argument";
+        return STEPTH_ERR_INVALID_ARG;
+    }
+    const size_t nd = m->ctxs.size();
+    std::vector<int32_t> rcs(nd, STEPTH_OK);
+    std::vector<std::thread> th;
+    for (size_t d = 0; d < nd; ++d) {
+        th.emplace_back([&, d] {
+            std::vector<const uint8_t *> pm, pa;
+            std::vector<uint8_t *> pd, pr, pk;
+            std::vector<uint32_t> idx;
+            for (uint32_t i = (uint32_t)d; i < n_pairs; i += (uint32_t)nd) {
+                idx.push_back(i);
+                pm.push_back(main_rgba[i]);
+                pa.push_back(add_rgb[i]);
+                pd.push_back(depth_out[i]);
+                if (rgba_out) pr.push_back(rgba_out[i]);
+                if (mask_out) pk.push_back(mask_out[i]);
+            }
+            if (idx.empty()) return;
+            std::vector<int32_t> st(idx.size(), 0);
+            std::vector<uint8_t> ft(2 * idx.size(), 0);
+            rcs[d] = stepth_cuda_depth_dense_batch(m->ctxs[d], (uint32_t)idx.size(), pm.data(), w, h, pa.data(), wa, ha, params,
+                                                   pd.data(), rgba_out ? pr.data() : nullptr, mask_out ? pk.data() : nullptr,
+                                                   ft.data(), st.data());
+            for (size_t k = 0; k < idx.size(); ++k) {
+                status_out[idx[k]] = st[k];
+                if (from_to_out) {
+                    from_to_out[2 * idx[k]] = ft[2 * k];
+                    from_to_out[2 * idx[k] + 1] = ft[2 * k + 1];
+                }
+            }
+        });
+    }
+    for (auto &t : th) t.join();
+    for (size_t d = 0; d < nd; ++d)
+        if (rcs[d] != STEPTH_OK) {
+            m->err = std::string("device ") + std::to_string(m->devices[d]) + ": " + stepth_cuda_last_error(m->ctxs[d]);
+            return rcs[d];
+        }
+    return STEPTH_OK;
+}
+
+// configs[4]: ONE pair, main rows banded over the devices.  Every device uploads its band and the additional rows it can
+// reach, runs stepth_cuda_dev_depth_dense_band (NCCL for the three small exchanges) and writes its rows of the results
+// straight into the caller's buffers.
+extern "C" int32_t stepth_cuda_multi_depth_dense_banded(stepth_multi *m, const uint8_t *main_rgba, uint32_t w, uint32_t h,
+                                                        const uint8_t *add_rgb, uint32_t wa, uint32_t ha,
+                                                        const stepth_params *params, uint8_t *depth_out, uint8_t *rgba_out,
+                                                        uint8_t *mask_out, uint8_t *from_to_out) {
+    if (!m) return STEPTH_ERR_INVALID_ARG;
+    if (!main_rgba || !add_rgb || !depth_out || !params_ok(params) || w == 0 || h == 0 || wa == 0 || ha == 0) {
+        m->err = "multi_depth_dense_banded: null or invalid argument";
+        return STEPTH_ERR_INVALID_ARG;
+    }
+    if ((uint64_t)w * h < 8) {
+        m->err = "fewer than 8 pixels: par_chunks_mut(0) panics";
+        return STEPTH_ERR_TOO_FEW_BLOCKS;
+    }
+    const uint32_t flags = params->flags;
+    const bool want_fg = (flags & STEPTH_FLAG_FOREGROUND) != 0, want_apply = (flags & STEPTH_FLAG_APPLY) != 0;
+    if (want_apply && (!want_fg || !rgba_out)) {
+        m->err = "APPLY needs FOREGROUND and rgba_out";
+        return STEPTH_ERR_INVALID_ARG;
+    }
+    const size_t nd = m->ctxs.size();
+    // only the columns a query can reach are uploaded (origins are half-coordinates: depth_image.rs:114-117)
+    const uint32_t wa_d = std::min(wa, w / 2 + params->max_rings);
+    std::vector<int32_t> rcs(nd, STEPTH_OK), status(nd, 0);
+    std::vector<uint8_t> ft(2 * nd, 0);
+    std::vector<std::thread> th;
+    for (size_t d = 0; d < nd; ++d) {
+        th.emplace_back([&, d] {
+            stepth_ctx *ctx = m->ctxs[d];
+            stepth_comm *c = m->comms[d];
+            auto run = [&]() -> int32_t {
+                STEPTH_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+                cudaStream_t st = ctx->stream;
+                uint32_t pl[4];
+                band_plan(h, ha, params->max_rings, (uint32_t)nd, (uint32_t)d, pl);
+                const uint32_t y0 = pl[0], rows = pl[1] - pl[0], ay0 = pl[2], arows = pl[3] - pl[2];
+                const size_t px = (size_t)rows * w;
+                int32_t rc;
+                if ((rc = ensure(ctx, ctx->main_rgba, px * 4 + 16)) != STEPTH_OK) return rc;
+                if ((rc = ensure(ctx, ctx->add_rgb, (size_t)arows * wa_d * 3 + 16)) != STEPTH_OK) return rc;
+                if ((rc = ensure(ctx, ctx->depth, px + 16)) != STEPTH_OK) return rc;
+                if (want_fg && mask_out && (rc = ensure(ctx, ctx->mask, px + 16)) != STEPTH_OK) return rc;
+                if (want_apply && (rc = ensure(ctx, ctx->rgba_out, px * 4 + 16)) != STEPTH_OK) return rc;
+                if (arows) {
+                    if (wa_d == wa)
+                        STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->add_rgb.p, add_rgb + (size_t)ay0 * wa * 3, (size_t)arows * wa * 3,
+                                                             cudaMemcpyHostToDevice, st));
+                    else
+                        STEPTH_CUDA_TRY(ctx, cudaMemcpy2DAsync(ctx->add_rgb.p, (size_t)wa_d * 3, add_rgb + (size_t)ay0 * wa * 3,
+                                                               (size_t)wa * 3, (size_t)wa_d * 3, arows, cudaMemcpyHostToDevice, st));
+                }
+                if (rows) STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->main_rgba.p, main_rgba + (size_t)y0 * w * 4, px * 4, cudaMemcpyHostToDevice, st));
+                if ((rc = stepth_cuda_dev_depth_dense_band(c, st, w, h, wa_d, ha, params, (const uint8_t *)ctx->main_rgba.p,
+                                                           (const uint8_t *)ctx->add_rgb.p, (uint8_t *)ctx->depth.p, nullptr,
+                                                           want_fg && mask_out ? (uint8_t *)ctx->mask.p : nullptr,
+                                                           want_apply ? (uint8_t *)ctx->rgba_out.p : nullptr)) != STEPTH_OK)
+                    return rc;
+                if (rows) {
+                    STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(depth_out + (size_t)y0 * w, ctx->depth.p, px, cudaMemcpyDeviceToHost, st));
+                    if (want_fg && mask_out)
+                        STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(mask_out + (size_t)y0 * w, ctx->mask.p, px, cudaMemcpyDeviceToHost, st));
+                    if (want_apply)
+                        STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(rgba_out + (size_t)y0 * w * 4, ctx->rgba_out.p, px * 4, cudaMemcpyDeviceToHost, st));
+                }
+                return stepth_cuda_comm_band_result(c, st, &status[d], &ft[2 * d]);
+            };
+            rcs[d] = run();
+        });
+    }
+    for (auto &t : th) t.join();
+    for (size_t d = 0; d < nd; ++d)
+        if (rcs[d] != STEPTH_OK) {
+            m->err = std::string("device ") + std::to_string(m->devices[d]) + ": " + stepth_cuda_last_error(m->ctxs[d]);
+            return rcs[d];
+        }
+    // the status is a property of the whole image (max == 0, degenerate depth range): every device reports the same one
+    if (status[0] != STEPTH_OK) {
+        m->err = status[0] == STEPTH_ERR_DIV_BY_ZERO_MAX ? "max distance is 0: attempt to divide by zero (depth_image.rs:127)"
+                                                          : "depth_split failed on the depth range (depth_image.rs:212-216)";
+        return status[0];
+    }
+    if (want_fg && from_to_out) {
+        from_to_out[0] = ft[0];
+        from_to_out[1] = ft[1];
+    }
+    return STEPTH_OK;
+}

@@ -738,6 +738,8 @@ __global__ void __launch_bounds__(128, STEPTH_FAR_MINB) search_far_kernel(HierAr
     }
 }
 
+__global__ void search_tile_kernel(HierArgs a, int ty_first);   // search_tile.cuh
+
 // planes (K0) + search (K1) for n_pairs dense pairs, or for one block list (a.blocks != nullptr)
 inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const SearchArgs &a, uint32_t n_pairs) {
     if (a.wa > 0xffffu || a.add_img_h > 0xffffu)
@@ -786,9 +788,10 @@ inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const Search
     STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(wl1, 0, 64, st));
     h.wl_cap = (uint32_t)cap;
 
-    // NEAR: ring 0 + coarse rings 0..1
+    // NEAR: ring 0 + the first coarse rings
+    const bool tile_stage = !a.blocks && ctx->near_tile;   // dense mode: rings 0..1 from TMA-staged tile records (search_tile.cuh)
     h.S0 = 0;
-    h.S1 = ctx->near_rings;
+    h.S1 = tile_stage ? 2 : ctx->near_rings;
     h.wl_out = (uint2 *)(wl0 + 64);
     h.wl_out_count = (uint32_t *)wl0;
     // A CTA settles ring 0 for up to STEPTH_NEAR_KP patches before it walks; a launch that would not fill the SMs a few
@@ -797,7 +800,15 @@ inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const Search
     const uint32_t per_sm = units / (uint32_t)std::max(1, ctx->sm_count);
     int kp = !ctx->near_compact ? 0 : (per_sm >= 160 ? 4 : per_sm >= 80 ? 2 : 1);
     if (kp > STEPTH_NEAR_KP) kp = STEPTH_NEAR_KP;
-    if (a.blocks) {
+    if (tile_stage) {
+        // one CTA per two origin tiles: origins are (x+1)/2, (y+y0+1)/2 - add_y0 (depth_image.rs:114-117)
+        auto floor8 = [](int64_t v) { return (int)(v >= 0 ? v / 8 : -((-v + 7) / 8)); };
+        const int64_t oy_min = (int64_t)((a.y0 + 1) >> 1) - (int64_t)a.add_y0, oy_max = (int64_t)((a.y0 + a.h) >> 1) - (int64_t)a.add_y0;
+        const int ty_first = floor8(oy_min), n_ty = floor8(oy_max) - ty_first + 1;
+        const uint32_t n_tx = ((a.w >> 1) >> 3) + 1;
+        if (n_ty > 65535) return set_err(ctx, STEPTH_ERR_INVALID_ARG, "band taller than 1M rows");
+        search_tile_kernel<<<dim3((n_tx + 1) / 2, (uint32_t)n_ty, n_pairs), 256, 0, st>>>(h, ty_first);
+    } else if (a.blocks) {
         const uint32_t gx = (uint32_t)((a.n_queries + 255) / 256);
         if (kp == 4) search_near_kernel<true, 4><<<dim3((gx + 3) / 4, 1, 1), 256, 0, st>>>(h);
         else if (kp == 2) search_near_kernel<true, 2><<<dim3((gx + 1) / 2, 1, 1), 256, 0, st>>>(h);
@@ -817,12 +828,18 @@ inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const Search
     // FAR: one or two resumptions; the last one walks to the end
     // one resumption by default: with the pooled tile tests a second stage boundary no longer pays (16 pairs 1080p: nat 2.318 ->
     // 2.308 ms, worst case 6.59 -> 6.00 ms; one pair 0.260 -> 0.241 ms); STEPTH_MID_RINGS brings it back
-    const int mid = ctx->mid_rings;
     const uint32_t far_grid = (uint32_t)ctx->sm_count * 16;
     uint8_t *in = wl0, *out = wl1;
-    if (mid > h.S1) {
+    // resumption points between the first stage and the last: after the tile stage the walk resumes at coarse ring 2 and may be cut
+    // again at near_rings and at mid_rings; after the walking near kernel only at mid_rings
+    const int cuts[2] = {tile_stage ? ctx->near_rings : 0, ctx->mid_rings};
+    bool used_out = false;
+    for (int ci = 0; ci < 2; ++ci) {
+        const int cut = cuts[ci];
+        if (cut <= h.S1) continue;
+        if (used_out) STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(out, 0, 64, st));   // a list consumed two stages ago is the output again
         h.S0 = h.S1;
-        h.S1 = mid;
+        h.S1 = cut;
         h.wl_in = (const uint2 *)(in + 64);
         h.wl_in_count = (const uint32_t *)in;
         h.wl_in_cursor = (uint32_t *)in + 1;
@@ -833,6 +850,7 @@ inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const Search
         ctx->launches++;
         STEPTH_CUDA_TRY(ctx, cudaGetLastError());
         std::swap(in, out);
+        used_out = true;
     }
     h.S0 = h.S1;
     h.S1 = 1 << 20;

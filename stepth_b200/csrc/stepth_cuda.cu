@@ -9,6 +9,7 @@
 #include "ctx.cuh"
 #include "search_literal.cuh"
 #include "search_hier.cuh"
+#include "search_tile.cuh"
 #include "tail.cuh"
 #include "brightness.cuh"
 #include "intpeak.cuh"
@@ -79,6 +80,7 @@ extern "C" int32_t stepth_cuda_ctx_create(int32_t device, stepth_ctx **ctx_out) 
     if (const char *ev = getenv("STEPTH_NEAR_RINGS")) ctx->near_rings = std::max(1, atoi(ev));  // tuning knobs
     if (const char *ev = getenv("STEPTH_MID_RINGS")) ctx->mid_rings = atoi(ev);
     if (const char *ev = getenv("STEPTH_NEAR_COMPACT")) ctx->near_compact = atoi(ev);
+    if (const char *ev = getenv("STEPTH_NEAR_TILE")) ctx->near_tile = atoi(ev);
     if (const char *ev = getenv("STEPTH_BATCH_CHUNKS")) ctx->batch_chunks = atoi(ev);
     if (const char *ev = getenv("STEPTH_TWO_STREAMS")) ctx->two_streams = atoi(ev);
     if (const char *ev = getenv("STEPTH_FINISH_STREAMING")) ctx->finish_streaming = atoi(ev);
@@ -1072,3 +1074,4 @@ extern "C" size_t stepth_host_discretise_v0(const uint8_t *main_px, uint32_t str
     d.rec(0, 0, w, h, 0);
     return d.n;
 }
+#include "multi_api.cuh"

@@ -88,6 +88,10 @@ def test_search_seeded_random_cases(ctx, orc, seed):
     {"STEPTH_NEAR_RINGS": "3", "STEPTH_MID_RINGS": "3"},
     {"STEPTH_NEAR_RINGS": "40", "STEPTH_MID_RINGS": "0"},
     {"STEPTH_NEAR_COMPACT": "0"},
+    {"STEPTH_NEAR_TILE": "0"},
+    {"STEPTH_NEAR_TILE": "0", "STEPTH_NEAR_RINGS": "1", "STEPTH_MID_RINGS": "4"},
+    {"STEPTH_NEAR_TILE": "1", "STEPTH_NEAR_RINGS": "2", "STEPTH_MID_RINGS": "0"},
+    {"STEPTH_NEAR_TILE": "1", "STEPTH_NEAR_RINGS": "3", "STEPTH_MID_RINGS": "9"},
     {"STEPTH_BATCH_CHUNKS": "3", "STEPTH_TWO_STREAMS": "0", "STEPTH_TRACE": "1"},
     {"STEPTH_BATCH_CHUNKS": "16", "STEPTH_UPLOAD_FULL_ROWS": "1", "STEPTH_FINISH_STREAMING": "0"},
 ])
@@ -738,6 +742,55 @@ def test_band_runner_one_rank_equals_host_api(ctx, orc):
     assert np.array_equal(out["rgba_band"][0].cpu().numpy(), host["rgba"])
 
 
+def test_multi_handle_equals_one_context(ctx, orc):
+    """`stepth_multi` (one process, a context + host thread per device) over every GPU of the box: pair batches dealt to the
+    devices and ONE pair in row bands, against the single-context calls.  With one GPU the same code runs on one device."""
+    import stepth_b200 as sb
+
+    devs = list(range(torch.cuda.device_count()))
+    mu = sb.Multi(devs)
+    flags = sb.RESAMPLE_U8 | sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY
+    pairs = [synth_pair("nat" if i % 3 else "geo", 200, 120, seed=50 + i) for i in range(2 * len(devs) + 1)]
+    got = mu.depth_dense_batch([p[0] for p in pairs], [p[1] for p in pairs], P36, 64, flags)
+    want = ctx.depth_dense_batch([p[0] for p in pairs], [p[1] for p in pairs], P36, 64, flags)
+    assert got["status"].tolist() == want["status"].tolist() and np.array_equal(got["from_to"], want["from_to"])
+    for i in range(len(pairs)):
+        for k in ("depth", "mask", "rgba"):
+            assert np.array_equal(got[k][i], want[k][i]), (k, i)
+    # one pair in row bands (each band >= 3 rows); a shorter additional image so that the last bands reach nothing
+    for (w, h, ha, rings) in [(320, 250, 250, 48), (64, 96, 12, 6)]:
+        m, a = synth_pair("nat", w, h, seed=9)
+        a = a[:ha].copy()
+        one = ctx.depth_dense(m, a, P36, rings, flags)
+        banded = mu.depth_dense_banded(m, a, P36, rings, flags)
+        assert banded["from_to"] == one["from_to"]
+        for k in ("depth", "mask", "rgba"):
+            assert np.array_equal(banded[k], one[k]), (k, w, h)
+    same = np.full((40, 64, 3), 50, np.uint8)
+    with pytest.raises(sb.StepthPanic) as e:      # max == 0 is a property of the whole image: every band reports it
+        mu.depth_dense_banded(rgba_of(same), same, P36, 32, sb.RESAMPLE_U8)
+    assert e.value.code == 3
+    assert mu.launch_count() > 0
+    mu.close()
+
+
+def test_comm_band_runner_one_rank_equals_host_api(ctx, orc):
+    """the band function below the boundary (stepth_cuda_dev_depth_dense_band) with a group of one"""
+    import stepth_b200 as sb
+    from stepth_b200 import bands
+
+    m, a = synth_pair("nat", 120, 90, seed=33)
+    flags = sb.RESAMPLE_U8 | sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY
+    host = ctx.depth_dense(m, a, P36, 40, flags)
+    runner = bands.CommBandRunner(ctx, 120, 90, 90, P36, 40, flags)
+    out = runner.run(torch.from_numpy(m).cuda()[None], torch.from_numpy(a).cuda()[None], gather_depth=True)
+    assert out["status"] == 0 and out["from_to"] == host["from_to"]
+    for got, want in ((out["depth_band"], host["depth"]), (out["depth"], host["depth"]), (out["mask_band"], host["mask"]),
+                      (out["rgba_band"], host["rgba"])):
+        assert np.array_equal(got[0].cpu().numpy(), want)
+    runner.close()
+
+
 def _band_worker(rank, world, port, w, h, rings, q):
     import os
 
@@ -756,11 +809,18 @@ def _band_worker(rank, world, port, w, h, rings, q):
         flags = sb.RESAMPLE_U8 | sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY
         runner = bands.BandRunner(bands.DeviceStages(c), w, h, h, P36, rings, flags)
         b = runner.band
-        out = runner.run(m[None, b.y0:b.y1].cuda().contiguous(), a[None, b.ay0:b.ay1].cuda().contiguous(), gather_depth=True)
+        mb, ab = m[None, b.y0:b.y1].cuda().contiguous(), a[None, b.ay0:b.ay1].cuda().contiguous()
+        out = runner.run(mb, ab, gather_depth=True)
         torch.cuda.synchronize()
+        # the same through the C ABI's own communicator (csrc/multi_api.cuh: NCCL called by the library)
+        crun = bands.CommBandRunner(c, w, h, h, P36, rings, flags)
+        cout = crun.run(mb, ab, gather_depth=True)
+        same = (cout["status"] == out["status"] and cout.get("from_to") == out.get("from_to")
+                and all(torch.equal(cout[k], out[k]) for k in ("depth", "depth_band", "mask_band", "rgba_band")))
+        crun.close()
         q.put({"rank": rank, "band": (b.y0, b.y1), "status": out["status"], "from_to": out.get("from_to"),
                "depth": out["depth"][0].cpu().numpy(), "mask_band": out["mask_band"][0].cpu().numpy(),
-               "rgba_band": out["rgba_band"][0].cpu().numpy()})
+               "rgba_band": out["rgba_band"][0].cpu().numpy(), "comm_runner_same": bool(same)})
     finally:
         dist.destroy_process_group()
 
@@ -794,6 +854,7 @@ def test_row_bands_over_nccl_equal_one_gpu(ctx, orc):
     for r in results:
         y0, y1 = r["band"]
         assert r["status"] == 0 and r["from_to"] == host["from_to"]
+        assert r["comm_runner_same"], "stepth_cuda_dev_depth_dense_band disagrees with the torch.distributed orchestration"
         assert np.array_equal(r["depth"], host["depth"])
         assert np.array_equal(r["mask_band"], host["mask"][y0:y1])
         assert np.array_equal(r["rgba_band"], host["rgba"][y0:y1])
