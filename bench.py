@@ -274,7 +274,7 @@ def describe(name, wl, kind, world):
     w, h = wl["w"], wl["h"]
     if wl["mode"] == "bands":
         return workload_config(name, wl, kind, world, 1, 1, "inputs larger than L2",
-                               f"row bands x{world}: allreduce(MAX) + 3-row halo exchange + all-gather of depth bands")
+                               f"row bands x{world}: allreduce(MAX) + 3-row halo exchange + all-gather of depth bands (NCCL, called by the library)")
     total = pairs if wl["scaling"] == "strong" else pairs * world
     mine = (pairs + world - 1) // world if wl["scaling"] == "strong" else pairs
     in_mb = mine * 7 * w * h / 1e6
@@ -836,18 +836,20 @@ def run_blocks(env, name, kind, steps, warmup, main_line):
 # GPU arm: one giant pair in row bands (configs[4])
 # ---------------------------------------------------------------------------------------------------------------
 def run_giant(env, name, kind, steps, warmup, main_line):
-    """ONE pair, main rows banded over the ranks (bands.BandRunner): MAX all-reduce of the normaliser, 3-row halo exchange,
-    and an all-gather of the depth bands so that every GPU ends with the assembled map."""
+    """ONE pair, main rows banded over the ranks.  The orchestration lives below the C ABI (csrc/multi_api.cuh): this rank's
+    stepth_comm + stepth_cuda_dev_depth_dense_band = ring search of the band, MAX all-reduce of the normaliser, 3-row halo
+    exchange, finish, and an all-gather of the depth bands so that every GPU ends with the assembled map (NCCL, called by the
+    library); bands.CommBandRunner only allocates the tensors."""
     import numpy as np
 
-    from stepth_b200 import bands, synth
+    from stepth_b200 import bands, device, synth
 
     torch, args, sb, ctx, dev, dist = env.torch, env.args, env.sb, env.ctx, env.dev, env.dist
     wl = WORKLOADS[name]
     W, H, D = wl["w"], wl["h"], wl["d"]
     rank, world = env.rank, env.world
     flags = sb.RESAMPLE_U8
-    runner = bands.BandRunner(bands.DeviceStages(ctx), W, H, H, PRECISION, D, flags)
+    runner = bands.CommBandRunner(ctx, W, H, H, PRECISION, D, flags)
     b = runner.band
     # every rank generates the same pair from the same seed and keeps only its rows (synthetic data; no scatter timed)
     m, a = synth.make_pair(kind, W, H, seed=1, device=dev)
@@ -860,14 +862,13 @@ def run_giant(env, name, kind, steps, warmup, main_line):
     gather = world > 1
     l0 = ctx.launch_count()
     out = runner.run(mb, ab, gather_depth=gather)
-    torch.cuda.synchronize()
     launches = ctx.launch_count() - l0
     assert out["status"] == 0
 
     def step(events):
         if events is not None:
             events[0].record()
-        runner.run(mb, ab, gather_depth=gather)
+        runner.enqueue(mb, ab, gather_depth=gather)
         if events is not None:
             events[1].record()
 
@@ -876,20 +877,19 @@ def run_giant(env, name, kind, steps, warmup, main_line):
         sampler.start()
     total_ms, _ = time_resident(env, step, steps, warmup)
     clocks = sampler.stop() if sampler else None
+    out = runner.result()
+    assert out["status"] == 0
     value = steps * W * H * D / (total_ms * 1e-3) / 1e6
-    # one more (untimed) run with CUDA events between the stages: where each rank's time goes
-    runner.profile = True
-    out = runner.run(mb, ab, gather_depth=gather)
-    runner.profile = False
-    stage_ms = [runner.stage_ms]
+    # where each rank's time went in the last step (CUDA events recorded by the library between the stages)
+    mine = runner.stage_ms()
+    stage_ms = [mine]
     if world > 1:
         stage_ms = [None] * world
-        dist.all_gather_object(stage_ms, runner.stage_ms)
+        dist.all_gather_object(stage_ms, mine)
     # roofline of the search stage on the slowest band: this rank's main rows + the additional rows it can reach
     rw = min(W, W // 2 + D)
     my_alg = 4 * W * (b.y1 - b.y0) + 3 * rw * (b.ay1 - b.ay0) + W * (b.y1 - b.y0)
-    my_search = runner.stage_ms.get("search", 0.0)
-    slow = env.max_over_ranks(my_search)
+    slow = env.max_over_ranks(mine.get("search", 0.0))
     alg_all = int(env.sum_over_ranks(my_alg))
     roofline = build_roofline(name, kind, wl, alg_all // world, 1, slow, slow / (total_ms / steps),
                               "ring search stage of one band (tile_planes + coarse_transpose + search_near + search_far), the slowest rank's time, mean band bytes")
@@ -903,9 +903,9 @@ def run_giant(env, name, kind, steps, warmup, main_line):
         def e2e_step():
             dm.copy_(hm, non_blocking=True)
             da.copy_(ha, non_blocking=True)
-            o = runner.run(dm, da, gather_depth=False)     # bands go straight back to pinned host memory (no gather)
-            hd.copy_(o["depth_band"], non_blocking=True)
-            torch.cuda.synchronize()
+            runner.enqueue(dm, da, gather_depth=False)      # bands go straight back to pinned host memory (no gather)
+            hd.copy_(runner.depth_band, non_blocking=True)
+            runner.result()                                 # waits for the stream
 
         e2e_steps = max(2, min(steps, 5))
         ms = time_e2e(env, e2e_step, e2e_steps, warmup)
@@ -913,16 +913,19 @@ def run_giant(env, name, kind, steps, warmup, main_line):
                "h2d_bytes_per_step": int(env.sum_over_ranks(hm.numel() + ha.numel())),
                "d2h_bytes_per_step": int(env.sum_over_ranks(hd.numel())),
                "ms_per_step": round(ms / e2e_steps, 3), "steps": e2e_steps,
-               "api": "bands.BandRunner over the stage API: each rank uploads its band (+ reachable additional rows) from pinned "
-                      "memory, MAX all-reduce + halo exchange, its depth band returns to pinned memory"}
+               "api": "stepth_cuda_dev_depth_dense_band per rank: its band (+ reachable additional rows) up from pinned memory, "
+                      "MAX all-reduce + halo exchange inside the library, its depth band back to pinned memory"}
         del hm, ha, hd, dm, da
 
     parity = None
     if not args.no_parity:
         from oracle import oracle
 
+        out = runner.run(mb, ab, gather_depth=gather)
         rows = b.y1 - b.y0
-        raw_band = out["d8_band"][0].cpu().numpy()
+        # the raw distances of this band, by the very search call the band function makes
+        raw_t, _ = device.search_dense(ctx, mb, ab, PRECISION, D, 0, y0=b.y0, add_y0=b.ay0, add_img_h=H, img_h=H)
+        raw_band = raw_t[0].cpu().numpy()
         rng = np.random.default_rng(77 + rank)
         n_q = min(2000, rows * W)
         local = rng.choice(rows * W, n_q, replace=False).astype(np.int64)
@@ -932,16 +935,14 @@ def run_giant(env, name, kind, steps, warmup, main_line):
         ok = bool(np.array_equal(raw_band.reshape(-1)[local], sub))
         planes = 0
         # the finished plane, whole: rank 0 assembles the raw bands and runs the oracle's normalise + Gaussian over them
-        raw_t = out["d8_band"].contiguous()
         depth_t = out["depth_band"].contiguous()
         if world > 1:
             assert len({p.y1 - p.y0 for p in runner.plan}) == 1, "equal bands expected for the parity gather"
             raws = torch.empty((world,) + tuple(raw_t.shape), dtype=torch.uint8, device=dev)
             deps = torch.empty_like(raws)
-            dist.all_gather_into_tensor(raws, raw_t)
+            dist.all_gather_into_tensor(raws, raw_t.contiguous())
             dist.all_gather_into_tensor(deps, depth_t)
-            if rank == 0:
-                ok = ok and bool(torch.equal(deps.reshape(H, W), out["depth"].reshape(H, W)))   # the timed all-gather's result
+            ok = ok and bool(torch.equal(deps.reshape(H, W), out["depth"].reshape(H, W)))   # the library's own all-gather, on every rank
             raw_full, depth_full = raws.reshape(H, W), deps.reshape(H, W)
         else:
             raw_full, depth_full = raw_t.reshape(H, W), depth_t.reshape(H, W)
@@ -965,6 +966,7 @@ def run_giant(env, name, kind, steps, warmup, main_line):
     }
     if clocks is not None:
         line["clocks"] = clocks
+    runner.close()
     del mb, ab, out, runner
     torch.cuda.empty_cache()
     return line

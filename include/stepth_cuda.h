@@ -247,6 +247,9 @@ int32_t stepth_cuda_dev_depth_dense_band(stepth_comm *comm, void *stream, uint32
 /* waits for `stream` and reports the last band call's status (0, 3 = max == 0, 5 / 6 = depth_split) and cluster 0's (from, to) */
 int32_t stepth_cuda_comm_band_result(stepth_comm *comm, void *stream, int32_t *status_out, uint8_t from_to_out[2]);
 
+/* ms_out[4]: device time the last band call spent in search | MAX all-reduce + halo exchange | finish | tail + gather */
+int32_t stepth_cuda_comm_band_stage_ms(stepth_comm *comm, float ms_out[4]);
+
 /* One process driving several GPUs (what a Rust host links): a context per device, a host thread per device per call. */
 typedef struct stepth_multi stepth_multi;
 int32_t stepth_cuda_multi_create(const int32_t *devices, uint32_t n_devices, stepth_multi **multi_out);

@@ -319,3 +319,9 @@ class CommBandRunner:
     def run(self, main_band, add_band, gather_depth: bool = False) -> dict:
         self.enqueue(main_band, add_band, gather_depth)
         return self.result()
+
+    def stage_ms(self) -> dict:
+        """device time of the last call per stage (after result())"""
+        ms = (self.C.c_float * 4)()
+        self.ctx.check(self.ctx._lib.stepth_cuda_comm_band_stage_ms(self._h, self.C.byref(ms)))
+        return {k: round(float(v), 4) for k, v in zip(("search", "allreduce_max+halos", "finish", "tail+gather"), ms)}

@@ -33,6 +33,7 @@ struct NcclApi {
     decltype(&ncclCommDestroy) CommDestroy = nullptr;
     decltype(&ncclAllReduce) AllReduce = nullptr;
     decltype(&ncclBroadcast) Broadcast = nullptr;
+    decltype(&ncclAllGather) AllGather = nullptr;
     decltype(&ncclSend) Send = nullptr;
     decltype(&ncclRecv) Recv = nullptr;
     decltype(&ncclGroupStart) GroupStart = nullptr;
@@ -68,6 +69,7 @@ inline NcclApi &nccl_api() {
         api.CommDestroy = (decltype(api.CommDestroy))sym("ncclCommDestroy");
         api.AllReduce = (decltype(api.AllReduce))sym("ncclAllReduce");
         api.Broadcast = (decltype(api.Broadcast))sym("ncclBroadcast");
+        api.AllGather = (decltype(api.AllGather))sym("ncclAllGather");
         api.Send = (decltype(api.Send))sym("ncclSend");
         api.Recv = (decltype(api.Recv))sym("ncclRecv");
         api.GroupStart = (decltype(api.GroupStart))sym("ncclGroupStart");
@@ -92,6 +94,7 @@ struct stepth_comm {
     // scratch of the band path (device): raw distances of the band with 3 halo rows above and below, small state
     stepth_ctx::Buf d8h, small;
     void *h_small = nullptr;     // pinned mirror of `small`
+    cudaEvent_t marks[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // start | search | exchanges | finish | tail + gather
     // small state layout (u32 words): [0] max  [1] status  [2] n_out  [3] pad  [4..260) hist  then 512 bytes of ranges
     static constexpr size_t SMALL_BYTES = 4 * 260 + 512;
 };

@@ -48,6 +48,8 @@ extern "C" void stepth_cuda_comm_destroy(stepth_comm *c) {
     if (c->d8h.p) cudaFree(c->d8h.p);
     if (c->small.p) cudaFree(c->small.p);
     if (c->h_small) cudaFreeHost(c->h_small);
+    for (cudaEvent_t e : c->marks)
+        if (e) cudaEventDestroy(e);
     delete c;
 }
 
@@ -100,6 +102,9 @@ extern "C" int32_t stepth_cuda_dev_depth_dense_band(stepth_comm *c, void *stream
     uint32_t *d_max = sm, *d_nout = sm + 2, *d_hist = sm + 4;
     int32_t *d_status = (int32_t *)(sm + 1);
     uint8_t *d_ranges = (uint8_t *)(sm + 260);
+    for (cudaEvent_t &e : c->marks)
+        if (!e) STEPTH_CUDA_TRY(ctx, cudaEventCreate(&e));
+    STEPTH_CUDA_TRY(ctx, cudaEventRecord(c->marks[0], st));
     STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(c->small.p, 0, stepth_comm::SMALL_BYTES, st));
     uint8_t *d8 = (uint8_t *)c->d8h.p + (size_t)BAND_HALO * w;
 
@@ -109,6 +114,7 @@ extern "C" int32_t stepth_cuda_dev_depth_dense_band(stepth_comm *c, void *stream
     s.n_pairs = 1; s.w = w; s.h = rows; s.img_h = h; s.y0 = y0;
     s.wa = wa; s.ha = ay1 - ay0; s.add_y0 = ay0; s.add_img_h = add_h;
     if ((rc = stepth_cuda_dev_search_dense(ctx, st, &s, params, main_band, add_band, d8, d_max)) != STEPTH_OK) return rc;
+    STEPTH_CUDA_TRY(ctx, cudaEventRecord(c->marks[1], st));
     const uint32_t above = r > 0 ? std::min(BAND_HALO, y0) : 0u, below = r < n - 1 ? std::min(BAND_HALO, h - y1) : 0u;
     if (n > 1) {
         // 2. exchange 1: the normaliser is the maximum over the WHOLE image (depth_image.rs:124)
@@ -126,11 +132,13 @@ extern "C" int32_t stepth_cuda_dev_depth_dense_band(stepth_comm *c, void *stream
         }
         STEPTH_NCCL_TRY(ctx, nc.GroupEnd());
     }
+    STEPTH_CUDA_TRY(ctx, cudaEventRecord(c->marks[2], st));
     // 4. normalise + Gaussian (+ invert, + histogram) of the band, halo rows as source only
     const uint32_t fin_flags = flags & (STEPTH_RESAMPLE_MASK | STEPTH_FLAG_INVERT);
     if ((rc = stepth_cuda_dev_finish(ctx, st, 1, w, h, d8 - (size_t)above * w, y0 - above, above + rows + below, d_max, fin_flags,
                                      depth_band_out, y0, rows, want_fg ? d_hist : nullptr, d_status)) != STEPTH_OK)
         return rc;
+    STEPTH_CUDA_TRY(ctx, cudaEventRecord(c->marks[3], st));
     if (want_fg) {
         // 5. exchange 3: depth_split runs on the histogram of the whole image (depth_image.rs:162-218); every rank then
         // computes the same clusters
@@ -144,7 +152,15 @@ extern "C" int32_t stepth_cuda_dev_depth_dense_band(stepth_comm *c, void *stream
     }
     if (depth_full_out) {
         // 6. exchange 4 (optional): the assembled map on every GPU -- one broadcast per band, grouped (bands may differ in height)
-        if (n > 1) {
+        bool equal = true;   // equal bands are consecutive slabs of the assembled map: one all-gather straight into it
+        for (int q = 0; q < n; ++q) {
+            uint32_t pq[4];
+            band_plan(h, add_h, params->max_rings, (uint32_t)n, (uint32_t)q, pq);
+            equal = equal && pq[1] - pq[0] == rows;
+        }
+        if (n > 1 && equal) {
+            STEPTH_NCCL_TRY(ctx, nc.AllGather(depth_band_out, depth_full_out, (size_t)rows * w, ncclUint8, c->nccl, st));
+        } else if (n > 1) {
             STEPTH_NCCL_TRY(ctx, nc.GroupStart());
             for (int q = 0; q < n; ++q) {
                 uint32_t pq[4];
@@ -158,7 +174,17 @@ extern "C" int32_t stepth_cuda_dev_depth_dense_band(stepth_comm *c, void *stream
             STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(depth_full_out, depth_band_out, (size_t)rows * w, cudaMemcpyDeviceToDevice, st));
         }
     }
+    STEPTH_CUDA_TRY(ctx, cudaEventRecord(c->marks[4], st));
     STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(c->h_small, c->small.p, stepth_comm::SMALL_BYTES, cudaMemcpyDeviceToHost, st));
+    return STEPTH_OK;
+}
+
+// milliseconds the last band call spent in: search | MAX all-reduce + halo exchange (the wait for the slowest band shows up
+// here) | finish | tail + gather.  Call after stepth_cuda_comm_band_result.
+extern "C" int32_t stepth_cuda_comm_band_stage_ms(stepth_comm *c, float *ms_out) {
+    if (!c || !c->ctx) return STEPTH_ERR_INVALID_ARG;
+    if (!ms_out || !c->marks[0]) return set_err(c->ctx, STEPTH_ERR_INVALID_ARG, "comm_band_stage_ms: no band call has been made");
+    for (int i = 0; i < 4; ++i) STEPTH_CUDA_TRY(c->ctx, cudaEventElapsedTime(&ms_out[i], c->marks[i], c->marks[i + 1]));
     return STEPTH_OK;
 }
 
