@@ -331,7 +331,7 @@ def run_reference(args):
         "e2e": {"value": round(val, 3), "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ---------------------------------------------------------------------------------------------------------------
@@ -998,7 +998,7 @@ def run_ours(args):
                 bad.append(name)
         line["other_workloads"] = others
     if env.rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if env.world > 1:
         env.dist.destroy_process_group()
     if bad:
@@ -1006,8 +1006,27 @@ def run_ours(args):
         raise SystemExit(3)
 
 
+_STDOUT_FD = None
+
+
+def quiet_stdout():
+    """stdout carries ONE JSON line: libraries that printf there (NCCL's version banner at communicator creation) are sent to
+    stderr for the length of the run; `emit` writes the line to the real stdout."""
+    global _STDOUT_FD
+    sys.stdout.flush()
+    _STDOUT_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    text = (json.dumps(line) + "\n").encode()
+    os.write(_STDOUT_FD if _STDOUT_FD is not None else 1, text)
+
+
 def main():
     args = parse_args()
+    quiet_stdout()
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -758,8 +758,8 @@ def test_multi_handle_equals_one_context(ctx, orc):
         for k in ("depth", "mask", "rgba"):
             assert np.array_equal(got[k][i], want[k][i]), (k, i)
     # one pair in row bands (each band >= 3 rows); a shorter additional image so that the last bands reach nothing
-    for (w, h, ha, rings) in [(320, 250, 250, 48), (64, 96, 12, 6)]:
-        m, a = synth_pair("nat", w, h, seed=9)
+    for (w, h, ha, rings, seed) in [(320, 250, 250, 48, 9), (120, 96, 14, 8, 5)]:
+        m, a = synth_pair("nat", w, h, seed=seed)
         a = a[:ha].copy()
         one = ctx.depth_dense(m, a, P36, rings, flags)
         banded = mu.depth_dense_banded(m, a, P36, rings, flags)
