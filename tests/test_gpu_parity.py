@@ -783,7 +783,8 @@ def test_comm_band_runner_one_rank_equals_host_api(ctx, orc):
     flags = sb.RESAMPLE_U8 | sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY
     host = ctx.depth_dense(m, a, P36, 40, flags)
     runner = bands.CommBandRunner(ctx, 120, 90, 90, P36, 40, flags)
-    out = runner.run(torch.from_numpy(m).cuda()[None], torch.from_numpy(a).cuda()[None], gather_depth=True)
+    b = runner.band   # one rank owns every main row; only the additional rows a query can reach belong to the band
+    out = runner.run(torch.from_numpy(m).cuda()[None], torch.from_numpy(a[b.ay0:b.ay1]).cuda()[None].contiguous(), gather_depth=True)
     assert out["status"] == 0 and out["from_to"] == host["from_to"]
     for got, want in ((out["depth_band"], host["depth"]), (out["depth"], host["depth"]), (out["mask_band"], host["mask"]),
                       (out["rgba_band"], host["rgba"])):
