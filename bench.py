@@ -755,16 +755,20 @@ def run_blocks(env, name, kind, steps, warmup, main_line):
     wl = WORKLOADS[name]
     W, H, D = wl["w"], wl["h"], wl["d"]
     m, a = load_assets()
-    # the disage discretiser stays on the host in the drop-in (blocks are an INPUT of the boundary); disc_v0 is the
-    # documented stand-in.  It is outside both the GPU and the CPU timed regions.
-    blocks = sb.discretise_v0(m, PRECISION)
+    # disage's source is absent; disc_v0 is the documented stand-in for rgb_discrete (depth_image.rs:104-109).  It runs on the
+    # GPU (csrc/disc.cuh) INSIDE the timed step: main image -> block list -> search -> paint -> finish.  The host version of the
+    # same stand-in gives the list the CPU port is timed on (not timed there: the reference's discretiser is not ours to time).
+    blocks = ctx.discretise_v0(m, PRECISION)
     nb = len(blocks)
-    blocks_t = torch.from_numpy(blocks.view(np.uint8).reshape(nb, 20)).to(dev).contiguous()
+    blocks_host = sb.discretise_v0(m, PRECISION)
+    disc_equal = blocks.tobytes() == blocks_host.tobytes()
+    blocks_t = torch.zeros((nb, 20), dtype=torch.uint8, device=dev)
+    main_t = torch.from_numpy(m).to(dev).contiguous()
     add_t = torch.from_numpy(a).to(dev).contiguous()
     pipe = device.BlockPipeline(ctx, nb, W, H, a.shape[1], a.shape[0], PRECISION, D, sb.RESAMPLE_U8)
 
     def step(events):
-        pipe.run(blocks_t, add_t, search_events=events)
+        pipe.run(blocks_t, add_t, search_events=events, main_px=main_t)
 
     l0 = ctx.launch_count()
     step(None)
@@ -781,25 +785,27 @@ def run_blocks(env, name, kind, steps, warmup, main_line):
     roofline = build_roofline(name, "assets", wl, alg, 1, search_ms / steps_r, search_ms / total_ms,
                               "ring search stage, block mode (stepth_cuda_dev_search_blocks: tile_planes + coarse_transpose + search_near<blocks> + search_far<blocks>)")
     raw_gpu, depth_gpu = pipe.d8.cpu().numpy(), pipe.depth[0].cpu().numpy()
+    disc_equal = disc_equal and int(pipe.n_blocks[0]) == nb and blocks_t.cpu().numpy().tobytes() == blocks_host.tobytes()
 
     e2e, host_depth = None, None
     if not args.no_e2e:
         pin_a = torch.from_numpy(a).pin_memory()
-        pin_b = torch.from_numpy(blocks.view(np.uint8).reshape(nb, 20).copy()).pin_memory()
-        blocks_pinned = pin_b.numpy().reshape(-1).view(sb.BLOCK_DTYPE)
+        pin_m = torch.from_numpy(m).pin_memory()
         res = {}
 
-        def call(add_host, blocks_host):
-            res["out"] = ctx.depth_from_blocks(add_host, blocks_host, W, H, PRECISION, D, sb.RESAMPLE_U8)
+        def call(main_host, add_host):
+            res["out"] = ctx.depth_from_additional(main_host, add_host, PRECISION, D, sb.RESAMPLE_U8)
 
         e2e_steps = max(steps, 20)
-        ms = time_e2e(env, lambda: call(pin_a.numpy(), blocks_pinned), e2e_steps, warmup, flush=True)
+        ms = time_e2e(env, lambda: call(pin_m.numpy(), pin_a.numpy()), e2e_steps, warmup, flush=True)
         host_depth = res["out"]["depth"].copy()
-        ms_pg = time_e2e(env, lambda: call(a, blocks), e2e_steps, warmup, flush=True)
+        disc_equal = disc_equal and res["out"]["n_blocks"] == nb
+        ms_pg = time_e2e(env, lambda: call(m, a), e2e_steps, warmup, flush=True)
         e2e = {"value": round(env.world * e2e_steps * px_disp / (ms * 1e-3) / 1e6, 3), "unit": METRIC,
-               "h2d_bytes_per_step": nb * 20 + 3 * rw * rh, "d2h_bytes_per_step": W * H,
+               "h2d_bytes_per_step": 4 * W * H + 3 * rw * rh, "d2h_bytes_per_step": W * H + 4,
                "ms_per_step": round(ms / e2e_steps, 4), "steps": e2e_steps,
-               "api": "stepth_cuda_depth_from_blocks (host buffers; inputs pinned, the depth plane lands in a numpy array)",
+               "api": "stepth_cuda_depth_from_additional (host buffers: main RGBA + additional RGB in, pinned; discretiser, search, "
+                      "paint and finish on the device; the depth plane lands in a numpy array)",
                "pageable": {"value": round(env.world * e2e_steps * px_disp / (ms_pg * 1e-3) / 1e6, 3),
                             "ms_per_step": round(ms_pg / e2e_steps, 4), "steps": e2e_steps}}
 
@@ -809,13 +815,15 @@ def run_blocks(env, name, kind, steps, warmup, main_line):
 
         ref_depth, ref_raw = oracle.depth_from_blocks(a, blocks, PRECISION, W, H, D, resample=oracle.RESAMPLE_U8,
                                                       threads=os.cpu_count() or 1, want_raw=True)
-        ok = bool(np.array_equal(raw_gpu, ref_raw)) and bool(np.array_equal(depth_gpu, ref_depth))
+        ok = bool(np.array_equal(raw_gpu, ref_raw)) and bool(np.array_equal(depth_gpu, ref_depth)) and disc_equal
         planes = 1
         if host_depth is not None:
             ok = ok and bool(np.array_equal(host_depth, ref_depth))
             planes += 1
         parity = finish_parity(env, {"bit_exact": ok, "checked_queries": nb, "checked_planes": planes})
-        parity["what"] = "every block's raw distance + the whole finished plane, resident and host-buffer results"
+        parity["what"] = ("the device discretiser's block list against the host stand-in's (bytes), every block's raw distance + the "
+                          "whole finished plane, resident and host-buffer results")
+        parity["block_list_identical"] = bool(disc_equal)
 
     cpu = None
     if env.rank == 0 and env.world == 1 and not args.no_cpu_baseline:
@@ -824,10 +832,10 @@ def run_blocks(env, name, kind, steps, warmup, main_line):
         "metric": METRIC, "value": round(value, 3), "unit": METRIC, "n_gpus": env.world, "steps": steps_r, "warmup": warmup,
         "ms_per_step": round(total_ms / steps_r, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8", "data": "assets", "config": dict(describe(name, wl, kind, env.world), n_blocks=nb,
-                                                      discretiser="disc_v0 stand-in on the host, outside the timed regions (disage source absent)"),
+                                                      discretiser="disc_v0 stand-in (disage source absent) on the device, inside the timed step and the e2e call"),
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "parity": parity, "gpu_launches": launches_per_step * steps_r,
     }
-    del pipe, blocks_t, add_t
+    del pipe, blocks_t, add_t, main_t
     torch.cuda.empty_cache()
     return line
 

@@ -153,6 +153,20 @@ size_t stepth_host_discretise_v0(const uint8_t *main_px, uint32_t stride, uint32
                                  const uint8_t precision[3], uint32_t min_splits, uint32_t max_splits,
                                  stepth_block *blocks_out, size_t cap);
 
+/* the same stand-in on the device (csrc/disc.cuh): the block list is bit-identical to stepth_host_discretise_v0's, order included.
+ * Host buffers; *n_out = the number of blocks, at most `cap` of them written (blocks_out may be NULL to size the buffer). */
+int32_t stepth_cuda_discretise_v0(stepth_ctx *ctx, const uint8_t *main_px, uint32_t stride, uint32_t w, uint32_t h,
+                                  const uint8_t precision[3], uint32_t min_splits, uint32_t max_splits,
+                                  stepth_block *blocks_out, size_t cap, size_t *n_out);
+
+/* load_depth_from_additional whole (depth_image.rs:91-136) in ONE call: to_rgb8 + the stand-in for rgb_discrete (:104-109, on the
+ * device) + the block search + normalise + paint + resample (+ the fused tail by flags).  main_rgba: w*h*4; precision doubles as
+ * the discretiser's (:103); min_splits / max_splits as at :101-102 (16, ceil(log2(w*h))).  n_blocks_out: optional. */
+int32_t stepth_cuda_depth_from_additional(stepth_ctx *ctx, const uint8_t *main_rgba, uint32_t w, uint32_t h,
+                                          const uint8_t *add_rgb, uint32_t wa, uint32_t ha, const stepth_params *params,
+                                          uint32_t min_splits, uint32_t max_splits, uint8_t *depth_out, uint8_t *rgba_out,
+                                          uint8_t *mask_out, uint8_t *from_to_out, size_t *n_blocks_out);
+
 /* ---- device-resident stage API (device pointers; work is enqueued on `stream`, a cudaStream_t) ------------ */
 /* Used by the batch / row-band orchestration (one process per GPU) and by the device-resident benchmark.
  * ONE stream in flight per context: the stages keep scratch in the context (match planes, work lists, the plane between the
@@ -180,6 +194,12 @@ int32_t stepth_cuda_dev_search_blocks(stepth_ctx *ctx, void *stream, const stept
                                       const uint8_t *add_rgb, uint32_t wa, uint32_t ha,
                                       const stepth_block *blocks, size_t n_blocks, uint8_t *d8_out,
                                       uint32_t *max_out);
+
+/* the stand-in discretiser on the device (csrc/disc.cuh): main_px [h,w,stride] (device), blocks_out [cap] (device, may be NULL),
+ * n_out [1] u32 (device, may be NULL) = the number of blocks; the list equals stepth_host_discretise_v0's, order included */
+int32_t stepth_cuda_dev_discretise_v0(stepth_ctx *ctx, void *stream, const uint8_t *main_px, uint32_t stride, uint32_t w,
+                                      uint32_t h, const uint8_t precision[3], uint32_t min_splits, uint32_t max_splits,
+                                      stepth_block *blocks_out, size_t cap, uint32_t *n_out);
 
 /* paint: plane_out[h,w] = d8[b] over each block rectangle (DiscreteImage::collect + luma, depth_image.rs:130-132).
  * The plane holds RAW distances: the normalisation of :125-129 is a per-byte map and is applied by dev_finish. */

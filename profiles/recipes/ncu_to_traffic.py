@@ -28,7 +28,7 @@ def val(r, name, default=None):
     return v * scale
 
 
-stage = ("tile_planes", "coarse_transpose", "search_near", "search_far")
+stage = ("tile_planes", "coarse_transpose", "search_near", "search_otile", "search_far")
 seq, seen = [], set()
 for r in rows[2:]:
     name = r[idx["Kernel Name"]]

@@ -137,6 +137,50 @@ class Context:
             out["rgba"] = rgba
         return out
 
+    def discretise_v0(self, main_px, precision, min_splits: int = 16, max_splits: int | None = None) -> np.ndarray:
+        """The stand-in discretiser on the GPU (csrc/disc.cuh): the same block list as the host `discretise_v0`, order included."""
+        main_px = _u8c(main_px)
+        h, w, stride = main_px.shape
+        if max_splits is None:
+            max_splits = _max_splits(w, h)
+        prec = np.ascontiguousarray(np.asarray(precision, dtype=np.uint8).reshape(3))
+        n = C.c_size_t(0)
+        with self._lock:
+            self.check(self._lib.stepth_cuda_discretise_v0(self._h, _ffi.ptr(main_px), stride, w, h, _ffi.ptr(prec), min_splits,
+                                                           max_splits, None, 0, C.byref(n)))
+            blocks = np.zeros(n.value, dtype=BLOCK_DTYPE)
+            if n.value:
+                self.check(self._lib.stepth_cuda_discretise_v0(self._h, _ffi.ptr(main_px), stride, w, h, _ffi.ptr(prec), min_splits,
+                                                               max_splits, blocks.ctypes.data, n.value, C.byref(n)))
+        return blocks
+
+    def depth_from_additional(self, main_rgba, add_rgb, precision, max_rings=255, flags=_ffi.RESAMPLE_U8, min_splits: int = 16,
+                              max_splits: int | None = None):
+        """load_depth_from_additional in one call (depth_image.rs:91-136): the stand-in discretiser runs on the GPU and its block
+        list stays there.  Returns a dict: depth, n_blocks [, mask, rgba, from_to]."""
+        main_rgba = _u8c(main_rgba, (4,))
+        add_rgb = _u8c(add_rgb, (3,))
+        h, w = main_rgba.shape[:2]
+        ha, wa = add_rgb.shape[:2]
+        if max_splits is None:
+            max_splits = _max_splits(w, h)
+        p = _ffi.make_params(precision, max_rings, flags)
+        out = {"depth": np.empty((h, w), np.uint8)}
+        mask = np.empty((h, w), np.uint8) if flags & _ffi.FLAG_FOREGROUND else None
+        rgba = np.empty((h, w, 4), np.uint8) if flags & _ffi.FLAG_APPLY else None
+        ft = np.zeros(2, np.uint8)
+        n = C.c_size_t(0)
+        with self._lock:
+            self.check(self._lib.stepth_cuda_depth_from_additional(self._h, _ffi.ptr(main_rgba), w, h, _ffi.ptr(add_rgb), wa, ha,
+                                                                   C.byref(p), min_splits, max_splits, _ffi.ptr(out["depth"]),
+                                                                   _ffi.ptr(rgba), _ffi.ptr(mask), _ffi.ptr(ft), C.byref(n)))
+        out["n_blocks"] = int(n.value)
+        if mask is not None:
+            out["mask"], out["from_to"] = mask, (int(ft[0]), int(ft[1]))
+        if rgba is not None:
+            out["rgba"] = rgba
+        return out
+
     def depth_from_blocks(self, add_rgb, blocks, w, h, precision, max_rings=255, flags=_ffi.RESAMPLE_U8,
                           rgba_in=None, want_raw=False):
         """depth_image.rs:110-134 from a DiscretePixel list (the discretiser stays on the host)."""
@@ -405,13 +449,17 @@ class Multi:
         return res
 
 
+def _max_splits(w: int, h: int) -> int:
+    """(W*H as f32).log2().ceil()   depth_image.rs:101-103"""
+    return int(np.ceil(np.log2(np.float32(w * h))))
+
+
 def discretise_v0(main_px, precision, min_splits: int = 16, max_splits: int | None = None) -> np.ndarray:
     """Host stand-in for disage::open::rgb_discrete (depth_image.rs:104-109); NOT disage (source absent)."""
     main_px = _u8c(main_px)
     h, w, stride = main_px.shape
     if max_splits is None:
-        # (W*H as f32).log2().ceil()   depth_image.rs:101-103
-        max_splits = int(np.ceil(np.log2(np.float32(w * h))))
+        max_splits = _max_splits(w, h)
     prec = np.ascontiguousarray(np.asarray(precision, dtype=np.uint8).reshape(3))
     L = _ffi.lib()
     n = L.stepth_host_discretise_v0(_ffi.ptr(main_px), stride, w, h, _ffi.ptr(prec), min_splits, max_splits, None, 0)

@@ -39,8 +39,12 @@ struct stepth_ctx {
                                        // main images are still on their way up while the planes of the additional ones are built)
     int trace = 0;  // STEPTH_TRACE=1: the batch entry point prints each chunk's copy-in / compute / copy-out end times to stderr
     int upload_full_rows = 0;  // host-buffer entry points upload whole rows of the additional image (STEPTH_UPLOAD_FULL_ROWS)
-    int near_tile = 0;     // 1: dense mode runs ring 0 + coarse rings 0..1 from TMA-staged tile records (search_tile.cuh) and resumes the walk at ring 2
-                           // (STEPTH_NEAR_TILE; measured slower than the walking near kernel so far: 2.59 vs 2.26 ms per 16 pairs 1080p)
+    int near_tile = 2;     // dense mode's near stage (STEPTH_NEAR_TILE): 2 = one warp per origin tile (search_otile.cuh), 0 = the walking near kernel,
+                           // 1 = ring 0 + coarse rings 0..1 from TMA-staged tile records (search_tile.cuh; measured slower than the walk: 2.59 vs 2.26 ms
+                           // per 16 pairs 1080p)
+    int near_rings_otile = 12;  // coarse rings the origin-tile near stage walks, 2..16 (STEPTH_OT_RINGS; 16 pairs 1080p: 6 -> 2.17 ms, 12 -> 2.13, 16 -> 2.13)
+    int otile_nit = 0;         // origin-tile stage: origin rows per warp, 8 (a whole tile) / 4 / 2 / 1; 0 = by launch size (STEPTH_OT_NIT)
+    int otile_warps_per_sm = 128;  // ... so that the launch has at least this many warps per SM (STEPTH_OT_WARPS_PER_SM)
     int near_compact = 1;  // the near kernel packs the queries that survive ring 0 into full warps (STEPTH_NEAR_COMPACT)
     int mid_rings = 0;   // > near_rings: a second resumption point (FAR-1 walks rings [near_rings, mid_rings)); 0 = the far stage runs once (STEPTH_MID_RINGS)
     Buf planes2, worklist2, work2;  // scratch set of slot 1 (work / work2: the plane between the two streaming finish passes)
@@ -49,6 +53,8 @@ struct stepth_ctx {
     stepth::Stager stager;   // pinned rings + copy threads for pageable caller buffers (batch path; created on first use)
     int stage_threads = 8;   // STEPTH_STAGE_THREADS: copy threads (the caller included; default min(8, cores / 2)); 0 = hand pageable pointers to the driver
     Buf main_rgb;            // RGB8 main images as uploaded by the *_rgb entry point, expanded to main_rgba on the device
+    Buf disc_counts;         // device discretiser: leaves per top-level region, then their offsets (disc.cuh)
+    int blocks_on_device = 0;  // run_pairs: the block list it is handed already lies in HBM (stepth_cuda_depth_from_additional)
     Buf planes;  // two-level match bit-planes of the additional image(s) (tiles.cuh), rebuilt by every search
     // small per-pair state: [max u32][hist 256 u32][status i32][n_out u32][ranges 512 B] per pair
     void *h_small = nullptr;  // pinned mirror

@@ -8,12 +8,12 @@
 // There is no CPU fallback anywhere: without a usable sm_100 device every entry point returns STEPTH_ERR_CUDA.
 #include "ctx.cuh"
 #include "search_literal.cuh"
-#include "search_hier.cuh"
-#include "search_tile.cuh"
+#include "search_launch.cuh"
 #include "tail.cuh"
 #include "brightness.cuh"
 #include "intpeak.cuh"
 #include "edit.cuh"
+#include "disc.cuh"
 
 #include <algorithm>
 
@@ -81,6 +81,9 @@ extern "C" int32_t stepth_cuda_ctx_create(int32_t device, stepth_ctx **ctx_out) 
     if (const char *ev = getenv("STEPTH_MID_RINGS")) ctx->mid_rings = atoi(ev);
     if (const char *ev = getenv("STEPTH_NEAR_COMPACT")) ctx->near_compact = atoi(ev);
     if (const char *ev = getenv("STEPTH_NEAR_TILE")) ctx->near_tile = atoi(ev);
+    if (const char *ev = getenv("STEPTH_OT_RINGS")) ctx->near_rings_otile = atoi(ev);
+    if (const char *ev = getenv("STEPTH_OT_NIT")) ctx->otile_nit = atoi(ev);
+    if (const char *ev = getenv("STEPTH_OT_WARPS_PER_SM")) ctx->otile_warps_per_sm = std::max(1, atoi(ev));
     if (const char *ev = getenv("STEPTH_BATCH_CHUNKS")) ctx->batch_chunks = atoi(ev);
     if (const char *ev = getenv("STEPTH_TWO_STREAMS")) ctx->two_streams = atoi(ev);
     if (const char *ev = getenv("STEPTH_FINISH_STREAMING")) ctx->finish_streaming = atoi(ev);
@@ -111,7 +114,7 @@ extern "C" void stepth_cuda_ctx_destroy(stepth_ctx *ctx) {
     stepth_ctx::Buf *bufs[] = {&ctx->main_rgba, &ctx->add_rgb, &ctx->d8,   &ctx->depth, &ctx->mask, &ctx->rgba_out,
                                &ctx->blocks,    &ctx->plane,   &ctx->small, &ctx->u16a,  &ctx->u16b, &ctx->u16o,
                                &ctx->work,      &ctx->planes, &ctx->worklist, &ctx->planes2, &ctx->worklist2, &ctx->work2,
-                               &ctx->main_rgb};
+                               &ctx->main_rgb, &ctx->disc_counts};
     for (auto *b : bufs)
         if (b->p) cudaFree(b->p);
     for (auto &kv : ctx->taps)
@@ -452,7 +455,7 @@ int32_t run_pairs_impl(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_r
     TRY_RC(ensure(ctx, ctx->d8, n_q * n));
     TRY_RC(ensure(ctx, ctx->depth, px * n));
     if (blocks) {
-        TRY_RC(ensure(ctx, ctx->blocks, sizeof(stepth_block) * n_blocks));
+        if (!ctx->blocks_on_device) TRY_RC(ensure(ctx, ctx->blocks, sizeof(stepth_block) * n_blocks));
         TRY_RC(ensure(ctx, ctx->plane, px));
     }
     if (!blocks || want_apply) TRY_RC(ensure(ctx, ctx->main_rgba, px * 4 * n));
@@ -536,7 +539,7 @@ int32_t run_pairs_impl(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_r
         }
         for (uint32_t i = i0; i < i1; ++i) {
             const uint8_t *rgba_src = blocks ? (want_apply ? rgba_in[i] : nullptr) : main_rgba[i];
-            if (!rgba_src) continue;
+            if (!rgba_src || ctx->blocks_on_device) continue;   // (the device discretiser's caller left the main image in d_main)
             if (main_stride == 3) TRY_RC(upload((uint8_t *)ctx->main_rgb.p + px * 3 * i, rgba_src, px * 3, px * 3, 1, s_in));
             else TRY_RC(upload(d_main + px * 4 * i, rgba_src, px * 4, px * 4, 1, s_in));
         }
@@ -559,12 +562,13 @@ int32_t run_pairs_impl(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_r
         uint8_t *c_ranges = sm.ranges(ctx->small.p) + 512 * (size_t)i0;
         const uint8_t *plane = nullptr;  // the raw-distance plane handed to finish
         if (blocks) {
-            STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->blocks.p, blocks, sizeof(stepth_block) * n_blocks,
-                                                 cudaMemcpyHostToDevice, st));
-            TRY_RC(stepth_cuda_dev_search_blocks(ctx, st, params, d_add, wa_d, ha_d, (const stepth_block *)ctx->blocks.p,
-                                                 n_blocks, d_d8, c_max));
-            TRY_RC(stepth_cuda_dev_paint_blocks(ctx, st, (const stepth_block *)ctx->blocks.p, d_d8, n_blocks, w, h,
-                                                (uint8_t *)ctx->plane.p));
+            // the list is the caller's (host) or the device discretiser's (already in HBM: stepth_cuda_depth_from_additional)
+            const stepth_block *d_blocks = ctx->blocks_on_device ? blocks : (const stepth_block *)ctx->blocks.p;
+            if (!ctx->blocks_on_device)
+                STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->blocks.p, blocks, sizeof(stepth_block) * n_blocks,
+                                                     cudaMemcpyHostToDevice, st));
+            TRY_RC(stepth_cuda_dev_search_blocks(ctx, st, params, d_add, wa_d, ha_d, d_blocks, n_blocks, d_d8, c_max));
+            TRY_RC(stepth_cuda_dev_paint_blocks(ctx, st, d_blocks, d_d8, n_blocks, w, h, (uint8_t *)ctx->plane.p));
             plane = (const uint8_t *)ctx->plane.p;
         } else {
             stepth_dev_shape s;
@@ -1073,5 +1077,118 @@ extern "C" size_t stepth_host_discretise_v0(const uint8_t *main_px, uint32_t str
     d.out = blocks_out; d.cap = blocks_out ? cap : 0; d.n = 0;
     d.rec(0, 0, w, h, 0);
     return d.n;
+}
+
+// ---- disc_v0 on the device (disc.cuh) ----------------------------------------------------------------------------------------
+namespace {
+// count pass + scan: afterwards a.counts holds every top-level region's offset and, last, the number of blocks
+int32_t disc_count(stepth_ctx *ctx, cudaStream_t st, const uint8_t *px_dev, uint32_t stride, uint32_t w, uint32_t h,
+                   const uint8_t precision[3], uint32_t min_splits, uint32_t max_splits, stepth::DiscArgs &a) {
+    using namespace stepth;
+    memset(&a, 0, sizeof a);
+    a.px = px_dev; a.stride = stride; a.w = w; a.h = h;
+    a.pr = precision[0]; a.pg = precision[1]; a.pb = precision[2];
+    a.min_s = min_splits; a.max_s = max_splits;
+    a.top = std::min(std::min(min_splits, max_splits), DISC_MAX_TOP);
+    const uint32_t n_top = 1u << a.top;
+    int32_t rc = ensure(ctx, ctx->disc_counts, sizeof(uint32_t) * ((size_t)n_top + 1));
+    if (rc != STEPTH_OK) return rc;
+    a.counts = (uint32_t *)ctx->disc_counts.p;
+    disc_kernel<false><<<(n_top + 127) / 128, 128, 0, st>>>(a);
+    ctx->launches++;
+    STEPTH_CUDA_TRY(ctx, cudaGetLastError());
+    disc_scan_kernel<<<1, 1024, 0, st>>>(a.counts, n_top);
+    ctx->launches++;
+    STEPTH_CUDA_TRY(ctx, cudaGetLastError());
+    return STEPTH_OK;
+}
+int32_t disc_write(stepth_ctx *ctx, cudaStream_t st, stepth::DiscArgs &a, stepth_block *out_dev, size_t cap) {
+    using namespace stepth;
+    a.out = out_dev; a.cap = cap;
+    const uint32_t n_top = 1u << a.top;
+    disc_kernel<true><<<(n_top + 127) / 128, 128, 0, st>>>(a);
+    ctx->launches++;
+    STEPTH_CUDA_TRY(ctx, cudaGetLastError());
+    return STEPTH_OK;
+}
+bool disc_args_ok(const void *px, uint32_t stride, uint32_t w, uint32_t h, const uint8_t *precision) {
+    return px && precision && (stride == 3 || stride == 4) && w != 0 && h != 0 && (uint64_t)w * h <= 0xfffffff0ull;
+}
+// uploads the image and runs the count pass; the number of blocks comes back through the pinned small buffer
+int32_t disc_host_count(stepth_ctx *ctx, const uint8_t *main_px, uint32_t stride, uint32_t w, uint32_t h, const uint8_t precision[3],
+                        uint32_t min_splits, uint32_t max_splits, stepth::DiscArgs &a, size_t *n_out) {
+    using namespace stepth;
+    STEPTH_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    const size_t bytes = (size_t)w * h * stride;
+    int32_t rc = ensure(ctx, ctx->main_rgba, (size_t)w * h * 4);
+    if (rc == STEPTH_OK) rc = ensure_host_small(ctx, 64);
+    if (rc != STEPTH_OK) return rc;
+    cudaStream_t st = ctx->stream;
+    STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->main_rgba.p, main_px, bytes, cudaMemcpyHostToDevice, st));
+    rc = disc_count(ctx, st, (const uint8_t *)ctx->main_rgba.p, stride, w, h, precision, min_splits, max_splits, a);
+    if (rc != STEPTH_OK) return rc;
+    STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_small, a.counts + (1u << a.top), sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    *n_out = *(const uint32_t *)ctx->h_small;
+    return STEPTH_OK;
+}
+}  // namespace
+
+extern "C" int32_t stepth_cuda_dev_discretise_v0(stepth_ctx *ctx, void *stream, const uint8_t *main_px, uint32_t stride, uint32_t w,
+                                                 uint32_t h, const uint8_t precision[3], uint32_t min_splits, uint32_t max_splits,
+                                                 stepth_block *blocks_out, size_t cap, uint32_t *n_out) {
+    if (!ctx) return STEPTH_ERR_INVALID_ARG;
+    if (!disc_args_ok(main_px, stride, w, h, precision) || ((uintptr_t)blocks_out & 3))
+        return set_err(ctx, STEPTH_ERR_INVALID_ARG, "dev_discretise_v0: null or invalid argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    stepth::DiscArgs a;
+    TRY_RC(disc_count(ctx, st, main_px, stride, w, h, precision, min_splits, max_splits, a));
+    if (blocks_out && cap) TRY_RC(disc_write(ctx, st, a, blocks_out, cap));
+    if (n_out) STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(n_out, a.counts + (1u << a.top), sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+    return STEPTH_OK;
+}
+
+extern "C" int32_t stepth_cuda_discretise_v0(stepth_ctx *ctx, const uint8_t *main_px, uint32_t stride, uint32_t w, uint32_t h,
+                                             const uint8_t precision[3], uint32_t min_splits, uint32_t max_splits,
+                                             stepth_block *blocks_out, size_t cap, size_t *n_out) {
+    if (!ctx) return STEPTH_ERR_INVALID_ARG;
+    if (!disc_args_ok(main_px, stride, w, h, precision) || !n_out)
+        return set_err(ctx, STEPTH_ERR_INVALID_ARG, "discretise_v0: null or invalid argument");
+    stepth::DiscArgs a;
+    size_t n = 0;
+    TRY_RC(disc_host_count(ctx, main_px, stride, w, h, precision, min_splits, max_splits, a, &n));
+    *n_out = n;
+    const size_t n_write = std::min(n, blocks_out ? cap : (size_t)0);
+    if (n_write) {
+        TRY_RC(ensure(ctx, ctx->blocks, sizeof(stepth_block) * n_write));
+        TRY_RC(disc_write(ctx, ctx->stream, a, (stepth_block *)ctx->blocks.p, n_write));
+        STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(blocks_out, ctx->blocks.p, sizeof(stepth_block) * n_write, cudaMemcpyDeviceToHost, ctx->stream));
+        STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    return STEPTH_OK;
+}
+
+// load_depth_from_additional whole (depth_image.rs:91-136) with the stand-in discretiser: the main image goes up once, is cut
+// into blocks on the device, and the block list never visits the host
+extern "C" int32_t stepth_cuda_depth_from_additional(stepth_ctx *ctx, const uint8_t *main_rgba, uint32_t w, uint32_t h,
+                                                     const uint8_t *add_rgb, uint32_t wa, uint32_t ha, const stepth_params *params,
+                                                     uint32_t min_splits, uint32_t max_splits, uint8_t *depth_out, uint8_t *rgba_out,
+                                                     uint8_t *mask_out, uint8_t *from_to_out, size_t *n_blocks_out) {
+    if (!ctx) return STEPTH_ERR_INVALID_ARG;
+    if (!main_rgba || !add_rgb || !depth_out || !params_ok(params) || w == 0 || h == 0 || wa == 0 || ha == 0 ||
+        (uint64_t)w * h > 0xfffffff0ull)
+        return set_err(ctx, STEPTH_ERR_INVALID_ARG, "depth_from_additional: null or invalid argument");
+    stepth::DiscArgs a;
+    size_t n = 0;
+    TRY_RC(disc_host_count(ctx, main_rgba, 4, w, h, params->precision, min_splits, max_splits, a, &n));
+    if (n_blocks_out) *n_blocks_out = n;
+    if (n < 8) return set_err(ctx, STEPTH_ERR_TOO_FEW_BLOCKS, "fewer than 8 blocks: par_chunks_mut(0) panics (depth_image.rs:111-112)");
+    TRY_RC(ensure(ctx, ctx->blocks, sizeof(stepth_block) * n));
+    TRY_RC(disc_write(ctx, ctx->stream, a, (stepth_block *)ctx->blocks.p, n));
+    ctx->blocks_on_device = 1;
+    const int32_t rc = run_pairs(ctx, 1, nullptr, w, h, &add_rgb, wa, ha, (const stepth_block *)ctx->blocks.p, n, params, &depth_out,
+                                 nullptr, &main_rgba, &rgba_out, mask_out ? &mask_out : nullptr, from_to_out, nullptr);
+    ctx->blocks_on_device = 0;
+    return rc;
 }
 #include "multi_api.cuh"

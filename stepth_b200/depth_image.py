@@ -186,9 +186,8 @@ class DepthImage:
                                    max_rings: int | None = None, flags: int = _ffi.RESAMPLE_U8) -> None:
         """depth_image.rs:91-136.
 
-        mode="blocks": steps 3-5 (the disage discretisation) run on the host -- `blocks` may carry the
-        DiscretePixel list produced by the real disage; by default the documented stand-in `discretise_v0` is
-        used -- and steps 6-10 run on the GPU.  mode="dense": every pixel is its own block (the limit case the
+        mode="blocks": `blocks` may carry the DiscretePixel list produced by the real disage on the host (steps 3-5); by default
+        the documented stand-in `discretise_v0` runs on the GPU in the same call as steps 6-10.  mode="dense": every pixel is its own block (the limit case the
         benchmark configs use).
         """
         add_rgb = _to_rgb8(add_image)  # :96
@@ -198,9 +197,10 @@ class DepthImage:
         if mode == "dense":
             out = ctx.depth_dense(self.image, add_rgb, precision, max_rings, flags)
         elif mode == "blocks":
-            if blocks is None:
-                blocks = discretise_v0(self.image, precision, self.MIN_SPLITS)  # :101-109
-            out = ctx.depth_from_blocks(add_rgb, blocks, self.width(), self.height(), precision, max_rings, flags)
+            if blocks is None:   # :101-109 on the GPU too (the stand-in discretiser; its block list never visits the host)
+                out = ctx.depth_from_additional(self.image, add_rgb, precision, max_rings, flags, self.MIN_SPLITS)
+            else:
+                out = ctx.depth_from_blocks(add_rgb, blocks, self.width(), self.height(), precision, max_rings, flags)
         else:
             raise ValueError("mode must be 'blocks' or 'dense'")
         self.load_depth(out["depth"])  # :135

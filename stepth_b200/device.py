@@ -90,12 +90,29 @@ class BlockPipeline:
         self.max = torch.zeros(1, dtype=torch.int32, device=dev)
         self.status = torch.zeros(1, dtype=torch.int32, device=dev)
 
-    def run(self, blocks: torch.Tensor, add_rgb: torch.Tensor, search_events=None) -> None:
+    def discretise(self, main_px: torch.Tensor, blocks: torch.Tensor, min_splits: int = 16, max_splits: int | None = None):
+        """the stand-in discretiser on the device (csrc/disc.cuh): main_px [h, w, 3|4] -> blocks [nb, 20]; the count lands in
+        self.n_blocks (a device u32; the caller sized `blocks` from an earlier count)"""
+        assert main_px.is_cuda and main_px.dtype == torch.uint8 and tuple(main_px.shape[:2]) == (self.h, self.w)
+        if max_splits is None:
+            from .context import _max_splits
+
+            max_splits = _max_splits(self.w, self.h)
+        if not hasattr(self, "n_blocks"):
+            self.n_blocks = torch.zeros(1, dtype=torch.int32, device=main_px.device)
+        self.ctx.check(self.ctx._lib.stepth_cuda_dev_discretise_v0(
+            self.ctx.handle, _stream_handle(), _ffi.ptr(main_px), int(main_px.shape[2]), self.w, self.h, self.params.precision,
+            min_splits, max_splits, _ffi.ptr(blocks), int(blocks.shape[0]), _ffi.ptr(self.n_blocks)))
+
+    def run(self, blocks: torch.Tensor, add_rgb: torch.Tensor, search_events=None, main_px: torch.Tensor | None = None) -> None:
+        """main_px given: the block list is rebuilt from it on the device first (the whole of load_depth_from_additional)"""
         assert blocks.is_cuda and blocks.dtype == torch.uint8 and tuple(blocks.shape) == (self.nb, 20)
         assert tuple(add_rgb.shape) == (self.ha, self.wa, 3)
         lib, ctx, st = self.ctx._lib, self.ctx, _stream_handle()
         p = C.byref(self.params)
         self.status.zero_()
+        if main_px is not None:
+            self.discretise(main_px, blocks)
         if search_events is not None:
             search_events[0].record()
         ctx.check(lib.stepth_cuda_dev_search_blocks(ctx.handle, st, p, _ffi.ptr(add_rgb), self.wa, self.ha, _ffi.ptr(blocks),

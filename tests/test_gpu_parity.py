@@ -935,3 +935,53 @@ def test_image_replace_vs_oracle(ctx, orc):
     assert a.image[:4, :4].min() == 1 and a.image[4:].max() == 0
     a.mask_not()
     assert a.mask[0, 0] == 0 and a.mask[9, 9] == 255
+
+
+# ---- the stand-in discretiser on the device (csrc/disc.cuh) ------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize(
+    "w,h,min_s,max_s",
+    [(600, 400, 16, None), (96, 64, 16, None), (161, 77, 10, None), (33, 9, 4, 11), (1, 17, 16, None), (5, 1, 16, None),
+     (2, 2, 16, None), (64, 64, 0, 7), (64, 64, 3, 3), (300, 200, 18, 18), (257, 3, 16, 40), (1920, 1080, 16, None)],
+)
+def test_device_discretiser_equals_host_stand_in(ctx, assets, w, h, min_s, max_s):
+    """identical block list, order included, for the README image, synthetic images, ragged shapes and split bounds that force
+    leaves above, at and below the top level"""
+    import stepth_b200 as sb
+
+    if (w, h) == (600, 400):
+        imgs = [rgba_of(assets["main"]), np.ascontiguousarray(assets["main"])]           # RGBA and RGB strides
+    else:
+        rng = np.random.default_rng(w * 131 + h)
+        imgs = [synth_pair("nat", w, h, seed=w + h)[0], synth_pair("geo", w, h, seed=3)[0],
+                np.full((h, w, 3), 77, np.uint8), (rng.integers(0, 4, (h, w, 3)) * 60).astype(np.uint8)]
+    for img in imgs:
+        for prec in (P36, [1, 200, 17], [0, 36, 36]):
+            want = sb.discretise_v0(img, prec, min_s, max_s)
+            got = ctx.discretise_v0(img, prec, min_s, max_s)
+            assert len(got) == len(want)
+            assert got.tobytes() == want.tobytes()
+
+
+@pytest.mark.gpu
+def test_depth_from_additional_equals_host_discretiser_plus_blocks(ctx, orc, assets):
+    """load_depth_from_additional in one call (the block list never leaves the device) == host stand-in + depth_from_blocks"""
+    import stepth_b200 as sb
+
+    main, add = rgba_of(assets["main"]), assets["additional"]
+    blocks = sb.discretise_v0(main, P36)
+    flags = sb.RESAMPLE_U8 | sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY
+    want = ctx.depth_from_blocks(add, blocks, 600, 400, P36, 255, flags, rgba_in=main)
+    got = ctx.depth_from_additional(main, add, P36, 255, flags)
+    assert got["n_blocks"] == len(blocks) and got["from_to"] == want["from_to"]
+    for k in ("depth", "mask", "rgba"):
+        assert np.array_equal(got[k], want[k]), k
+    plain = ctx.depth_from_additional(main, add, P36, 255, sb.RESAMPLE_U8)
+    assert np.array_equal(plain["depth"], orc.depth_from_blocks(add, blocks, P36, 600, 400, 255, resample=orc.RESAMPLE_U8, threads=8))
+    # the public API takes the same route when no block list is handed in
+    img = sb.DepthImage.from_image(assets["main"], ctx)
+    img.load_depth_from_additional(add, P36)
+    assert np.array_equal(img.depth_plane, plain["depth"])
+    # fewer than 8 blocks: par_chunks_mut(0) panics (depth_image.rs:111-112)
+    with pytest.raises(sb.StepthPanic):
+        ctx.depth_from_additional(np.full((1, 2, 4), 9, np.uint8), np.zeros((4, 4, 3), np.uint8), P36, 255, sb.RESAMPLE_U8)
