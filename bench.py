@@ -968,7 +968,11 @@ def run_giant(env, name, kind, steps, warmup, main_line):
         "metric": METRIC, "value": round(value, 3), "unit": METRIC, "n_gpus": world, "steps": steps,
         "warmup": warmup, "ms_per_step": round(total_ms / steps, 4), "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": dict(describe(name, wl, kind, world), bands=[[p.y0, p.y1, p.ay0, p.ay1] for p in runner.plan]),
+        "config": dict(describe(name, wl, kind, world), bands=[[p.y0, p.y1, p.ay0, p.ay1] for p in runner.plan],
+                       exchange={1: "peer windows: the library's own kernels store maxima, halo rows and the depth bands into the other "
+                                    "ranks' HBM over NVLink (csrc/peer.cuh); NCCL only bootstraps the window handles",
+                                 0: "NCCL (all-reduce MAX, send/recv halos, all-gather of the depth bands)"}.get(
+                                     runner.peer_mode() if world > 1 and runner.peer_mode() >= 0 else (0 if world > 1 else -1), "one rank: none")),
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "parity": parity, "gpu_launches": launches * steps,
         "stage_ms_per_rank": stage_ms,
     }

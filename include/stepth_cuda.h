@@ -267,6 +267,13 @@ int32_t stepth_cuda_dev_depth_dense_band(stepth_comm *comm, void *stream, uint32
 /* waits for `stream` and reports the last band call's status (0, 3 = max == 0, 5 / 6 = depth_split) and cluster 0's (from, to) */
 int32_t stepth_cuda_comm_band_result(stepth_comm *comm, void *stream, int32_t *status_out, uint8_t from_to_out[2]);
 
+/* 1 when this group's band exchanges are stores into the peers' HBM over NVLink (csrc/peer.cuh), 0 when they go through NCCL
+ * (no peer access between the GPUs, or STEPTH_PEER=0), -1 before the first multi-rank band call has decided. */
+int32_t stepth_cuda_comm_peer_mode(const stepth_comm *comm);
+/* The assembled depth map inside this rank's window (device pointer, w*h bytes): handing it to stepth_cuda_dev_depth_dense_band
+ * as depth_full_out saves the copy out of the window.  COLLECTIVE.  *ptr_out = NULL when the group runs over NCCL. */
+int32_t stepth_cuda_comm_full_map(stepth_comm *comm, void *stream, uint32_t w, uint32_t h, uint32_t add_h, uint32_t max_rings,
+                                  uint8_t **ptr_out);
 /* ms_out[4]: device time the last band call spent in search | MAX all-reduce + halo exchange | finish | tail + gather */
 int32_t stepth_cuda_comm_band_stage_ms(stepth_comm *comm, float ms_out[4]);
 

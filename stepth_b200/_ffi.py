@@ -104,6 +104,8 @@ SIGNATURES = {
     "stepth_cuda_comm_destroy": (None, [_vp]),
     "stepth_cuda_dev_depth_dense_band": (_i32, [_vp, _vp, _u32, _u32, _u32, _u32, _PP, _u8p, _u8p, _u8p, _u8p, _u8p, _u8p]),
     "stepth_cuda_comm_band_result": (_i32, [_vp, _vp, C.POINTER(_i32), _u8p]),
+    "stepth_cuda_comm_peer_mode": (_i32, [_vp]),
+    "stepth_cuda_comm_full_map": (_i32, [_vp, _vp, _u32, _u32, _u32, _u32, C.POINTER(_vp)]),
     "stepth_cuda_comm_band_stage_ms": (_i32, [_vp, C.POINTER(C.c_float * 4)]),
     "stepth_cuda_multi_create": (_i32, [C.POINTER(_i32), _u32, C.POINTER(_vp)]),
     "stepth_cuda_multi_destroy": (None, [_vp]),

@@ -237,6 +237,14 @@ class BandRunner:
         return torch.cat([parts[p.rank][:, : p.y1 - p.y0] for p in self.plan], dim=1).contiguous()
 
 
+class _DeviceBytes:
+    """a device buffer owned by the library, shown to torch through __cuda_array_interface__ (no copy)"""
+
+    def __init__(self, ptr: int, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "|u1", "data": (int(ptr), False), "version": 3,
+                                         "strides": None}
+
+
 class CommBandRunner:
     """The row-band path below the C ABI (csrc/multi_api.cuh): this rank's `stepth_comm` (context + NCCL communicator created
     from a 128-byte id that rank 0 makes and torch.distributed broadcasts) and `stepth_cuda_dev_depth_dense_band`, which
@@ -295,9 +303,19 @@ class CommBandRunner:
         """main_band [1, rows, w, 4], add_band [1, arows, wa, 3] of THIS rank (device tensors); asynchronous"""
         b = self.band
         assert tuple(main_band.shape) == (1, b.y1 - b.y0, self.w, 4) and tuple(add_band.shape) == (1, b.ay1 - b.ay0, self.wa, 3)
-        if gather_depth and self.depth_full is None:
-            self.depth_full = torch.empty((1, self.h, self.w), dtype=torch.uint8, device=main_band.device)
         st = torch.cuda.current_stream().cuda_stream
+        if gather_depth and self.depth_full is None:
+            # the assembled map lives in this rank's peer window when the group has one (csrc/peer.cuh: the other ranks' finish
+            # kernels store their bands straight into it over NVLink); a tensor of our own when the exchanges go through NCCL
+            ptr = self.C.c_void_p()
+            self.ctx.check(self.ctx._lib.stepth_cuda_comm_full_map(self._h, st, self.w, self.h, self.add_h, int(self.params.max_rings),
+                                                                   self.C.byref(ptr)))
+            if ptr.value:
+                self._window_full = _DeviceBytes(ptr.value, (1, self.h, self.w))
+                self.depth_full = torch.as_tensor(self._window_full, device=main_band.device)
+                assert self.depth_full.data_ptr() == ptr.value
+            else:
+                self.depth_full = torch.empty((1, self.h, self.w), dtype=torch.uint8, device=main_band.device)
         self.ctx.check(self.ctx._lib.stepth_cuda_dev_depth_dense_band(
             self._h, st, self.w, self.h, self.wa, self.add_h, self.C.byref(self.params), _ffi.ptr(main_band), _ffi.ptr(add_band),
             _ffi.ptr(self.depth_band), _ffi.ptr(self.depth_full) if gather_depth else None, _ffi.ptr(self.mask_band),
@@ -319,6 +337,10 @@ class CommBandRunner:
     def run(self, main_band, add_band, gather_depth: bool = False) -> dict:
         self.enqueue(main_band, add_band, gather_depth)
         return self.result()
+
+    def peer_mode(self) -> int:
+        """1: the exchanges are stores into the peers' HBM over NVLink (csrc/peer.cuh); 0: NCCL; -1: not decided yet"""
+        return int(self.ctx._lib.stepth_cuda_comm_peer_mode(self._h))
 
     def stage_ms(self) -> dict:
         """device time of the last call per stage (after result())"""

@@ -53,6 +53,10 @@ struct stepth_ctx {
     stepth::Stager stager;   // pinned rings + copy threads for pageable caller buffers (batch path; created on first use)
     int stage_threads = 8;   // STEPTH_STAGE_THREADS: copy threads (the caller included; default min(8, cores / 2)); 0 = hand pageable pointers to the driver
     Buf main_rgb;            // RGB8 main images as uploaded by the *_rgb entry point, expanded to main_rgba on the device
+    uint8_t *finish_mirror[8] = {};  // row bands: where the next dev_finish call also stores its outputs (peer.cuh); cleared by the caller
+    uint32_t finish_n_mirror = 0;
+    int finish_mirrored = 0;         // set by dev_finish when it did
+    int peer_enabled = 1;            // STEPTH_PEER=0: the row-band exchanges go through NCCL instead of peer windows
     Buf disc_counts;         // device discretiser: leaves per top-level region, then their offsets (disc.cuh)
     int blocks_on_device = 0;  // run_pairs: the block list it is handed already lies in HBM (stepth_cuda_depth_from_additional)
     Buf planes;  // two-level match bit-planes of the additional image(s) (tiles.cuh), rebuilt by every search

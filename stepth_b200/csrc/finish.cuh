@@ -45,6 +45,10 @@ struct FinishArgs {
     // order gives the bits of the clipped sum (rows of 8 or more columns; filled by stepth_cuda_dev_finish)
     float wx_edge[6][7];
     uint32_t seg_rows;       // output rows per thread of the vertical pass: FV_ROWS, or 7 for a launch that would leave SMs idle
+    // row bands over several GPUs (peer.cuh): the streaming horizontal pass also stores every output into these planes -- the band's
+    // rows inside each rank's assembled map, reached over NVLink -- so the all-gather of the depth bands rides on the pass
+    uint8_t *mirror[8];      // [n_mirror] same geometry as dst (n == 1)
+    uint32_t n_mirror;
 };
 
 // clamp(t, 0.0, 255.0) then f32::round (half away from zero), as NumCast::from(FloatNearest(t)) does
@@ -398,6 +402,21 @@ __global__ void __launch_bounds__(256) finish_horz_kernel(FinishArgs a, const ui
         const int n = min(8, w - x0);                                                      // 4 or 8 (w % 4 == 0)
         drow[0] = o[0];
         if (n == 8) drow[1] = o[1];
+        if (a.n_mirror) {
+            const size_t off = (size_t)row * w + x0;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                if (q < (int)a.n_mirror) {
+                    if (n == 8 && (w & 7) == 0) {
+                        *reinterpret_cast<uint2 *>(a.mirror[q] + off) = make_uint2(o[0], o[1]);   // a warp stores 256 contiguous bytes
+                    } else {
+                        uint32_t *m = reinterpret_cast<uint32_t *>(a.mirror[q] + off);
+                        m[0] = o[0];
+                        if (n == 8) m[1] = o[1];
+                    }
+                }
+            }
+        }
         if (a.hist) {
             // neighbouring outputs are mostly equal: feed the shared-memory histogram run-length encoded
             uint32_t run_val = o[0] & 0xffu, run_len = 0;

@@ -19,7 +19,10 @@
 #include <mutex>
 #include <thread>
 
+#include <unistd.h>
+
 #include "ctx.cuh"
+#include "peer.cuh"
 
 #define STEPTH_ERR_NCCL 101
 
@@ -95,6 +98,16 @@ struct stepth_comm {
     stepth_ctx::Buf d8h, small;
     void *h_small = nullptr;     // pinned mirror of `small`
     cudaEvent_t marks[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // start | search | exchanges | finish | tail + gather
+    // peer window (peer.cuh): the exchanges as stores into the other ranks' HBM over NVLink
+    int peer_mode = -1;               // -1 not tried yet, 0 = not available (the exchanges go through NCCL), 1 = windows mapped
+    void *win = nullptr;              // this rank's window
+    size_t win_bytes = 0;
+    uint8_t *peer_base[8] = {};       // every rank's window as seen from this device ([rank] = win)
+    bool peer_opened[8] = {};         // mapped through a cudaIpc handle (another process): closed before the owner frees it
+    stepth_ctx::Buf xchg;             // bootstrap scratch: handles in, handles out
+    uint32_t seq = 0;                 // band calls so far (the same on every rank)
+    size_t off_d8h = 0, off_full = 0, halo_zone = 0;
+    bool win_has_full = false;
     // small state layout (u32 words): [0] max  [1] status  [2] n_out  [3] pad  [4..260) hist  then 512 bytes of ranges
     static constexpr size_t SMALL_BYTES = 4 * 260 + 512;
 };

@@ -41,9 +41,149 @@ static int32_t comm_alloc(stepth_ctx *ctx, int32_t n_ranks, int32_t rank, ncclCo
     return STEPTH_OK;
 }
 
+// ---- peer windows (peer.cuh) ---------------------------------------------------------------------------------------------------
+namespace {
+struct PeerInfo {   // what the ranks tell each other about their windows (bootstrap, over NCCL)
+    uint64_t pid, ptr;
+    int32_t device, ok;
+    cudaIpcMemHandle_t handle;
+};
+static_assert(sizeof(PeerInfo) <= 128, "bootstrap record");
+
+void comm_close_peers(stepth_comm *c) {
+    for (int q = 0; q < 8; ++q) {
+        if (c->peer_opened[q] && c->peer_base[q]) cudaIpcCloseMemHandle(c->peer_base[q]);
+        c->peer_opened[q] = false;
+        c->peer_base[q] = nullptr;
+    }
+}
+
+// window geometry for an image of w x h in n row bands (identical on every rank)
+struct WinPlan {
+    size_t halo_zone, off_d8h, off_full, bytes;
+};
+WinPlan win_plan(uint32_t w, uint32_t h, uint32_t add_h, uint32_t max_rings, int n, bool full) {
+    auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    uint32_t rows_max = 0;
+    for (int q = 0; q < n; ++q) {
+        uint32_t pq[4];
+        band_plan(h, add_h, max_rings, (uint32_t)n, (uint32_t)q, pq);
+        rows_max = std::max(rows_max, pq[1] - pq[0]);
+    }
+    WinPlan p;
+    p.halo_zone = ((size_t)BAND_HALO * w + 15) & ~(size_t)15;
+    p.off_d8h = up(PW_OFF_HALO + 4 * p.halo_zone);
+    p.off_full = up(p.off_d8h + (size_t)(rows_max + 2 * BAND_HALO) * w);
+    p.bytes = p.off_full + (full ? up((size_t)w * h) : 0);
+    return p;
+}
+
+// Makes sure every rank owns (and has mapped everybody's) window of at least plan.bytes.  COLLECTIVE: every rank of the group
+// calls it with the same plan.  On a box without peer access between the GPUs peer_mode becomes 0 and the caller uses NCCL.
+int32_t comm_ensure_window(stepth_comm *c, cudaStream_t st, const WinPlan &plan, bool full) {
+    stepth_ctx *ctx = c->ctx;
+    const int n = c->n_ranks, r = c->rank;
+    if (c->peer_mode == 0) return STEPTH_OK;
+    if (c->win && c->win_bytes >= plan.bytes && (c->win_has_full || !full) && c->off_d8h == plan.off_d8h &&
+        (!full || c->off_full == plan.off_full)) {
+        c->halo_zone = plan.halo_zone;
+        return STEPTH_OK;
+    }
+    NcclApi &nc = nccl_api();
+    int32_t rc;
+    if ((rc = ensure(ctx, c->xchg, 128 * 9 + 64)) != STEPTH_OK) return rc;
+    uint8_t *x_send = (uint8_t *)c->xchg.p, *x_recv = x_send + 128;
+    int *x_flag = (int *)(x_send + 128 * 9);
+    // nobody frees a window a peer still has mapped: close, meet, free
+    STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    comm_close_peers(c);
+    STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(x_flag, 0, sizeof(int), st));
+    STEPTH_NCCL_TRY(ctx, nc.AllReduce(x_flag, x_flag, 1, ncclInt32, ncclSum, c->nccl, st));
+    STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    if (c->win) STEPTH_CUDA_TRY(ctx, cudaFree(c->win));
+    c->win = nullptr;
+    c->win_bytes = 0;
+    STEPTH_CUDA_TRY(ctx, cudaMalloc(&c->win, plan.bytes));
+    STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(c->win, 0, PW_OFF_HALO, st));
+    PeerInfo me;
+    memset(&me, 0, sizeof me);
+    me.pid = (uint64_t)getpid();
+    me.ptr = (uint64_t)(uintptr_t)c->win;
+    me.device = ctx->device;
+    me.ok = cudaIpcGetMemHandle(&me.handle, c->win) == cudaSuccess ? 1 : 0;
+    (void)cudaGetLastError();
+    STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(x_send, &me, sizeof me, cudaMemcpyHostToDevice, st));
+    STEPTH_NCCL_TRY(ctx, nc.AllGather(x_send, x_recv, 128, ncclUint8, c->nccl, st));
+    std::vector<uint8_t> all((size_t)128 * n);
+    STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(all.data(), x_recv, all.size(), cudaMemcpyDeviceToHost, st));
+    STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    int ok = 1;
+    for (int q = 0; q < n; ++q) {
+        PeerInfo pi;
+        memcpy(&pi, all.data() + (size_t)128 * q, sizeof pi);
+        if (q == r) {
+            c->peer_base[q] = (uint8_t *)c->win;
+        } else if (pi.pid == me.pid) {   // a thread of this process drives that GPU (stepth_multi): plain peer access
+            int can = 0;
+            if (cudaDeviceCanAccessPeer(&can, ctx->device, pi.device) != cudaSuccess || !can) ok = 0;
+            else {
+                const cudaError_t e = cudaDeviceEnablePeerAccess(pi.device, 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) ok = 0;
+                (void)cudaGetLastError();
+                c->peer_base[q] = (uint8_t *)(uintptr_t)pi.ptr;
+            }
+        } else {
+            void *p = nullptr;
+            if (!pi.ok || cudaIpcOpenMemHandle(&p, pi.handle, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                ok = 0;
+                (void)cudaGetLastError();
+            } else {
+                c->peer_base[q] = (uint8_t *)p;
+                c->peer_opened[q] = true;
+            }
+        }
+    }
+    // all or nobody
+    STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(x_flag, &ok, sizeof(int), cudaMemcpyHostToDevice, st));
+    STEPTH_NCCL_TRY(ctx, nc.AllReduce(x_flag, x_flag, 1, ncclInt32, ncclMin, c->nccl, st));
+    STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(&ok, x_flag, sizeof(int), cudaMemcpyDeviceToHost, st));
+    STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    if (!ok) {
+        comm_close_peers(c);
+        STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(x_flag, 0, sizeof(int), st));   // the owners free only after everybody has let go
+        STEPTH_NCCL_TRY(ctx, nc.AllReduce(x_flag, x_flag, 1, ncclInt32, ncclSum, c->nccl, st));
+        STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(st));
+        cudaFree(c->win);
+        c->win = nullptr;
+        c->peer_mode = 0;
+        return STEPTH_OK;
+    }
+    c->peer_mode = 1;
+    c->win_bytes = plan.bytes;
+    c->win_has_full = full;
+    c->off_d8h = plan.off_d8h;
+    c->off_full = plan.off_full;
+    c->halo_zone = plan.halo_zone;
+    c->seq = 0;   // the new windows' flags start at zero on every rank
+    return STEPTH_OK;
+}
+
+PeerView comm_view(const stepth_comm *c) {
+    PeerView v;
+    memset(&v, 0, sizeof v);
+    for (int q = 0; q < c->n_ranks && q < 8; ++q) v.base[q] = c->peer_base[q];
+    v.n = c->n_ranks;
+    v.rank = c->rank;
+    return v;
+}
+}  // namespace
+
 extern "C" void stepth_cuda_comm_destroy(stepth_comm *c) {
     if (!c) return;
     if (c->ctx) cudaSetDevice(c->ctx->device);
+    comm_close_peers(c);
+    if (c->win) cudaFree(c->win);
+    if (c->xchg.p) cudaFree(c->xchg.p);
     if (c->nccl && c->owns_nccl && nccl_api().lib) nccl_api().CommDestroy(c->nccl);
     if (c->d8h.p) cudaFree(c->d8h.p);
     if (c->small.p) cudaFree(c->small.p);
@@ -95,7 +235,15 @@ extern "C" int32_t stepth_cuda_dev_depth_dense_band(stepth_comm *c, void *stream
     cudaStream_t st = (cudaStream_t)stream;
     STEPTH_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     int32_t rc;
-    if ((rc = ensure(ctx, c->d8h, (size_t)(rows + 2 * BAND_HALO) * w)) != STEPTH_OK) return rc;
+    // the exchanges: stores into the peers' windows over NVLink (peer.cuh) when every GPU of the group reaches every other, NCCL
+    // otherwise (and with STEPTH_PEER=0)
+    bool peer = n > 1 && n <= PW_MAX_RANKS && ctx->peer_enabled && c->peer_mode != 0;
+    if (peer) {
+        const WinPlan plan = win_plan(w, h, add_h, params->max_rings, n, depth_full_out != nullptr || c->win_has_full);
+        if ((rc = comm_ensure_window(c, st, plan, depth_full_out != nullptr || c->win_has_full)) != STEPTH_OK) return rc;
+        peer = c->peer_mode == 1;
+    }
+    if (!peer && (rc = ensure(ctx, c->d8h, (size_t)(rows + 2 * BAND_HALO) * w)) != STEPTH_OK) return rc;
     if ((rc = ensure(ctx, c->small, stepth_comm::SMALL_BYTES)) != STEPTH_OK) return rc;
     if (!c->h_small) STEPTH_CUDA_TRY(ctx, cudaMallocHost(&c->h_small, stepth_comm::SMALL_BYTES));
     uint32_t *sm = (uint32_t *)c->small.p;
@@ -106,7 +254,10 @@ extern "C" int32_t stepth_cuda_dev_depth_dense_band(stepth_comm *c, void *stream
         if (!e) STEPTH_CUDA_TRY(ctx, cudaEventCreate(&e));
     STEPTH_CUDA_TRY(ctx, cudaEventRecord(c->marks[0], st));
     STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(c->small.p, 0, stepth_comm::SMALL_BYTES, st));
-    uint8_t *d8 = (uint8_t *)c->d8h.p + (size_t)BAND_HALO * w;
+    uint8_t *d8h = peer ? (uint8_t *)c->win + c->off_d8h : (uint8_t *)c->d8h.p;
+    uint8_t *d8 = d8h + (size_t)BAND_HALO * w;
+    const PeerView pv = comm_view(c);
+    if (peer) ++c->seq;
 
     // 1. ring search of this band (helpers.rs:9-54, depth_image.rs:113-122); the per-band maximum lands in d_max
     stepth_dev_shape s;
@@ -116,7 +267,16 @@ extern "C" int32_t stepth_cuda_dev_depth_dense_band(stepth_comm *c, void *stream
     if ((rc = stepth_cuda_dev_search_dense(ctx, st, &s, params, main_band, add_band, d8, d_max)) != STEPTH_OK) return rc;
     STEPTH_CUDA_TRY(ctx, cudaEventRecord(c->marks[1], st));
     const uint32_t above = r > 0 ? std::min(BAND_HALO, y0) : 0u, below = r < n - 1 ? std::min(BAND_HALO, h - y1) : 0u;
-    if (n > 1) {
+    if (peer) {
+        // 2 + 3. one kernel: my maximum into every mailbox, my first / last three rows into the neighbours' halo zones, flags,
+        // the maximum over all bands (depth_image.rs:124), the neighbours' rows next to my band (:133)
+        PeerExchangeArgs xa;
+        xa.pv = pv; xa.seq = c->seq; xa.halo_zone = c->halo_zone; xa.halo_bytes = (size_t)BAND_HALO * w;
+        xa.band = d8; xa.rows = rows; xa.w = w; xa.max_io = d_max; xa.timed_out = sm + 3;
+        peer_exchange_kernel<<<8, 256, 0, st>>>(xa);
+        ctx->launches++;
+        STEPTH_CUDA_TRY(ctx, cudaGetLastError());
+    } else if (n > 1) {
         // 2. exchange 1: the normaliser is the maximum over the WHOLE image (depth_image.rs:124)
         STEPTH_NCCL_TRY(ctx, nc.AllReduce(d_max, d_max, 1, ncclUint32, ncclMax, c->nccl, st));
         // 3. exchange 2: the unit-scale Gaussian (:133) reads 3 rows across each seam
@@ -124,7 +284,7 @@ extern "C" int32_t stepth_cuda_dev_depth_dense_band(stepth_comm *c, void *stream
         STEPTH_NCCL_TRY(ctx, nc.GroupStart());
         if (r > 0) {
             STEPTH_NCCL_TRY(ctx, nc.Send(d8, hb, ncclUint8, r - 1, c->nccl, st));
-            STEPTH_NCCL_TRY(ctx, nc.Recv(c->d8h.p, hb, ncclUint8, r - 1, c->nccl, st));
+            STEPTH_NCCL_TRY(ctx, nc.Recv(d8h, hb, ncclUint8, r - 1, c->nccl, st));
         }
         if (r < n - 1) {
             STEPTH_NCCL_TRY(ctx, nc.Send(d8 + (size_t)(rows - BAND_HALO) * w, hb, ncclUint8, r + 1, c->nccl, st));
@@ -135,9 +295,18 @@ extern "C" int32_t stepth_cuda_dev_depth_dense_band(stepth_comm *c, void *stream
     STEPTH_CUDA_TRY(ctx, cudaEventRecord(c->marks[2], st));
     // 4. normalise + Gaussian (+ invert, + histogram) of the band, halo rows as source only
     const uint32_t fin_flags = flags & (STEPTH_RESAMPLE_MASK | STEPTH_FLAG_INVERT);
-    if ((rc = stepth_cuda_dev_finish(ctx, st, 1, w, h, d8 - (size_t)above * w, y0 - above, above + rows + below, d_max, fin_flags,
-                                     depth_band_out, y0, rows, want_fg ? d_hist : nullptr, d_status)) != STEPTH_OK)
-        return rc;
+    const bool peer_gather = peer && depth_full_out != nullptr;
+    if (peer_gather) {   // 6 rides on 4: the pass that produces the depth band stores it into every rank's assembled map
+        for (int q = 0; q < n; ++q) ctx->finish_mirror[q] = pv.base[q] + c->off_full + (size_t)y0 * w;
+        ctx->finish_n_mirror = (uint32_t)n;
+    }
+    ctx->finish_mirrored = 0;
+    rc = stepth_cuda_dev_finish(ctx, st, 1, w, h, d8 - (size_t)above * w, y0 - above, above + rows + below, d_max, fin_flags,
+                                depth_band_out, y0, rows, want_fg ? d_hist : nullptr, d_status);
+    ctx->finish_n_mirror = 0;
+    const bool mirrored = ctx->finish_mirrored != 0;
+    ctx->finish_mirrored = 0;
+    if (rc != STEPTH_OK) return rc;
     STEPTH_CUDA_TRY(ctx, cudaEventRecord(c->marks[3], st));
     if (want_fg) {
         // 5. exchange 3: depth_split runs on the histogram of the whole image (depth_image.rs:162-218); every rank then
@@ -150,7 +319,21 @@ extern "C" int32_t stepth_cuda_dev_depth_dense_band(stepth_comm *c, void *stream
                                                  want_apply ? rgba_band_out : nullptr)) != STEPTH_OK)
                 return rc;
     }
-    if (depth_full_out) {
+    if (peer_gather) {
+        // 6. exchange 4: the bands are already on their way (mirror stores of the finish pass; a copy kernel when that pass could
+        // not mirror); one flag round later every band has landed in every rank's window
+        if (!mirrored) {
+            peer_scatter_kernel<<<(unsigned)ctx->sm_count, 256, 0, st>>>(pv, c->off_full + (size_t)y0 * w, depth_band_out, (size_t)rows * w);
+            ctx->launches++;
+            STEPTH_CUDA_TRY(ctx, cudaGetLastError());
+        }
+        peer_barrier_kernel<<<1, 32, 0, st>>>(pv, 1, c->seq, sm + 3);
+        ctx->launches++;
+        STEPTH_CUDA_TRY(ctx, cudaGetLastError());
+        uint8_t *own_full = (uint8_t *)c->win + c->off_full;
+        if (depth_full_out != own_full)
+            STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(depth_full_out, own_full, (size_t)w * h, cudaMemcpyDeviceToDevice, st));
+    } else if (depth_full_out) {
         // 6. exchange 4 (optional): the assembled map on every GPU -- one broadcast per band, grouped (bands may differ in height)
         bool equal = true;   // equal bands are consecutive slabs of the assembled map: one all-gather straight into it
         for (int q = 0; q < n; ++q) {
@@ -179,6 +362,30 @@ extern "C" int32_t stepth_cuda_dev_depth_dense_band(stepth_comm *c, void *stream
     return STEPTH_OK;
 }
 
+// 1 when the band exchanges of this group go through peer windows over NVLink (peer.cuh), 0 when through NCCL, -1 before the
+// first multi-rank band call has decided
+extern "C" int32_t stepth_cuda_comm_peer_mode(const stepth_comm *c) { return c ? c->peer_mode : -1; }
+
+// The assembled depth map inside this rank's window (device pointer, w * h bytes, valid until the group is destroyed or a larger
+// image is banded): a caller that hands it to stepth_cuda_dev_depth_dense_band as depth_full_out saves the copy out of the
+// window.  COLLECTIVE (every rank calls it with the same arguments); *ptr_out = NULL when the group runs over NCCL.
+extern "C" int32_t stepth_cuda_comm_full_map(stepth_comm *c, void *stream, uint32_t w, uint32_t h, uint32_t add_h, uint32_t max_rings,
+                                             uint8_t **ptr_out) {
+    if (!c || !c->ctx) return STEPTH_ERR_INVALID_ARG;
+    if (!ptr_out || w == 0 || h == 0 || add_h == 0 || max_rings == 0) return set_err(c->ctx, STEPTH_ERR_INVALID_ARG, "comm_full_map: invalid argument");
+    *ptr_out = nullptr;
+    stepth_ctx *ctx = c->ctx;
+    STEPTH_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    if (c->n_ranks < 2 || c->n_ranks > PW_MAX_RANKS || !ctx->peer_enabled || c->peer_mode == 0) return STEPTH_OK;
+    NcclApi &nc = nccl_api();
+    if (!nc.lib) return set_err(ctx, STEPTH_ERR_NCCL, "%s", nc.why.c_str());
+    const WinPlan plan = win_plan(w, h, add_h, max_rings, c->n_ranks, true);
+    const int32_t rc = comm_ensure_window(c, (cudaStream_t)stream, plan, true);
+    if (rc != STEPTH_OK) return rc;
+    if (c->peer_mode == 1) *ptr_out = (uint8_t *)c->win + c->off_full;
+    return STEPTH_OK;
+}
+
 // milliseconds the last band call spent in: search | MAX all-reduce + halo exchange (the wait for the slowest band shows up
 // here) | finish | tail + gather.  Call after stepth_cuda_comm_band_result.
 extern "C" int32_t stepth_cuda_comm_band_stage_ms(stepth_comm *c, float *ms_out) {
@@ -194,6 +401,7 @@ extern "C" int32_t stepth_cuda_comm_band_result(stepth_comm *c, void *stream, in
     STEPTH_CUDA_TRY(c->ctx, cudaSetDevice(c->ctx->device));
     STEPTH_CUDA_TRY(c->ctx, cudaStreamSynchronize((cudaStream_t)stream));
     const uint32_t *sm = (const uint32_t *)c->h_small;
+    if (sm[3]) return set_err(c->ctx, STEPTH_ERR_NCCL, "row-band exchange: a peer's flag did not arrive within 20 s (peer.cuh)");
     // max == 0 is a property of the whole image: every rank holds the same all-reduced value
     const int32_t st = sm[0] == 0 ? STEPTH_ERR_DIV_BY_ZERO_MAX : (int32_t)sm[1];
     if (status_out) *status_out = st;

@@ -88,6 +88,7 @@ extern "C" int32_t stepth_cuda_ctx_create(int32_t device, stepth_ctx **ctx_out) 
     if (const char *ev = getenv("STEPTH_TWO_STREAMS")) ctx->two_streams = atoi(ev);
     if (const char *ev = getenv("STEPTH_FINISH_STREAMING")) ctx->finish_streaming = atoi(ev);
     if (const char *ev = getenv("STEPTH_TRACE")) ctx->trace = atoi(ev);
+    if (const char *ev = getenv("STEPTH_PEER")) ctx->peer_enabled = atoi(ev);
     if (const char *ev = getenv("STEPTH_UPLOAD_FULL_ROWS")) ctx->upload_full_rows = atoi(ev);
     ctx->stage_threads = (int)std::max(2u, std::min(8u, std::thread::hardware_concurrency() / 2));
     if (const char *ev = getenv("STEPTH_STAGE_THREADS")) ctx->stage_threads = std::max(0, std::min(64, atoi(ev)));
@@ -328,6 +329,11 @@ extern "C" int32_t stepth_cuda_dev_finish(stepth_ctx *ctx, void *stream, uint32_
         if (gv.y > 65535) return set_err(ctx, STEPTH_ERR_INVALID_ARG, "dev_finish: more than 1M rows in one band");
         finish_vert_kernel<<<gv, 128, 0, st>>>(a, (uint8_t *)tmp.p);
         LAUNCH_CHECK(ctx);
+        if (ctx->finish_n_mirror && n_pairs == 1) {   // set by the row-band call (multi_api.cuh) around this one
+            for (uint32_t q = 0; q < ctx->finish_n_mirror && q < 8; ++q) a.mirror[q] = ctx->finish_mirror[q];
+            a.n_mirror = std::min(ctx->finish_n_mirror, 8u);
+            ctx->finish_mirrored = 1;
+        }
         finish_horz_kernel<<<gh, 256, 0, st>>>(a, (const uint8_t *)tmp.p);
         LAUNCH_CHECK(ctx);
         return STEPTH_OK;

@@ -814,20 +814,43 @@ def _band_worker(rank, world, port, w, h, rings, q):
         out = runner.run(mb, ab, gather_depth=True)
         torch.cuda.synchronize()
         # the same through the C ABI's own communicator (csrc/multi_api.cuh: NCCL called by the library)
+        def same_as_torch(res):
+            return (res["status"] == out["status"] and res.get("from_to") == out.get("from_to")
+                    and all(torch.equal(res[k], out[k]) for k in ("depth", "depth_band", "mask_band", "rgba_band")))
+
         crun = bands.CommBandRunner(c, w, h, h, P36, rings, flags)
-        cout = crun.run(mb, ab, gather_depth=True)
-        same = (cout["status"] == out["status"] and cout.get("from_to") == out.get("from_to")
-                and all(torch.equal(cout[k], out[k]) for k in ("depth", "depth_band", "mask_band", "rgba_band")))
+        same = True
+        for _ in range(3):   # three calls: the mailboxes and halo zones of the peer windows alternate with the call's parity
+            same = same and same_as_torch(crun.run(mb, ab, gather_depth=True))
+        peer_mode = crun.peer_mode()
+        # a second image through the same group: other bytes in the same windows
+        m2, a2 = synth.make_pair("nat", w, h, 10)
+        one = sb.Context(rank).depth_dense(m2.numpy(), a2.numpy(), P36, rings, flags) if rank == 0 else None
+        res2 = crun.run(m2[None, b.y0:b.y1].cuda().contiguous(), a2[None, b.ay0:b.ay1].cuda().contiguous(), gather_depth=True)
+        if rank == 0:
+            same = same and res2["status"] == 0 and res2["from_to"] == one["from_to"] and np.array_equal(res2["depth"][0].cpu().numpy(), one["depth"])
         crun.close()
+        # the same exchanges through NCCL (what a box without peer access between its GPUs runs)
+        os.environ["STEPTH_PEER"] = "0"
+        c_nccl = sb.Context(rank)
+        del os.environ["STEPTH_PEER"]
+        nrun = bands.CommBandRunner(c_nccl, w, h, h, P36, rings, flags)
+        same_nccl = same_as_torch(nrun.run(mb, ab, gather_depth=True)) and nrun.peer_mode() != 1
+        nrun.close()
         q.put({"rank": rank, "band": (b.y0, b.y1), "status": out["status"], "from_to": out.get("from_to"),
                "depth": out["depth"][0].cpu().numpy(), "mask_band": out["mask_band"][0].cpu().numpy(),
-               "rgba_band": out["rgba_band"][0].cpu().numpy(), "comm_runner_same": bool(same)})
+               "rgba_band": out["rgba_band"][0].cpu().numpy(), "comm_runner_same": bool(same), "peer_mode": peer_mode,
+               "nccl_runner_same": bool(same_nccl)})
     finally:
         dist.destroy_process_group()
 
 
-def test_row_bands_over_nccl_equal_one_gpu(ctx, orc):
-    """configs[4]'s decomposition on every GPU of the box: bands + MAX all-reduce + halo exchange + NCCL all-gather"""
+@pytest.mark.parametrize("w", [320, 324, 321])   # rows of whole 8-byte words, of whole 4-byte words (mirror stores word by word),
+                                                  # odd (the tiled finish pass does not mirror: the band goes out by a copy kernel)
+def test_row_bands_over_nccl_equal_one_gpu(ctx, orc, w):
+    """configs[4]'s decomposition on every GPU of the box: bands + the normaliser's maximum + halo exchange + the gather of the
+    depth bands -- by torch.distributed, by the library over peer windows (NVLink stores, csrc/peer.cuh) and by the library over
+    NCCL -- against one GPU"""
     world = torch.cuda.device_count()
     if world < 2:
         pytest.skip("needs at least 2 GPUs")
@@ -837,7 +860,7 @@ def test_row_bands_over_nccl_equal_one_gpu(ctx, orc):
 
     import stepth_b200 as sb
 
-    w, h, rings = 320, 250, 48
+    h, rings = 250, 48
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
@@ -856,6 +879,8 @@ def test_row_bands_over_nccl_equal_one_gpu(ctx, orc):
         y0, y1 = r["band"]
         assert r["status"] == 0 and r["from_to"] == host["from_to"]
         assert r["comm_runner_same"], "stepth_cuda_dev_depth_dense_band disagrees with the torch.distributed orchestration"
+        assert r["nccl_runner_same"], "the NCCL fallback of the band exchanges disagrees"
+        assert r["peer_mode"] in (0, 1)
         assert np.array_equal(r["depth"], host["depth"])
         assert np.array_equal(r["mask_band"], host["mask"][y0:y1])
         assert np.array_equal(r["rgba_band"], host["rgba"][y0:y1])
