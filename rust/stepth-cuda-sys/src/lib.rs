@@ -1,5 +1,7 @@
 //! Raw bindings to `libstepth_cuda.so` -- one declaration per symbol of `include/stepth_cuda.h` that the patched
-//! `stepth` crate calls.  (The `stepth_cuda_dev_*` stage API is for in-process GPU pipelines and is not bound here.)
+//! `stepth` crate calls, plus the batch and multi-GPU entry points a batch tool built on the crate would use.  (The
+//! `stepth_cuda_dev_*` stage API and `stepth_comm` are for in-process GPU pipelines / one-process-per-GPU launchers and are
+//! not bound here.)
 #![allow(non_camel_case_types)]
 use std::os::raw::{c_char, c_double};
 
@@ -12,6 +14,7 @@ pub const STEPTH_ERR_DEGENERATE_DEPTH: i32 = 5;
 pub const STEPTH_ERR_NO_CONVERGENCE: i32 = 6;
 pub const STEPTH_ERR_OUT_OF_BOUNDS: i32 = 7;
 pub const STEPTH_ERR_CUDA: i32 = 100;
+pub const STEPTH_ERR_NCCL: i32 = 101;
 
 pub const STEPTH_RESAMPLE_OFF: u32 = 0;
 pub const STEPTH_RESAMPLE_U8: u32 = 1;
@@ -23,6 +26,12 @@ pub const STEPTH_FLAG_PIXELOPPS_SAT: u32 = 1 << 5;
 
 #[repr(C)]
 pub struct stepth_ctx {
+    _private: [u8; 0],
+}
+
+/// one process driving several GPUs: a context and a host thread per device
+#[repr(C)]
+pub struct stepth_multi {
     _private: [u8; 0],
 }
 
@@ -68,6 +77,51 @@ extern "C" {
         ctx: *mut stepth_ctx, n_pairs: u32, main_rgba: *const *const u8, w: u32, h: u32, add_rgb: *const *const u8,
         wa: u32, ha: u32, params: *const stepth_params, depth_out: *const *mut u8, rgba_out: *const *mut u8,
         mask_out: *const *mut u8, from_to_out: *mut u8, status_out: *mut i32,
+    ) -> i32;
+
+    /// `load_depth_from_additional` whole (src/depth_image.rs:91-136) with the stand-in discretiser on the device
+    pub fn stepth_cuda_depth_from_additional(
+        ctx: *mut stepth_ctx, main_rgba: *const u8, w: u32, h: u32, add_rgb: *const u8, wa: u32, ha: u32,
+        params: *const stepth_params, min_splits: u32, max_splits: u32, depth_out: *mut u8, rgba_out: *mut u8,
+        mask_out: *mut u8, from_to_out: *mut u8, n_blocks_out: *mut usize,
+    ) -> i32;
+    pub fn stepth_cuda_discretise_v0(
+        ctx: *mut stepth_ctx, main_px: *const u8, stride: u32, w: u32, h: u32, precision: *const u8, min_splits: u32,
+        max_splits: u32, blocks_out: *mut stepth_block, cap: usize, n_out: *mut usize,
+    ) -> i32;
+    pub fn stepth_host_discretise_v0(
+        main_px: *const u8, stride: u32, w: u32, h: u32, precision: *const u8, min_splits: u32, max_splits: u32,
+        blocks_out: *mut stepth_block, cap: usize,
+    ) -> usize;
+
+    pub fn stepth_cuda_depth_dense(
+        ctx: *mut stepth_ctx, main_rgba: *const u8, w: u32, h: u32, add_rgb: *const u8, wa: u32, ha: u32,
+        params: *const stepth_params, depth_out: *mut u8, raw_d8_out: *mut u8, rgba_out: *mut u8, mask_out: *mut u8,
+        from_to_out: *mut u8,
+    ) -> i32;
+    pub fn stepth_cuda_depth_dense_batch(
+        ctx: *mut stepth_ctx, n_pairs: u32, main_rgba: *const *const u8, w: u32, h: u32, add_rgb: *const *const u8,
+        wa: u32, ha: u32, params: *const stepth_params, depth_out: *const *mut u8, rgba_out: *const *mut u8,
+        mask_out: *const *mut u8, from_to_out: *mut u8, status_out: *mut i32,
+    ) -> i32;
+    pub fn stepth_cuda_depth_dense_batch_rgb(
+        ctx: *mut stepth_ctx, n_pairs: u32, main_rgb: *const *const u8, w: u32, h: u32, add_rgb: *const *const u8,
+        wa: u32, ha: u32, params: *const stepth_params, depth_out: *const *mut u8, mask_out: *const *mut u8,
+        from_to_out: *mut u8, status_out: *mut i32,
+    ) -> i32;
+
+    // several GPUs from one process: pair batches dealt to the devices; one giant pair in row bands
+    pub fn stepth_cuda_multi_create(devices: *const i32, n_devices: u32, multi_out: *mut *mut stepth_multi) -> i32;
+    pub fn stepth_cuda_multi_destroy(multi: *mut stepth_multi);
+    pub fn stepth_cuda_multi_last_error(multi: *const stepth_multi) -> *const c_char;
+    pub fn stepth_cuda_multi_depth_dense_batch(
+        multi: *mut stepth_multi, n_pairs: u32, main_rgba: *const *const u8, w: u32, h: u32,
+        add_rgb: *const *const u8, wa: u32, ha: u32, params: *const stepth_params, depth_out: *const *mut u8,
+        rgba_out: *const *mut u8, mask_out: *const *mut u8, from_to_out: *mut u8, status_out: *mut i32,
+    ) -> i32;
+    pub fn stepth_cuda_multi_depth_dense_banded(
+        multi: *mut stepth_multi, main_rgba: *const u8, w: u32, h: u32, add_rgb: *const u8, wa: u32, ha: u32,
+        params: *const stepth_params, depth_out: *mut u8, rgba_out: *mut u8, mask_out: *mut u8, from_to_out: *mut u8,
     ) -> i32;
 
     pub fn stepth_cuda_invert_depth(ctx: *mut stepth_ctx, depth_inout: *mut u8, n: usize) -> i32;
