@@ -34,7 +34,7 @@ struct stepth_ctx {
     Buf main_rgba, add_rgb, d8, depth, mask, rgba_out, blocks, plane, small, u16a, u16b, u16o, work;
     Buf worklist;  // two [count, cursor, pad..][uint2 entries] lists: queries handed from the near to the far kernel(s)
     int near_rings = 6;  // coarse rings the near kernel walks (STEPTH_NEAR_RINGS)
-    int batch_chunks = 8;  // the batch entry point pipelines this many chunks of pairs over its three streams (STEPTH_BATCH_CHUNKS)
+    int batch_chunks = 0;  // the batch entry point pipelines this many chunks of pairs over its three streams (STEPTH_BATCH_CHUNKS; 0 = 8, or 16 from 64 pairs on)
     cudaEvent_t main_ready = nullptr;  // set by the batch entry point: the dense search waits for it between K0 and K1 (the
                                        // main images are still on their way up while the planes of the additional ones are built)
     int trace = 0;  // STEPTH_TRACE=1: the batch entry point prints each chunk's copy-in / compute / copy-out end times to stderr
@@ -51,11 +51,12 @@ struct stepth_ctx {
     int finish_streaming = 1;       // STEPTH_FINISH_STREAMING: 0 = always the tiled finish kernel
     int two_streams = 1;     // STEPTH_TWO_STREAMS
     stepth::Stager stager;   // pinned rings + copy threads for pageable caller buffers (batch path; created on first use)
-    int stage_threads = 8;   // STEPTH_STAGE_THREADS: copy threads (the caller included; default min(8, cores / 2)); 0 = hand pageable pointers to the driver
+    int stage_threads = 8;   // STEPTH_STAGE_THREADS: copy threads (the caller included; default min(16, usable cpus / 2)); 0 = hand pageable pointers to the driver
     Buf main_rgb;            // RGB8 main images as uploaded by the *_rgb entry point, expanded to main_rgba on the device
     uint8_t *finish_mirror[8] = {};  // row bands: where the next dev_finish call also stores its outputs (peer.cuh); cleared by the caller
     uint32_t finish_n_mirror = 0;
     int finish_mirrored = 0;         // set by dev_finish when it did
+    int k0_tensor_map = 1;           // STEPTH_K0_TMAP=0: K0's strips by per-row bulk copies / plain loads only
     int peer_enabled = 1;            // STEPTH_PEER=0: the row-band exchanges go through NCCL instead of peer windows
     Buf disc_counts;         // device discretiser: leaves per top-level region, then their offsets (disc.cuh)
     int blocks_on_device = 0;  // run_pairs: the block list it is handed already lies in HBM (stepth_cuda_depth_from_additional)

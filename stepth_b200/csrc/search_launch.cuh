@@ -33,7 +33,29 @@ inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const Search
     h.planes = (const uint8_t *)planes.p;
     if (h.g.nty > 65535u) return set_err(ctx, STEPTH_ERR_INVALID_ARG, "too many tile rows for one launch");
     TileBuildArgs p{a.add_rgb, (size_t)a.ha * a.wa * 3, (uint8_t *)planes.p, h.g, a.pr, a.pg, a.pb, a.sat};
-    tile_planes_kernel<<<dim3(h.g.nxw, h.g.nty, n_pairs), 256, 0, st>>>(p);
+    // the strips of K0 come in through a tensor map when the images allow one: rows that start on 16 bytes (the same condition
+    // the per-row bulk copies have), at least one full 16-byte word per row
+    CUtensorMap tmap;
+    memset(&tmap, 0, sizeof tmap);
+    int use_tmap = 0;
+    const size_t pitch = (size_t)a.wa * 3;
+    if (ctx->k0_tensor_map && (pitch & 15) == 0 && (reinterpret_cast<uintptr_t>(a.add_rgb) & 15) == 0 && pitch / 4 <= 0xffffffffull) {
+        static const auto encode = [] {
+            void *fn = nullptr;
+            cudaDriverEntryPointQueryResult q;
+            if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) fn = nullptr;
+            (void)cudaGetLastError();
+            return (decltype(&cuTensorMapEncodeTiled))fn;
+        }();
+        if (encode) {
+            const cuuint64_t dims[3] = {(cuuint64_t)(pitch / 4), (cuuint64_t)a.ha, (cuuint64_t)n_pairs};
+            const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)p.src_pair_bytes};   // bytes, dimensions 1 and 2
+            const cuuint32_t box[3] = {192u, 8u, 1u}, estr[3] = {1u, 1u, 1u};
+            use_tmap = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, (void *)a.add_rgb, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+        }
+    }
+    tile_planes_kernel<<<dim3(h.g.nxw, h.g.nty, n_pairs), 256, 0, st>>>(p, tmap, use_tmap);
     ctx->launches++;
     STEPTH_CUDA_TRY(ctx, cudaGetLastError());
     coarse_transpose_kernel<<<dim3(h.g.nxw, h.g.nyw, n_pairs * CT_PARTS), 256, 0, st>>>(p);

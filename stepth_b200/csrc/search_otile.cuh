@@ -27,7 +27,7 @@ namespace stepth {
 #if defined(__CUDACC__)
 
 #ifndef STEPTH_OT_MINB
-#define STEPTH_OT_MINB 20   // resident CTAs per SM the register allocation must allow: 20 x 64 threads -> 48 registers
+#define STEPTH_OT_MINB 18   // resident CTAs per SM the register allocation must allow: 18 x 64 threads -> 56 registers (64: 2.16 ms, 56: 2.10, 48: 2.12, 40: 2.16)
 #endif
 #ifndef STEPTH_OT_WARPS
 #define STEPTH_OT_WARPS 2   // measured (16 pairs 1080p, search stage): 2 warps / 48 registers 2.13 ms, 4 / 48 2.15, 4 / 64 2.21, 8 / 48 2.45

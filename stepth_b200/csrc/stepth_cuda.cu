@@ -15,6 +15,8 @@
 #include "edit.cuh"
 #include "disc.cuh"
 
+#include <sched.h>
+
 #include <algorithm>
 
 using namespace stepth;
@@ -84,13 +86,21 @@ extern "C" int32_t stepth_cuda_ctx_create(int32_t device, stepth_ctx **ctx_out) 
     if (const char *ev = getenv("STEPTH_OT_RINGS")) ctx->near_rings_otile = atoi(ev);
     if (const char *ev = getenv("STEPTH_OT_NIT")) ctx->otile_nit = atoi(ev);
     if (const char *ev = getenv("STEPTH_OT_WARPS_PER_SM")) ctx->otile_warps_per_sm = std::max(1, atoi(ev));
-    if (const char *ev = getenv("STEPTH_BATCH_CHUNKS")) ctx->batch_chunks = atoi(ev);
+    if (const char *ev = getenv("STEPTH_BATCH_CHUNKS")) ctx->batch_chunks = std::max(0, atoi(ev));
     if (const char *ev = getenv("STEPTH_TWO_STREAMS")) ctx->two_streams = atoi(ev);
     if (const char *ev = getenv("STEPTH_FINISH_STREAMING")) ctx->finish_streaming = atoi(ev);
     if (const char *ev = getenv("STEPTH_TRACE")) ctx->trace = atoi(ev);
     if (const char *ev = getenv("STEPTH_PEER")) ctx->peer_enabled = atoi(ev);
+    if (const char *ev = getenv("STEPTH_K0_TMAP")) ctx->k0_tensor_map = atoi(ev);
     if (const char *ev = getenv("STEPTH_UPLOAD_FULL_ROWS")) ctx->upload_full_rows = atoi(ev);
-    ctx->stage_threads = (int)std::max(2u, std::min(8u, std::thread::hardware_concurrency() / 2));
+    {   // copy threads behind pageable host buffers: half of the CPUs this process may run on (its affinity mask -- a launcher
+        // that binds one process per GPU to the GPU's NUMA neighbourhood narrows it), at most 16 (64 x 4K, pageable: 8 threads
+        // 33.5 ms per 16 pairs, 12: 33.3, 16: 29.2)
+        unsigned cpus = std::thread::hardware_concurrency();
+        cpu_set_t set;
+        if (sched_getaffinity(0, sizeof set, &set) == 0 && CPU_COUNT(&set) > 0) cpus = (unsigned)CPU_COUNT(&set);
+        ctx->stage_threads = (int)std::max(2u, std::min(16u, cpus / 2));
+    }
     if (const char *ev = getenv("STEPTH_STAGE_THREADS")) ctx->stage_threads = std::max(0, std::min(64, atoi(ev)));
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
         g_create_err = std::string("cudaStreamCreate failed: ") + cudaGetErrorString(e);
@@ -496,7 +506,9 @@ int32_t run_pairs_impl(stepth_ctx *ctx, uint32_t n, const uint8_t *const *main_r
     // The batch is cut into chunks of pairs that move through three streams: copy_in uploads chunk k+1 while the compute
     // stream works on chunk k and copy_out brings chunk k-1 back, so the PCIe transfers hide behind the kernels.
     // The first chunk is half a chunk (the compute stream starts sooner) and so, then, is the last (a shorter copy-out tail).
-    const uint32_t parts = (uint32_t)std::max(1, ctx->batch_chunks);
+    // 8 chunks, or chunks of about 4 pairs for larger batches (64 x 4K fused in 8 / 16 / 32 chunks: 76.1 / 72.4 / 74.2 ms per call; the pipeline's un-overlapped
+    // first upload and last download shrink with the chunk)
+    const uint32_t parts = (uint32_t)std::max(1, ctx->batch_chunks > 0 ? ctx->batch_chunks : (int)std::min(32u, std::max(8u, n / 4)));
     const uint32_t chunk = (blocks || n <= 2) ? n : (n + parts - 1) / parts;
     std::vector<uint32_t> bounds{0};
     if (chunk >= 2 && chunk < n) bounds.push_back(chunk / 2);

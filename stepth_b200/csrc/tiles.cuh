@@ -35,6 +35,8 @@
 //
 // Algorithmic bytes per additional pixel: 3 read; 3 * 50 * 8 / 64 = 18.75 written (fine) + 2 * 2 * 3 * 256 / (8 * 64) = 6 (coarse).
 #pragma once
+#include <cuda.h>   // CUtensorMap (the encode function is resolved at run time through cudaGetDriverEntryPoint: no libcuda link)
+
 #include "common.cuh"
 
 namespace stepth {
@@ -180,8 +182,12 @@ __device__ __forceinline__ uint32_t dilate_values(uint32_t x, int lane16, int R,
 // 256 contiguous bytes (U) + 144 bytes (the 18 extra planes).  The coarse level: the set of values present in the tile
 // (warp OR-reductions) is dilated into E, 256 bits per (tile, channel); the CTA transposes the 32 tiles x 256 values of
 // a channel into 256 words of 32 tile bits and stores the cell with coalesced lines.
-__global__ void __launch_bounds__(256) tile_planes_kernel(TileBuildArgs a) {
-    __shared__ __align__(16) uint32_t s_raw[8][192];    // [row][interleaved RGB of 256 pixels]
+// `tmap` (use_tmap != 0): a rank-3 tensor map over the additional images as u32 words {row words, rows, pairs}; the CTA's strip
+// is ONE 2-D box of 192 words x 8 rows brought in by the TMA unit (cp.async.bulk.tensor), rows and words beyond the image
+// zero-filled by the unit.  A tensor map needs what the per-row bulk copies need (rows that start on 16 bytes), so images
+// whose pitch is not a multiple of 16 bytes -- the README pair's 1800-byte rows -- stay on the plain-load paths below.
+__global__ void __launch_bounds__(256) tile_planes_kernel(TileBuildArgs a, const __grid_constant__ CUtensorMap tmap, int use_tmap) {
+    __shared__ __align__(128) uint32_t s_raw[8][192];   // [row][interleaved RGB of 256 pixels]
     __shared__ __align__(8) unsigned long long s_bar;   // mbarrier of the bulk copies
     __shared__ uint2 s_tab[3][256];       // plane membership (plane_bits) of every value of a channel
     __shared__ uint32_t s_E[3][8][32];  // [channel][value word g][tile]: bit b <-> q = 32 g + b
@@ -197,7 +203,18 @@ __global__ void __launch_bounds__(256) tile_planes_kernel(TileBuildArgs a) {
     const uint32_t rows = min(8u, ha - y_base);
     const bool bulk = (pitch & 15) == 0 && (reinterpret_cast<uintptr_t>(add) & 15) == 0 && (row_bytes & 15) == 0;
     const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar);
-    if (bulk) {
+    if (use_tmap) {
+        if (tid == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(1));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(8u * 768u) : "memory");   // the whole box, zero fill included
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&s_raw[0][0]);
+            asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
+                         "l"(&tmap), "r"((int)(xw * 192u)), "r"((int)y_base), "r"((int)pair), "r"(bar)
+                         : "memory");
+        }
+    } else if (bulk) {
         if (tid == 0) {
             asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(1));
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -240,7 +257,7 @@ __global__ void __launch_bounds__(256) tile_planes_kernel(TileBuildArgs a) {
         s_tab[c][tid] = make_uint2(lo, hi);
     }
     __syncthreads();   // tables, s_E, the staged strip of the non-bulk paths -- and the mbarrier's initialisation
-    if (bulk) {        // rows and columns beyond the image keep whatever shared memory held: their pixels are masked (ok0 / ok1)
+    if (use_tmap || bulk) {   // rows and columns beyond the image: zero (tensor map) or whatever shared memory held (bulk rows); masked either way (ok0 / ok1)
         uint32_t done;
         do {
             asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
