@@ -99,7 +99,10 @@ extern "C" int32_t stepth_cuda_ctx_create(int32_t device, stepth_ctx **ctx_out) 
         unsigned cpus = std::thread::hardware_concurrency();
         cpu_set_t set;
         if (sched_getaffinity(0, sizeof set, &set) == 0 && CPU_COUNT(&set) > 0) cpus = (unsigned)CPU_COUNT(&set);
-        ctx->stage_threads = (int)std::max(2u, std::min(16u, cpus / 2));
+        // a launcher that runs one process per GPU says so (torchrun: LOCAL_WORLD_SIZE): the processes share the CPUs
+        unsigned procs = 1;
+        if (const char *ev = getenv("LOCAL_WORLD_SIZE")) procs = (unsigned)std::max(1, atoi(ev));
+        ctx->stage_threads = (int)std::max(2u, std::min(16u, cpus / (2 * procs)));
     }
     if (const char *ev = getenv("STEPTH_STAGE_THREADS")) ctx->stage_threads = std::max(0, std::min(64, atoi(ev)));
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
