@@ -156,15 +156,14 @@ public:
         p.precision[0] = precision[0]; p.precision[1] = precision[1]; p.precision[2] = precision[2];
         p.max_rings = max_rings;
         p.flags = flags & ~(uint32_t)(STEPTH_FLAG_FOREGROUND | STEPTH_FLAG_APPLY);
-        std::vector<stepth_block> own;
-        if (!blocks) {
-            const uint32_t max_splits = (uint32_t)std::ceil(std::log2((float)((size_t)w_ * h_)));  // :101-103
-            size_t n = stepth_host_discretise_v0(image_.data(), 4, w_, h_, precision, MIN_SPLITS, max_splits, nullptr, 0);
-            own.resize(n);
-            stepth_host_discretise_v0(image_.data(), 4, w_, h_, precision, MIN_SPLITS, max_splits, own.data(), n);
-            blocks = &own;
-        }
         std::vector<uint8_t> depth((size_t)w_ * h_);
+        if (!blocks) {   // the stand-in discretiser runs on the device in the same call; its block list never visits the host
+            const uint32_t max_splits = (uint32_t)std::ceil(std::log2((float)((size_t)w_ * h_)));  // :101-103
+            ctx_->check(stepth_cuda_depth_from_additional(ctx_->get(), image_.data(), w_, h_, add_rgb, wa, ha, &p, MIN_SPLITS, max_splits,
+                                                          depth.data(), nullptr, nullptr, nullptr, nullptr));
+            load_depth(std::move(depth), w_, h_);  // :135
+            return;
+        }
         ctx_->check(stepth_cuda_depth_from_blocks(ctx_->get(), add_rgb, wa, ha, blocks->data(), blocks->size(), w_, h_, &p,
                                                   depth.data(), nullptr, nullptr, nullptr, nullptr, nullptr));
         load_depth(std::move(depth), w_, h_);  // :135
