@@ -33,9 +33,6 @@ namespace stepth {
 #define STEPTH_OT_WARPS 2   // measured (16 pairs 1080p, search stage): 2 warps / 48 registers 2.13 ms, 4 / 48 2.15, 4 / 64 2.21, 8 / 48 2.45
 #endif
 constexpr int OT_WARPS = STEPTH_OT_WARPS;   // warps (origin tiles, or half tiles) per CTA, side by side
-#ifndef STEPTH_OT_RPP
-#define STEPTH_OT_RPP 1   // coarse rings per pass once one batch holds every open query of the warp
-#endif
 constexpr int OT_TASKS = 256;    // task slots of a warp
 constexpr int OT_MAX_S1 = 16;    // rings <= 15 have sides of at most 31 tiles: 32-bit flags
 
@@ -147,19 +144,15 @@ __global__ void __launch_bounds__(OT_WARPS * 32, STEPTH_OT_MINB) search_otile_ke
     const int S_end = a.S1 < Smax + 1 ? a.S1 : Smax + 1;     // rings [0, S_end) are walked here; the host keeps S1 in [2, OT_MAX_S1]
     const int xmax = v.ntx - 1, ymax = v.nty - 1;
     uint32_t mx = 0;                                         // largest distance this lane published
-    int S = 0;
 #pragma unroll 1
-    for (;;) {
-        // pass S: settles what the rings below S finished, packs the rest, walks rings [S, S2) (when S < S_end).  Once a single
-        // batch holds every open query the bookkeeping of a pass costs more than the windows of a ring: the pass then takes
-        // STEPTH_OT_RPP rings at once (tiles of the later ones that a match in the earlier ones puts out of reach are dropped
-        // when their task comes up: fine_test looks at the best key again)
+    for (int S = 0; S <= S_end; ++S) {
+        // pass S: settles what ring S - 1 finished, packs the rest, walks ring S (when S < S_end)
         const bool walk = S < S_end;
-        int S2 = S + 1;
-        if (walk && S >= 2 && n <= 32) S2 = min(S + STEPTH_OT_RPP, S_end);
         // the coarse square has left the tile grid on all four sides (nothing further out exists), or every ring below
         // max_rings has been walked: whatever the entries hold is final
         const bool all_final = (T0x - S < 0 && T0x + S > xmax && T0y - S < 0 && T0y + S > ymax) || (!walk && a.S1 > Smax);
+        const int rlo = T0x - S < 0 ? 0 : T0x - S, rhi = T0x + S > xmax ? xmax : T0x + S;                  // row sides (S >= 2)
+        const int clo = T0y - S + 1 < 0 ? 0 : T0y - S + 1, chi = T0y + S - 1 > ymax ? ymax : T0y + S - 1;  // column sides
         int n_new = 0;
 #pragma unroll 1
         for (int b0 = 0; b0 < n; b0 += 32) {
@@ -191,61 +184,56 @@ __global__ void __launch_bounds__(OT_WARPS * 32, STEPTH_OT_MINB) search_otile_ke
             }
             n_new += __popc(bal);
             if (!walk) continue;   // warp-uniform
-#pragma unroll 1
-            for (int R = S; R < S2; ++R) {   // warp-uniform
-                uint32_t f0 = 0, f1 = 0, f2 = 0, f3 = 0;   // flagged tiles of rows T0y+R, T0y-R (from r_lo), columns T0x+R, T0x-R (from c_lo)
-                int r_lo = T0x - R < 0 ? 0 : T0x - R, c_lo = T0y - R + 1 < 0 ? 0 : T0y - R + 1;
-                if (keep) {
-                    if (R == 0) {
-                        // three row windows give the nine flags of coarse rings 0 and 1 (search_hier.cuh: Block3)
-                        const Block3 b = block3_flags(v, q, T0x, T0y);
-                        f2 = block3_mid(b, T0x);   // the origin's own tile: "column T0x + 0, tile T0y"
-                        c_lo = T0y;
-                        const int sh = T0x - b.rlo;   // 0 or 1: bit of tile T0x - 1 + i in a row's flags is i - 1 + sh
-                        const uint32_t fa = sh ? b.fa : b.fa << 1, fc = sh ? b.fc : b.fc << 1;   // bit i <-> tile T0x - 1 + i
-                        ws->fl[pos] = (uint8_t)((fa & 7u) | (fc & 7u) << 3 | block3_mid(b, T0x + 1) << 6 | block3_mid(b, T0x - 1) << 7);
-                    } else if (R == 1) {
-                        r_lo = T0x - 1;   // may be -1: bit 0 is clear then
-                        c_lo = T0y;
-                        f1 = fl & 7u;
-                        f0 = (fl >> 3) & 7u;
-                        f2 = (fl >> 6) & 1u;
-                        f3 = (fl >> 7) & 1u;
-                    } else {
-                        const int rhi = T0x + R > xmax ? xmax : T0x + R, chi = T0y + R - 1 > ymax ? ymax : T0y + R - 1;
-                        f0 = side_flags32(v.crp, v.nxw, T0y + R, v.nty, r_lo, rhi, q);
-                        f1 = side_flags32(v.crp, v.nxw, T0y - R, v.nty, r_lo, rhi, q);
-                        f2 = side_flags32(v.ccp, v.nyw, T0x + R, v.ntx, c_lo, chi, q);
-                        f3 = side_flags32(v.ccp, v.nyw, T0x - R, v.ntx, c_lo, chi, q);
-                    }
-                    if (R > 0 && (f0 | f1 | f2 | f3)) {
-                        // with a match in hand (or at the last rings) most flagged tiles are out of reach and are not listed
-                        const int limit = min(D - 1, (int)(best >> 12));
-                        if (limit < 8 * R + 7) prune_sides(q, R, limit, r_lo, c_lo, f0, f1, f2, f3);
-                    }
+            uint32_t f0 = 0, f1 = 0, f2 = 0, f3 = 0;   // flagged tiles of rows T0y+S, T0y-S (from rlo), columns T0x+S, T0x-S (from clo)
+            int r_lo = rlo, c_lo = clo;
+            if (keep) {
+                if (S == 0) {
+                    // three row windows give the nine flags of coarse rings 0 and 1 (search_hier.cuh: Block3)
+                    const Block3 b = block3_flags(v, q, T0x, T0y);
+                    f2 = block3_mid(b, T0x);   // the origin's own tile: "column T0x + 0, tile T0y"
+                    c_lo = T0y;
+                    const int sh = T0x - b.rlo;   // 0 or 1: bit of tile T0x - 1 + i in a row's flags is i - 1 + sh
+                    const uint32_t fa = sh ? b.fa : b.fa << 1, fc = sh ? b.fc : b.fc << 1;   // bit i <-> tile T0x - 1 + i
+                    ws->fl[pos] = (uint8_t)((fa & 7u) | (fc & 7u) << 3 | block3_mid(b, T0x + 1) << 6 | block3_mid(b, T0x - 1) << 7);
+                } else if (S == 1) {
+                    r_lo = T0x - 1;   // may be -1: bit 0 is clear then
+                    c_lo = T0y;
+                    f1 = fl & 7u;
+                    f0 = (fl >> 3) & 7u;
+                    f2 = (fl >> 6) & 1u;
+                    f3 = (fl >> 7) & 1u;
+                } else {
+                    f0 = side_flags32(v.crp, v.nxw, T0y + S, v.nty, rlo, rhi, q);
+                    f1 = side_flags32(v.crp, v.nxw, T0y - S, v.nty, rlo, rhi, q);
+                    f2 = side_flags32(v.ccp, v.nyw, T0x + S, v.ntx, clo, chi, q);
+                    f3 = side_flags32(v.ccp, v.nyw, T0x - S, v.ntx, clo, chi, q);
                 }
-                // list the tiles; lanes whose tasks do not fit keep their flags and list them after the warp has tested a full list
-                for (;;) {
-                    const uint32_t cnt = __popc(f0) + __popc(f1) + __popc(f2) + __popc(f3);
-                    if (cnt) {
-                        uint32_t slot = atomicAdd(&ws->n_task, cnt);
-                        const uint32_t code = (uint32_t)pos | 16u << 8 | 16u << 13;
-                        f0 = ot_emit_side(f0, code + ((uint32_t)(r_lo - T0x) << 8) + ((uint32_t)R << 13), 8, slot, ws);
-                        f1 = ot_emit_side(f1, code + ((uint32_t)(r_lo - T0x) << 8) - ((uint32_t)R << 13), 8, slot, ws);
-                        f2 = ot_emit_side(f2, code + ((uint32_t)R << 8) + ((uint32_t)(c_lo - T0y) << 13), 13, slot, ws);
-                        f3 = ot_emit_side(f3, code - ((uint32_t)R << 8) + ((uint32_t)(c_lo - T0y) << 13), 13, slot, ws);
-                    }
-                    __syncwarp();
-                    const bool more = __any_sync(0xffffffffu, (f0 | f1 | f2 | f3) != 0u);
-                    if (more || ws->n_task > (uint32_t)(OT_TASKS - 96)) ot_run_tasks(ws, v, T0x, T0y, D, s_le, s_ge, lane);
-                    if (!more) break;
+                if (S > 0 && (f0 | f1 | f2 | f3)) {
+                    // with a match in hand (or at the last rings) most flagged tiles are out of reach and are not listed
+                    const int limit = min(D - 1, (int)(best >> 12));
+                    if (limit < 8 * S + 7) prune_sides(q, S, limit, r_lo, c_lo, f0, f1, f2, f3);
                 }
+            }
+            // list the tiles; lanes whose tasks do not fit keep their flags and list them after the warp has tested a full list
+            for (;;) {
+                const uint32_t cnt = __popc(f0) + __popc(f1) + __popc(f2) + __popc(f3);
+                if (cnt) {
+                    uint32_t slot = atomicAdd(&ws->n_task, cnt);
+                    const uint32_t code = (uint32_t)pos | 16u << 8 | 16u << 13;
+                    f0 = ot_emit_side(f0, code + ((uint32_t)(r_lo - T0x) << 8) + ((uint32_t)S << 13), 8, slot, ws);
+                    f1 = ot_emit_side(f1, code + ((uint32_t)(r_lo - T0x) << 8) - ((uint32_t)S << 13), 8, slot, ws);
+                    f2 = ot_emit_side(f2, code + ((uint32_t)S << 8) + ((uint32_t)(c_lo - T0y) << 13), 13, slot, ws);
+                    f3 = ot_emit_side(f3, code - ((uint32_t)S << 8) + ((uint32_t)(c_lo - T0y) << 13), 13, slot, ws);
+                }
+                __syncwarp();
+                const bool more = __any_sync(0xffffffffu, (f0 | f1 | f2 | f3) != 0u);
+                if (more || ws->n_task > (uint32_t)(OT_TASKS - 96)) ot_run_tasks(ws, v, T0x, T0y, D, s_le, s_ge, lane);
+                if (!more) break;
             }
         }
         n = n_new;
-        if (n == 0 || !walk) break;
-        ot_run_tasks(ws, v, T0x, T0y, D, s_le, s_ge, lane);
-        S = S2;
+        if (n == 0) break;
+        if (walk) ot_run_tasks(ws, v, T0x, T0y, D, s_le, s_ge, lane);
     }
 
     // ---- what is still open goes to the far kernel ------------------------------------------------------------------------------
