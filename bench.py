@@ -509,6 +509,9 @@ def int_roofline(env, wl, mains, adds, n_first, search_launch_ms, alg_bytes):
         "bound": "int-alu", "unit": "Tiop/s", "ops_per_launch": round(ops),
         "probes_per_query_min": round(min(per_q), 2), "probes_per_query_mean": round(sum(per_q) / len(per_q), 2),
         "probes_per_query_max": round(max(per_q), 2), "pairs_counted": n_first,
+        # early exit makes the nominal W*H*D much larger than what the reference order really visits
+        "reference_probes_per_s": round(total / (search_launch_ms * 1e-3), 1),
+        "nominal_over_effective": round(n_first * wl["w"] * wl["h"] * (2.0 * wl["d"] - 1) ** 2 / max(total, 1.0), 2),
         "achieved": round(ops / (search_launch_ms * 1e-3) / 1e12, 3), "peak": round(p_mixed / 1e12, 3),
         "frac": round(ops / (search_launch_ms * 1e-3) / p_mixed, 4), "peak_logic_only": round(p_logic / 1e12, 3),
         "peak_source": "measured (stepth_cuda_int_peak: LOP3+IMAD.IADD on both integer pipes; logic_only = LOP3+SHF, alu pipe)",

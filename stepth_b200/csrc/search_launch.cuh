@@ -109,7 +109,8 @@ inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const Search
             int nit = 8;
             while (nit > 1 && tiles * (uint64_t)(8 / nit) < want) nit >>= 1;
             if (ctx->otile_nit == 8 || ctx->otile_nit == 4 || ctx->otile_nit == 2 || ctx->otile_nit == 1) nit = ctx->otile_nit;
-            const dim3 grid((n_tx + OT_WARPS - 1) / OT_WARPS, (uint32_t)n_ty * (uint32_t)(8 / nit), n_pairs);
+            constexpr uint32_t per_cta = STEPTH_OT_SPAN > 0 ? STEPTH_OT_SPAN : OT_WARPS;   // origin tiles of a tile row per CTA
+            const dim3 grid((n_tx + per_cta - 1) / per_cta, (uint32_t)n_ty * (uint32_t)(8 / nit), n_pairs);
             if (nit == 8) search_otile_kernel<8><<<grid, OT_WARPS * 32, 0, st>>>(h, ty_first);
             else if (nit == 4) search_otile_kernel<4><<<grid, OT_WARPS * 32, 0, st>>>(h, ty_first);
             else if (nit == 2) search_otile_kernel<2><<<grid, OT_WARPS * 32, 0, st>>>(h, ty_first);

@@ -30,7 +30,7 @@ namespace stepth {
 #define STEPTH_OT_MINB 18   // resident CTAs per SM the register allocation must allow: 18 x 64 threads -> 56 registers (64: 2.16 ms, 56: 2.10, 48: 2.12, 40: 2.16)
 #endif
 #ifndef STEPTH_OT_WARPS
-#define STEPTH_OT_WARPS 2   // measured (16 pairs 1080p, search stage): 2 warps / 48 registers 2.13 ms, 4 / 48 2.15, 4 / 64 2.21, 8 / 48 2.45
+#define STEPTH_OT_WARPS 2   // warps per CTA; measured (16 pairs 1080p, search stage): 2 warps / 48 registers 2.13 ms, 4 / 48 2.15, 4 / 64 2.21, 8 / 48 2.45
 #endif
 constexpr int OT_WARPS = STEPTH_OT_WARPS;   // warps (origin tiles, or half tiles) per CTA, side by side
 constexpr int OT_TASKS = 256;    // task slots of a warp
@@ -77,22 +77,13 @@ __device__ __forceinline__ uint32_t ot_emit_side(uint32_t m, uint32_t code, int 
     return m;
 }
 
+// One origin tile (NIT = 8) or NIT of its eight origin rows, start to finish, by one warp.
 // NIT = origin rows per warp: 8 = a whole origin tile (256 queries); 4, 2, 1 = a half, a quarter, an eighth (small launches)
 template <int NIT>
-__global__ void __launch_bounds__(OT_WARPS * 32, STEPTH_OT_MINB) search_otile_kernel(HierArgs a, int ty_first) {
-    constexpr int HALVES = 8 / NIT;
-    __shared__ unsigned long long s_le[DIAG_N], s_ge[DIAG_N];
-    __shared__ OtWarp s_w[OT_WARPS];
-    load_diag_tables(s_le, s_ge);  // ends with __syncthreads()
+__device__ __forceinline__ void ot_tile(const HierArgs &a, const uint32_t pair, const int T0x, const int T0y, const int it0, OtWarp *ws,
+                                        const unsigned long long *s_le, const unsigned long long *s_ge, const uint32_t lane) {
     const SearchArgs &s = a.s;
-    const uint32_t pair = blockIdx.z;
-    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const int T0x = (int)blockIdx.x * OT_WARPS + (int)warp;
-    const int T0y = ty_first + (int)(blockIdx.y / HALVES);
-    const int it0 = (int)(blockIdx.y % HALVES) * NIT;
-    if (T0x > (int)((s.w >> 1) >> 3)) return;   // beyond the last origin tile column (warp-uniform; no barrier follows)
-    OtWarp *ws = &s_w[warp];
-    if (lane == 0) ws->n_task = 0;
+    if (T0x > (int)((s.w >> 1) >> 3)) return;   // beyond the last origin tile column (warp-uniform)
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t *main32 = reinterpret_cast<const uint32_t *>(s.main_rgba) + (size_t)pair * s.n_queries;
     uint8_t *d8 = s.d8 + (size_t)pair * s.n_queries;
@@ -251,6 +242,41 @@ __global__ void __launch_bounds__(OT_WARPS * 32, STEPTH_OT_MINB) search_otile_ke
     }
     const uint32_t m = __reduce_max_sync(0xffffffffu, mx);
     if (lane == 0 && m && m > *(volatile uint32_t *)(s.max_out + pair)) atomicMax(s.max_out + pair, m);
+}
+
+#ifndef STEPTH_OT_SPAN
+#define STEPTH_OT_SPAN 0   // > 0: a CTA owns this many consecutive origin tiles of a tile row and its warps pull them one by one
+#endif
+
+template <int NIT>
+__global__ void __launch_bounds__(OT_WARPS * 32, STEPTH_OT_MINB) search_otile_kernel(HierArgs a, int ty_first) {
+    constexpr int HALVES = 8 / NIT;
+    __shared__ unsigned long long s_le[DIAG_N], s_ge[DIAG_N];
+    __shared__ OtWarp s_w[OT_WARPS];
+#if STEPTH_OT_SPAN > 0
+    __shared__ int s_next;
+    if (threadIdx.x == 0) s_next = 0;
+#endif
+    load_diag_tables(s_le, s_ge);  // ends with __syncthreads()
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const int T0y = ty_first + (int)(blockIdx.y / HALVES);
+    const int it0 = (int)(blockIdx.y % HALVES) * NIT;
+    OtWarp *ws = &s_w[warp];
+    if (lane == 0) ws->n_task = 0;
+#if STEPTH_OT_SPAN > 0
+    // neighbouring tiles read the same occupancy cells and tile records: the warps of a CTA stay next to each other (L1) and
+    // none of them idles while a slower one finishes its tile, as it would with one tile per warp in a wide CTA
+    for (;;) {
+        int t = 0;
+        if (lane == 0) t = atomicAdd(&s_next, 1);
+        t = __shfl_sync(0xffffffffu, t, 0);
+        if (t >= STEPTH_OT_SPAN) break;
+        ot_tile<NIT>(a, blockIdx.z, (int)blockIdx.x * STEPTH_OT_SPAN + t, T0y, it0, ws, s_le, s_ge, lane);
+        __syncwarp();
+    }
+#else
+    ot_tile<NIT>(a, blockIdx.z, (int)blockIdx.x * OT_WARPS + (int)warp, T0y, it0, ws, s_le, s_ge, lane);
+#endif
 }
 
 #endif  // __CUDACC__
