@@ -42,7 +42,7 @@ if ROOT not in sys.path:
 
 PRECISION = [36, 36, 36]           # u8::MAX / 7 (Readme.md:15)
 METRIC = "Mpx*disparities/sec"
-SUB = int(os.environ.get("STEPTH_BENCH_SUB", "16"))   # most pairs per launch sequence (bounds the scratch in HBM)
+SUB = int(os.environ.get("STEPTH_BENCH_SUB", "32"))   # most pairs per launch sequence (bounds the scratch in HBM; 16 -> 32: 64 x 4K 36.6 -> 36.2 ms)
 
 # name -> shape of the workload.  pairs: per GPU when scaling == "weak", in total when "strong"
 WORKLOADS = {
@@ -480,8 +480,11 @@ def build_roofline(name, kind, wl, alg_bytes, pairs_per_launch, search_launch_ms
     hbm, which = peaks()
     achieved = alg_bytes / (search_launch_ms * 1e-3) / 1e9
     prof = ncu_profile(name, kind) or {}
+    traffic = prof.get("traffic")
+    if traffic is not None and prof.get("pairs_per_launch"):   # the capture's launch sequence may hold another number of pairs
+        traffic = int(traffic * pairs_per_launch / prof["pairs_per_launch"])
     r = {"bound": "hbm", "achieved": round(achieved, 2), "peak": hbm, "unit": "GB/s", "frac": round(achieved / hbm, 5),
-         "traffic": prof.get("traffic"), "peak_source": which, "kernel": kernel_desc,
+         "traffic": traffic, "peak_source": which, "kernel": kernel_desc,
          "alg_bytes_per_launch": alg_bytes, "pairs_per_launch": pairs_per_launch, "launch_ms": round(search_launch_ms, 4),
          "share_of_step": round(share, 4),
          "note": "the stage is instruction-issue / latency bound, not HBM bound (DESIGN.md section 5): `issue` is the ceiling "

@@ -44,6 +44,7 @@ extern "C" {
 #define STEPTH_ERR_NO_CONVERGENCE 6   /* k-means did not converge (reference: unbounded recursion)             */
 #define STEPTH_ERR_OUT_OF_BOUNDS 7    /* -> panic (ImageBuffer::get_pixel out of bounds)  mask_image.rs:106        */
 #define STEPTH_ERR_CUDA 100           /* CUDA runtime failure; text in stepth_cuda_last_error()                */
+#define STEPTH_ERR_CODEC 102          /* nvJPEG missing or failing (decode / encode entry points only)          */
 
 /* ---- flags (stepth_params.flags) ------------------------------------------------------------------------ */
 #define STEPTH_RESAMPLE_OFF 0u        /* skip depth_image.rs:133 (debug / raw distance maps)                   */
@@ -166,6 +167,17 @@ int32_t stepth_cuda_depth_from_additional(stepth_ctx *ctx, const uint8_t *main_r
                                           const uint8_t *add_rgb, uint32_t wa, uint32_t ha, const stepth_params *params,
                                           uint32_t min_splits, uint32_t max_splits, uint8_t *depth_out, uint8_t *rgba_out,
                                           uint8_t *mask_out, uint8_t *from_to_out, size_t *n_blocks_out);
+
+/* ---- decode / encode on the device (csrc/codec.cuh) -------------------------------------------------- */
+/* image::open (src/depth_image.rs:14,66,81) / save (src/mask_image.rs:197-199) for JPEG by nvJPEG, resolved at run time.  NOT
+ * on the parity path: decoded pixels differ from jpeg-decoder 0.1.22's by a level or two, as between any two JPEG decoders.
+ * decode: *w_out, *h_out always; rgb_out (w*h*3, interleaved RGB8) when not NULL.  A stream nvJPEG cannot parse answers
+ * STEPTH_ERR_INVALID_ARG with the reference's "Failed to open image".  encode: channels 1 (Luma8), 3 (RGB8) or 4 (RGBA8, alpha
+ * dropped); jpeg_out NULL sizes the buffer.  Status 102 = nvJPEG absent or failing. */
+int32_t stepth_cuda_decode_jpeg(stepth_ctx *ctx, const uint8_t *jpeg, size_t n_bytes, uint32_t *w_out, uint32_t *h_out,
+                                uint8_t *rgb_out, size_t cap);
+int32_t stepth_cuda_encode_jpeg(stepth_ctx *ctx, const uint8_t *pixels, uint32_t w, uint32_t h, uint32_t channels,
+                                int32_t quality, uint8_t *jpeg_out, size_t cap, size_t *n_out);
 
 /* ---- device-resident stage API (device pointers; work is enqueued on `stream`, a cudaStream_t) ------------ */
 /* Used by the batch / row-band orchestration (one process per GPU) and by the device-resident benchmark.

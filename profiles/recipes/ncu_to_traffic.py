@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""ncu_to_traffic.py REPORT.ncu-rep KEY [SMS] -> one entry of profiles/traffic.json (printed as JSON)
+"""ncu_to_traffic.py REPORT.ncu-rep KEY [PAIRS [SMS]] -> one entry of profiles/traffic.json (printed as JSON)
 
 From one `ncu --set full --clock-control none` capture of ONE launch sequence of the search stage (tile_planes,
 coarse_transpose, search_near, search_far):
@@ -11,7 +11,8 @@ bench.py copies the entry into roofline.traffic / roofline.issue."""
 import csv, io, json, subprocess, sys
 
 rep, key = sys.argv[1], sys.argv[2]
-sms = int(sys.argv[3]) if len(sys.argv) > 3 else 148
+pairs = int(sys.argv[3]) if len(sys.argv) > 3 else 16   # pairs in the captured launch sequence
+sms = int(sys.argv[4]) if len(sys.argv) > 4 else 148
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hdr, units = rows[0], rows[1]
@@ -48,6 +49,7 @@ if cyc is None:
     cyc = dur * (hz or 1.965e9)
 entry = {
     "traffic": int(traffic),
+    "pairs_per_launch": pairs,
     "traffic_per_kernel": {s: int(val(rr, "dram__bytes_read.sum", 0) + val(rr, "dram__bytes_write.sum", 0)) for s, _, rr in seq},
     "duration_us_per_kernel": {s: round(val(rr, "gpu__time_duration.sum", 0) * 1e6, 1) for s, _, rr in seq},
     "issue": {

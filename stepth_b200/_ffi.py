@@ -89,6 +89,8 @@ SIGNATURES = {
     "stepth_cuda_dev_discretise_v0": (_i32, [_vp, _vp, _u8p, _u32, _u32, _u32, _u8p, _u32, _u32, _vp, _sz, _u32p]),
     "stepth_cuda_depth_from_additional": (_i32, [_vp, _u8p, _u32, _u32, _u8p, _u32, _u32, _PP, _u32, _u32, _u8p, _u8p, _u8p, _u8p,
                                                  C.POINTER(_sz)]),
+    "stepth_cuda_decode_jpeg": (_i32, [_vp, _u8p, _sz, _u32p, _u32p, _u8p, _sz]),
+    "stepth_cuda_encode_jpeg": (_i32, [_vp, _u8p, _u32, _u32, _u32, _i32, _u8p, _sz, C.POINTER(_sz)]),
     "stepth_cuda_dev_search_dense": (_i32, [_vp, _vp, _SP, _PP, _u8p, _u8p, _u8p, _u32p]),
     "stepth_cuda_dev_search_blocks": (_i32, [_vp, _vp, _PP, _u8p, _u32, _u32, _vp, _sz, _u8p, _u32p]),
     "stepth_cuda_dev_paint_blocks": (_i32, [_vp, _vp, _vp, _u8p, _sz, _u32, _u32, _u8p]),

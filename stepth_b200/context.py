@@ -181,6 +181,30 @@ class Context:
             out["rgba"] = rgba
         return out
 
+    # ---- decode / encode on the device (csrc/codec.cuh: nvJPEG; NOT on the parity path) ---------------------------------------
+    def decode_jpeg(self, data: bytes) -> np.ndarray:
+        """JPEG bytes -> RGB8 [h, w, 3], decoded on the GPU.  Differs from the reference's jpeg-decoder by a level or two, as any two
+        JPEG decoders do; raises StepthIOError("Failed to open image") for a stream that is not a JPEG."""
+        buf = np.frombuffer(data, dtype=np.uint8)
+        w, h = C.c_uint32(0), C.c_uint32(0)
+        with self._lock:
+            self.check(self._lib.stepth_cuda_decode_jpeg(self._h, _ffi.ptr(buf), buf.size, C.byref(w), C.byref(h), None, 0))
+            out = np.empty((h.value, w.value, 3), np.uint8)
+            self.check(self._lib.stepth_cuda_decode_jpeg(self._h, _ffi.ptr(buf), buf.size, C.byref(w), C.byref(h), _ffi.ptr(out), out.size))
+        return out
+
+    def encode_jpeg(self, pixels, quality: int = 75) -> bytes:
+        """Luma8 [h, w], RGB8 [h, w, 3] or RGBA8 [h, w, 4] (alpha dropped) -> JPEG bytes, encoded on the GPU"""
+        px = np.ascontiguousarray(pixels, dtype=np.uint8)
+        ch = 1 if px.ndim == 2 else int(px.shape[2])
+        h, w = px.shape[:2]
+        n = C.c_size_t(0)
+        with self._lock:
+            self.check(self._lib.stepth_cuda_encode_jpeg(self._h, _ffi.ptr(px), w, h, ch, int(quality), None, 0, C.byref(n)))
+            out = np.empty(n.value, np.uint8)
+            self.check(self._lib.stepth_cuda_encode_jpeg(self._h, _ffi.ptr(px), w, h, ch, int(quality), _ffi.ptr(out), out.size, C.byref(n)))
+        return out[: n.value].tobytes()
+
     def depth_from_blocks(self, add_rgb, blocks, w, h, precision, max_rings=255, flags=_ffi.RESAMPLE_U8,
                           rgba_in=None, want_raw=False):
         """depth_image.rs:110-134 from a DiscretePixel list (the discretiser stays on the host)."""

@@ -14,6 +14,7 @@
 #include "intpeak.cuh"
 #include "edit.cuh"
 #include "disc.cuh"
+#include "codec.cuh"
 
 #include <sched.h>
 
@@ -128,12 +129,13 @@ extern "C" void stepth_cuda_ctx_destroy(stepth_ctx *ctx) {
     stepth_ctx::Buf *bufs[] = {&ctx->main_rgba, &ctx->add_rgb, &ctx->d8,   &ctx->depth, &ctx->mask, &ctx->rgba_out,
                                &ctx->blocks,    &ctx->plane,   &ctx->small, &ctx->u16a,  &ctx->u16b, &ctx->u16o,
                                &ctx->work,      &ctx->planes, &ctx->worklist, &ctx->planes2, &ctx->worklist2, &ctx->work2,
-                               &ctx->main_rgb, &ctx->disc_counts};
+                               &ctx->main_rgb, &ctx->disc_counts, &ctx->codec_a, &ctx->codec_b};
     for (auto *b : bufs)
         if (b->p) cudaFree(b->p);
     for (auto &kv : ctx->taps)
         if (kv.second.dev) cudaFree(kv.second.dev);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
+    codec_destroy(ctx);
     ctx->stager.destroy();
     for (cudaEvent_t e : ctx->events) cudaEventDestroy(e);
     if (ctx->copy_in) cudaStreamDestroy(ctx->copy_in);
@@ -1211,5 +1213,84 @@ extern "C" int32_t stepth_cuda_depth_from_additional(stepth_ctx *ctx, const uint
                                  nullptr, &main_rgba, &rgba_out, mask_out ? &mask_out : nullptr, from_to_out, nullptr);
     ctx->blocks_on_device = 0;
     return rc;
+}
+
+// ---- decode / encode on the device (codec.cuh; nvJPEG) -----------------------------------------------------------------------
+extern "C" int32_t stepth_cuda_decode_jpeg(stepth_ctx *ctx, const uint8_t *jpeg, size_t n_bytes, uint32_t *w_out, uint32_t *h_out,
+                                           uint8_t *rgb_out, size_t cap) {
+    if (!ctx) return STEPTH_ERR_INVALID_ARG;
+    if (!jpeg || n_bytes < 4 || !w_out || !h_out) return set_err(ctx, STEPTH_ERR_INVALID_ARG, "decode_jpeg: null or invalid argument");
+    STEPTH_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    TRY_RC(codec_ensure(ctx));
+    NvjpegApi &nj = nvjpeg_api();
+    int ncomp = 0, ws[NVJPEG_MAX_COMPONENT] = {0, 0, 0, 0}, hs[NVJPEG_MAX_COMPONENT] = {0, 0, 0, 0};
+    nvjpegChromaSubsampling_t css;
+    if (nj.GetImageInfo((nvjpegHandle_t)ctx->nvj_handle, jpeg, n_bytes, &ncomp, &css, ws, hs) != NVJPEG_STATUS_SUCCESS || ws[0] <= 0 || hs[0] <= 0)
+        return set_err(ctx, STEPTH_ERR_INVALID_ARG, "Failed to open image");   // the reference's message (src/depth_image.rs:16)
+    *w_out = (uint32_t)ws[0];
+    *h_out = (uint32_t)hs[0];
+    if (!rgb_out) return STEPTH_OK;
+    const size_t bytes = (size_t)ws[0] * hs[0] * 3;
+    if (cap < bytes) return set_err(ctx, STEPTH_ERR_SIZE_MISMATCH, "decode_jpeg: the output buffer holds %zu of %zu bytes", cap, bytes);
+    TRY_RC(ensure(ctx, ctx->codec_a, bytes));
+    nvjpegImage_t img;
+    memset(&img, 0, sizeof img);
+    img.channel[0] = (unsigned char *)ctx->codec_a.p;
+    img.pitch[0] = (size_t)ws[0] * 3;
+    STEPTH_NVJ_TRY(ctx, nj.Decode((nvjpegHandle_t)ctx->nvj_handle, (nvjpegJpegState_t)ctx->nvj_state, jpeg, n_bytes, NVJPEG_OUTPUT_RGBI, &img, ctx->stream));
+    STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(rgb_out, ctx->codec_a.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return STEPTH_OK;
+}
+
+extern "C" int32_t stepth_cuda_encode_jpeg(stepth_ctx *ctx, const uint8_t *pixels, uint32_t w, uint32_t h, uint32_t channels,
+                                           int32_t quality, uint8_t *jpeg_out, size_t cap, size_t *n_out) {
+    if (!ctx) return STEPTH_ERR_INVALID_ARG;
+    if (!pixels || !n_out || w == 0 || h == 0 || (channels != 1 && channels != 3 && channels != 4) || quality < 1 || quality > 100)
+        return set_err(ctx, STEPTH_ERR_INVALID_ARG, "encode_jpeg: null or invalid argument");
+    STEPTH_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    TRY_RC(codec_ensure(ctx));
+    NvjpegApi &nj = nvjpeg_api();
+    cudaStream_t st = ctx->stream;
+    const size_t px = (size_t)w * h;
+    TRY_RC(ensure(ctx, ctx->codec_a, px * channels));
+    STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(ctx->codec_a.p, pixels, px * channels, cudaMemcpyHostToDevice, st));
+    nvjpegHandle_t hd = (nvjpegHandle_t)ctx->nvj_handle;
+    nvjpegEncoderState_t es = (nvjpegEncoderState_t)ctx->nvj_enc_state;
+    nvjpegEncoderParams_t ep = (nvjpegEncoderParams_t)ctx->nvj_enc_params;
+    STEPTH_NVJ_TRY(ctx, nj.EncoderParamsSetQuality(ep, quality, st));
+    nvjpegImage_t img;
+    memset(&img, 0, sizeof img);
+    if (channels == 1) {   // Luma8 (DepthImage::depth().save): one luminance component
+        STEPTH_NVJ_TRY(ctx, nj.EncoderParamsSetSamplingFactors(ep, NVJPEG_CSS_GRAY, st));
+        img.channel[0] = (unsigned char *)ctx->codec_a.p;
+        img.pitch[0] = w;
+        STEPTH_NVJ_TRY(ctx, nj.EncodeYUV(hd, es, ep, &img, NVJPEG_CSS_GRAY, (int)w, (int)h, st));
+    } else {
+        STEPTH_NVJ_TRY(ctx, nj.EncoderParamsSetSamplingFactors(ep, NVJPEG_CSS_444, st));
+        const uint8_t *rgb = (const uint8_t *)ctx->codec_a.p;
+        if (channels == 4) {
+            TRY_RC(ensure(ctx, ctx->codec_b, px * 3));
+            rgba_to_rgb_kernel<<<(unsigned)std::min<size_t>((px + 255) / 256, (size_t)ctx->sm_count * 8), 256, 0, st>>>(
+                (const uint32_t *)ctx->codec_a.p, (uint8_t *)ctx->codec_b.p, px);
+            LAUNCH_CHECK(ctx);
+            rgb = (const uint8_t *)ctx->codec_b.p;
+        }
+        img.channel[0] = (unsigned char *)rgb;
+        img.pitch[0] = (size_t)w * 3;
+        STEPTH_NVJ_TRY(ctx, nj.EncodeImage(hd, es, ep, &img, NVJPEG_INPUT_RGBI, (int)w, (int)h, st));
+    }
+    size_t len = 0;
+    STEPTH_NVJ_TRY(ctx, nj.EncodeRetrieveBitstream(hd, es, nullptr, &len, st));
+    *n_out = len;
+    if (!jpeg_out) {   // sizing call: the stream stays in the encoder state until the next encode
+        STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(st));
+        return STEPTH_OK;
+    }
+    if (cap < len) return set_err(ctx, STEPTH_ERR_SIZE_MISMATCH, "encode_jpeg: the output buffer holds %zu of %zu bytes", cap, len);
+    STEPTH_NVJ_TRY(ctx, nj.EncodeRetrieveBitstream(hd, es, jpeg_out, &len, st));
+    STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    *n_out = len;
+    return STEPTH_OK;
 }
 #include "multi_api.cuh"

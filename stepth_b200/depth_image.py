@@ -22,7 +22,18 @@ MASK_TRUE = 255   # mask_image.rs:3
 MASK_FALSE = 0    # mask_image.rs:4
 
 
-def _open_image(path: str):
+def _open_image(path: str, ctx: Context | None = None):
+    """image::open (depth_image.rs:14).  STEPTH_GPU_DECODE=1: JPEG files are decoded on the GPU (csrc/codec.cuh, nvJPEG) -- faster, but
+    a level or two away from the host decoder's pixels, like any two JPEG decoders: off by default, the parity path decodes on the host."""
+    import os
+
+    if os.environ.get("STEPTH_GPU_DECODE") == "1" and path.lower().endswith((".jpg", ".jpeg")):
+        try:
+            with open(path, "rb") as f:
+                data = f.read()
+        except OSError:
+            raise StepthIOError("Failed to open image") from None
+        return (ctx or default_context()).decode_jpeg(data)
     from PIL import Image
 
     try:
@@ -68,7 +79,7 @@ class MaskImage:
 
     @classmethod
     def open(cls, image_path: str, ctx: Context | None = None) -> "MaskImage":  # mask_image.rs:13-19
-        return cls.from_image(_open_image(image_path), ctx)
+        return cls.from_image(_open_image(image_path, ctx), ctx)
 
     def width(self) -> int:
         return int(self.image.shape[1])
@@ -139,7 +150,7 @@ class DepthImage:
 
     @classmethod
     def open(cls, image_path: str, ctx: Context | None = None) -> "DepthImage":  # :13-21
-        return cls.from_image(_open_image(image_path), ctx)
+        return cls.from_image(_open_image(image_path, ctx), ctx)
 
     def _context(self) -> Context:
         if self._ctx is None:
@@ -176,11 +187,12 @@ class DepthImage:
         raise StepthIOError("Sizes don't match")
 
     def open_depth(self, depth_path: str) -> None:  # :65-74
-        self.load_depth(np.asarray(_open_image(depth_path).convert("L"), dtype=np.uint8))
+        im = _open_image(depth_path, self._ctx)
+        self.load_depth(np.ascontiguousarray(im[..., 0]) if isinstance(im, np.ndarray) else np.asarray(im.convert("L"), dtype=np.uint8))
 
     # ---- the hot path ----------------------------------------------------------------------------------------
     def open_depth_from_additional(self, add_path: str, precision, **kw) -> None:  # :76-89
-        self.load_depth_from_additional(_open_image(add_path), precision, **kw)
+        self.load_depth_from_additional(_open_image(add_path, self._ctx), precision, **kw)
 
     def load_depth_from_additional(self, add_image, precision, *, mode: str = "blocks", blocks=None,
                                    max_rings: int | None = None, flags: int = _ffi.RESAMPLE_U8) -> None:

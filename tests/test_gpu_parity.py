@@ -1010,3 +1010,59 @@ def test_depth_from_additional_equals_host_discretiser_plus_blocks(ctx, orc, ass
     # fewer than 8 blocks: par_chunks_mut(0) panics (depth_image.rs:111-112)
     with pytest.raises(sb.StepthPanic):
         ctx.depth_from_additional(np.full((1, 2, 4), 9, np.uint8), np.zeros((4, 4, 3), np.uint8), P36, 255, sb.RESAMPLE_U8)
+
+
+# ---- decode / encode on the device (csrc/codec.cuh; SURVEY 8(f) row 4: NOT on the parity path) --------------------------------
+@pytest.mark.gpu
+def test_jpeg_decode_and_encode_on_the_device(ctx, assets, tmp_path):
+    """nvJPEG against the host decoder (PIL / libjpeg): same size, pixels within a few levels (two JPEG decoders never agree bit for
+    bit -- which is why the parity path keeps decoding on the host); encode -> host decode round trip close to the source"""
+    import io
+
+    from PIL import Image
+
+    import stepth_b200 as sb
+
+    main = np.ascontiguousarray(assets["main"])                       # 400 x 600 x 3, the README image's decoded pixels
+    buf = io.BytesIO()
+    Image.fromarray(main, "RGB").save(buf, format="JPEG", quality=92, subsampling=0)
+    data = buf.getvalue()
+    host = np.asarray(Image.open(io.BytesIO(data)).convert("RGB"), dtype=np.uint8)
+    got = ctx.decode_jpeg(data)
+    assert got.shape == host.shape == main.shape
+    diff = np.abs(got.astype(np.int16) - host.astype(np.int16))
+    assert diff.max() <= 6 and diff.mean() < 0.6, (int(diff.max()), float(diff.mean()))
+    # 4:2:0 streams and grey streams decode too
+    buf = io.BytesIO()
+    Image.fromarray(main, "RGB").save(buf, format="JPEG", quality=85, subsampling=2)
+    g420 = ctx.decode_jpeg(buf.getvalue())
+    h420 = np.asarray(Image.open(io.BytesIO(buf.getvalue())).convert("RGB"), dtype=np.uint8)
+    assert g420.shape == main.shape and np.abs(g420.astype(np.int16) - h420.astype(np.int16)).mean() < 2.0
+    buf = io.BytesIO()
+    Image.fromarray(assets["depth"], "L").save(buf, format="JPEG", quality=90)
+    grey = ctx.decode_jpeg(buf.getvalue())
+    hgrey = np.asarray(Image.open(io.BytesIO(buf.getvalue())).convert("L"), dtype=np.uint8)
+    assert grey.shape == hgrey.shape + (3,) and np.abs(grey[..., 0].astype(np.int16) - hgrey.astype(np.int16)).max() <= 3
+    with pytest.raises(sb.StepthIOError, match="Failed to open image"):
+        ctx.decode_jpeg(b"this is not a jpeg stream at all")
+    # encode: RGB, RGBA (alpha dropped), Luma -> a stream the host decoder reads back close to the source
+    def psnr(a, b):
+        mse = np.mean((a.astype(np.float64) - b.astype(np.float64)) ** 2)
+        return 99.0 if mse == 0 else 10 * np.log10(255.0 ** 2 / mse)
+
+    for px, mode in ((main, "RGB"), (rgba_of(main), "RGB"), (np.ascontiguousarray(assets["depth"]), "L")):
+        stream = ctx.encode_jpeg(px, quality=90)
+        back = np.asarray(Image.open(io.BytesIO(stream)).convert(mode), dtype=np.uint8)
+        want = px[..., :3] if px.ndim == 3 else px
+        assert back.shape == want.shape and psnr(back, want) > 32.0, (mode, psnr(back, want))
+    # the public API takes the device decoder when asked to
+    path = tmp_path / "main.jpg"
+    path.write_bytes(data)
+    import os
+
+    os.environ["STEPTH_GPU_DECODE"] = "1"
+    try:
+        img = sb.DepthImage.open(str(path), ctx)
+    finally:
+        del os.environ["STEPTH_GPU_DECODE"]
+    assert img.image.shape == (400, 600, 4) and np.array_equal(img.image[..., :3], got)
