@@ -39,9 +39,9 @@ struct stepth_ctx {
                                        // main images are still on their way up while the planes of the additional ones are built)
     int trace = 0;  // STEPTH_TRACE=1: the batch entry point prints each chunk's copy-in / compute / copy-out end times to stderr
     int upload_full_rows = 0;  // host-buffer entry points upload whole rows of the additional image (STEPTH_UPLOAD_FULL_ROWS)
-    int near_tile = 2;     // dense mode's near stage (STEPTH_NEAR_TILE): 2 = one warp per origin tile (search_otile.cuh), 0 = the walking near kernel,
-                           // 1 = ring 0 + coarse rings 0..1 from TMA-staged tile records (search_tile.cuh; measured slower than the walk: 2.59 vs 2.26 ms
-                           // per 16 pairs 1080p)
+    int near_tile = 3;     // dense mode's near stage (STEPTH_NEAR_TILE): 2 = one warp per origin tile (search_otile.cuh), 0 = the walking near kernel,
+                           // 3 = by launch size (origin tiles except for mid-sized launches, search_launch.cuh), 1 = ring 0 + coarse rings 0..1 from
+                           // TMA-staged tile records (search_tile.cuh; measured slower than the walk: 2.59 vs 2.26 ms per 16 pairs 1080p)
     int near_rings_otile = 12;  // coarse rings the origin-tile near stage walks, 2..16 (STEPTH_OT_RINGS; 16 pairs 1080p: 6 -> 2.17 ms, 12 -> 2.13, 16 -> 2.13)
     int otile_nit = 0;         // origin-tile stage: origin rows per warp, 8 (a whole tile) / 4 / 2 / 1; 0 = by launch size (STEPTH_OT_NIT)
     int otile_warps_per_sm = 128;  // ... so that the launch has at least this many warps per SM (STEPTH_OT_WARPS_PER_SM)

@@ -82,7 +82,11 @@ inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const Search
     // dense mode: 2 (default) = one warp per origin tile (search_otile.cuh), 1 = rings 0..1 from TMA-staged tile records
     // (search_tile.cuh), 0 = the walking near kernel (also what block mode runs)
     const bool tile_stage = !a.blocks && ctx->near_tile == 1;
-    const bool otile_stage = !a.blocks && ctx->near_tile == 2;
+    // 3 (default): origin tiles, except for launches of 4K .. 28K origin tiles (one to three 1080p pairs), where the walking kernel's
+    // shorter per-CTA work leaves a shorter tail (one 1080p pair 0.221 vs 0.237 ms, three 0.531 vs 0.578; four 0.663 vs 0.660; one
+    // README pair 0.132 vs 0.127; two 4K pairs 1.236 vs 1.174: profiles/recipes/r2_run21.sh)
+    const uint64_t origin_tiles = (uint64_t)(((a.w >> 1) >> 3) + 1) * (uint64_t)((a.h >> 4) + 2) * n_pairs;
+    const bool otile_stage = !a.blocks && (ctx->near_tile == 2 || (ctx->near_tile == 3 && (origin_tiles < 4096 || origin_tiles >= 28000)));
     h.S0 = 0;
     h.S1 = tile_stage ? 2 : otile_stage ? std::min(OT_MAX_S1, std::max(2, ctx->near_rings_otile)) : ctx->near_rings;
     h.wl_out = (uint2 *)(wl0 + 64);
