@@ -258,8 +258,9 @@ int32_t stepth_cuda_int_peak(stepth_ctx *ctx, int32_t logic_only, double *ops_pe
  * rows can reach: origins are half-coordinates (depth_image.rs:114-117), widened by max_rings - 1 (helpers.rs:26). */
 void stepth_host_band_plan(uint32_t h, uint32_t add_h, uint32_t max_rings, uint32_t n_ranks, uint32_t rank, uint32_t out[4]);
 
-/* One rank of a row-band group: a context + an NCCL communicator (one process per GPU; rank 0 makes the 128-byte id and hands
- * it to the others by whatever channel the host has).  n_ranks == 1 needs no id and no NCCL. */
+/* One rank of a row-band group: a context + a bootstrap (NCCL) communicator (one process per GPU; rank 0 makes the 128-byte id and
+ * hands it to the others by whatever channel the host has).  n_ranks == 1 needs no id and no NCCL.  Destroy a group only after
+ * every rank's last band call has completed (stepth_cuda_comm_band_result returned): ranks map each other's exchange windows. */
 typedef struct stepth_comm stepth_comm;
 int32_t stepth_cuda_comm_unique_id(uint8_t id_out[128]);
 int32_t stepth_cuda_comm_create(stepth_ctx *ctx, int32_t n_ranks, int32_t rank, const uint8_t id[128], stepth_comm **comm_out);
@@ -268,10 +269,12 @@ void stepth_cuda_comm_destroy(stepth_comm *comm);
 /* This rank's share of depth_image.rs:110-134 (+ fused tail) for ONE pair whose main rows are banded over the group (device
  * pointers, enqueued on `stream`; every rank of the group must make the same call).  w, h: the whole main image; wa: width of
  * the additional rows held here; add_h: rows of the whole additional image.  main_band [rows, w, 4] and add_band [arows, wa, 3]
- * are the rows stepth_host_band_plan gives this rank.  Exchanges (NCCL): all-reduce MAX of the normaliser (:124), 3-row halos
- * of the raw distance plane for the Gaussian (:133), all-reduce SUM of the histogram for depth_split (:162-218), and -- when
- * depth_full_out [h, w] is given -- an all-gather of the depth bands.  depth_band_out [rows, w]; mask_band_out / rgba_band_out
- * optional (fused tail). */
+ * are the rows stepth_host_band_plan gives this rank.  Exchanges: the maximum over all bands for the normaliser (:124), 3-row
+ * halos of the raw distance plane for the Gaussian (:133), and -- when depth_full_out [h, w] is given, by EVERY rank or by none --
+ * the gather of the depth bands: all three as stores into the other ranks' HBM over NVLink by this library's kernels (csrc/peer.cuh;
+ * the gather rides on the finish pass), or as NCCL all-reduce / send-recv / all-gather when the GPUs cannot map each other's
+ * memory; all-reduce SUM of the histogram for depth_split (:162-218, NCCL).  depth_band_out [rows, w]; mask_band_out /
+ * rgba_band_out optional (fused tail).  Status 101 from stepth_cuda_comm_band_result: a peer did not arrive within 20 s. */
 int32_t stepth_cuda_dev_depth_dense_band(stepth_comm *comm, void *stream, uint32_t w, uint32_t h, uint32_t wa, uint32_t add_h,
                                          const stepth_params *params, const uint8_t *main_band, const uint8_t *add_band,
                                          uint8_t *depth_band_out, uint8_t *depth_full_out, uint8_t *mask_band_out,
