@@ -33,7 +33,10 @@ namespace stepth {
 #define STEPTH_OT_WARPS 2   // warps per CTA; measured (16 pairs 1080p, search stage): 2 warps / 48 registers 2.13 ms, 4 / 48 2.15, 4 / 64 2.21, 8 / 48 2.45
 #endif
 constexpr int OT_WARPS = STEPTH_OT_WARPS;   // warps (origin tiles, or half tiles) per CTA, side by side
-constexpr int OT_TASKS = 256;    // task slots of a warp
+#ifndef STEPTH_OT_TASKS
+#define STEPTH_OT_TASKS 256   // measured (16 pairs 1080p, search stage): 128 2.18 ms, 192 2.11, 256 2.10, 384 2.11, 512 2.10
+#endif
+constexpr int OT_TASKS = STEPTH_OT_TASKS;    // task slots of a warp
 constexpr int OT_MAX_S1 = 16;    // rings <= 15 have sides of at most 31 tiles: 32-bit flags
 
 struct OtWarp {
