@@ -171,12 +171,27 @@ STEPTH_HD void fine_test(const HierView &v, const HierQuery &q, int TX, int TY, 
     if (smin >= D || smin > (int)(best >> 12)) return;   // KEY_NONE >> 12 is larger than any ring
     const unsigned long long *rec = v.fine + ((size_t)TY * v.ntx + TX) * T_REC;
     unsigned long long m = ~0ull;
+#if defined(STEPTH_FINE_CANDIDATE) && defined(__CUDA_ARCH__)
+    // the candidate word first (3 loads: the pixels inside the union of the bin's ranges in all three channels); the 12 words
+    // that make it exact only when it is not empty.  Off by default: 16 pairs 1080p `nat` 2.10 -> 2.15 ms (a second dependent
+    // round trip for the two tests out of three that pass), `geo` 5.09 -> 4.93 ms (profiles/recipes/r2_run25.sh)
+#pragma unroll
+    for (int c = 0; c < 3; ++c) m &= ldg(rec + c * T_SLOTS + w_u((q.col >> (8 * c)) & 0xffu));
+    if (!m) return;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const uint32_t qc = (q.col >> (8 * c)) & 0xffu;
+        const unsigned long long *ch = rec + c * T_SLOTS;
+        m &= (ldg(ch + w_up1(qc)) | ldg(ch + w_nta(qc))) & (ldg(ch + w_um1(qc)) | ldg(ch + w_ntb(qc)));
+    }
+#else
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
         const uint32_t qc = (q.col >> (8 * c)) & 0xffu;
         const unsigned long long *ch = rec + c * T_SLOTS;
         m &= ldg(ch + w_u(qc)) & (ldg(ch + w_up1(qc)) | ldg(ch + w_nta(qc))) & (ldg(ch + w_um1(qc)) | ldg(ch + w_ntb(qc)));
     }
+#endif
     if (!m) return;
     const uint32_t k = tile_min_key(m, bx, by, tab_le, tab_ge);
     if ((int)(k >> 12) < D && k < best) best = k;
