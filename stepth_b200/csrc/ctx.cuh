@@ -60,6 +60,7 @@ struct stepth_ctx {
     int peer_enabled = 1;            // STEPTH_PEER=0: the row-band exchanges go through NCCL instead of peer windows
     void *nvj_handle = nullptr, *nvj_state = nullptr, *nvj_enc_state = nullptr, *nvj_enc_params = nullptr;   // codec.cuh (nvJPEG, created on first use)
     Buf codec_a, codec_b;            // codec.cuh: pixels and their RGB8 form on the device
+    Buf dbg;                         // -DSTEPTH_DEBUG_CHECKS builds: the mask of failed index checks of a search
     Buf disc_counts;         // device discretiser: leaves per top-level region, then their offsets (disc.cuh)
     int blocks_on_device = 0;  // run_pairs: the block list it is handed already lies in HBM (stepth_cuda_depth_from_additional)
     Buf planes;  // two-level match bit-planes of the additional image(s) (tiles.cuh), rebuilt by every search

@@ -344,7 +344,21 @@ struct HierArgs {
     uint32_t *wl_in_cursor;
     uint32_t wl_cap;   // entries wl_out can hold
     int S0, S1;        // coarse rings this launch walks
+    uint32_t *dbg_err; // -DSTEPTH_DEBUG_CHECKS builds only: bit mask of the index checks that failed (null otherwise)
 };
+
+// compute-sanitizer is closed on this pool; a -DSTEPTH_DEBUG_CHECKS build (tests run it through STEPTH_LIB) checks every index the
+// search kernels form into shared-memory lists, the tile grid and the work lists, and reports a mask through HierArgs::dbg_err
+#ifdef STEPTH_DEBUG_CHECKS
+#define STEPTH_CHECK(a, cond, bit)                                  \
+    do {                                                            \
+        if (!(cond) && (a).dbg_err) atomicOr((a).dbg_err, 1u << (bit)); \
+    } while (0)
+#else
+#define STEPTH_CHECK(a, cond, bit) \
+    do {                           \
+    } while (0)
+#endif
 
 __device__ __forceinline__ void load_diag_tables(unsigned long long *s_le, unsigned long long *s_ge) {
     for (int t = threadIdx.x; t < 2 * DIAG_N; t += blockDim.x) {
@@ -482,7 +496,7 @@ __device__ __forceinline__ uint32_t emit_side(uint32_t m, int lo, int line, bool
 // Walks coarse rings [S0, S1); returns true when this lane's answer is final.
 __device__ __forceinline__ bool hier_rings_warp(bool walking, const uint8_t *planes, const TileGeom &g, uint32_t pair,
                                                 const HierQuery &q, int D, int S0, int S1, const unsigned long long *tab_le,
-                                                const unsigned long long *tab_ge, uint32_t &best, WarpScratch *ws) {
+                                                const unsigned long long *tab_ge, uint32_t &best, WarpScratch *ws, uint32_t *dbg = nullptr) {
     const uint32_t lane = threadIdx.x & 31;
     const HierView v = make_view(planes, g, pair);
     const int T0x = q.ox >> 3, T0y = q.oy >> 3;
@@ -583,6 +597,9 @@ __device__ __forceinline__ bool hier_rings_warp(bool walking, const uint8_t *pla
                 if (has) {
                     const HierView ov = make_view(planes, g, o_pair);
                     const HierQuery oq = make_query(o_ox, o_oy, o_col);
+#ifdef STEPTH_DEBUG_CHECKS
+                    if (dbg && ((task >> 13 & 0x1fffu) >= (uint32_t)ov.ntx || (task & 0x1fffu) >= (uint32_t)ov.nty)) atomicOr(dbg, 1u << 8);
+#endif
                     uint32_t kb = ws->best[owner];
                     const uint32_t before = kb;
                     fine_test(ov, oq, (int)((task >> 13) & 0x1fffu), (int)(task & 0x1fffu), D, tab_le, tab_ge, kb);
@@ -689,7 +706,7 @@ __global__ void __launch_bounds__(256, STEPTH_NEAR_MINB) search_near_kernel(Hier
             const uint4 e = has ? s_open[i0 + lane] : make_uint4(0, 0, 0, 0);
             const HierQuery q = make_query((int)e.y, (int)e.z, e.w);
             uint32_t key = KEY_NONE;
-            const bool still = !hier_rings_warp(has, a.planes, a.g, pair, q, (int)s.max_rings, 0, a.S1, s_le, s_ge, key, &s_ws[warp]);
+            const bool still = !hier_rings_warp(has, a.planes, a.g, pair, q, (int)s.max_rings, 0, a.S1, s_le, s_ge, key, &s_ws[warp], a.dbg_err);
             export_open(a, has && still, pair, e.x, key);
             publish_result<true>(s, pair, e.x, key, has && !still);
         }
@@ -712,7 +729,7 @@ __global__ void __launch_bounds__(256, STEPTH_NEAR_MINB) search_near_kernel(Hier
     if (valid) ring0_of<BLOCKS>(s, pair, qi, X, Y, ox, oyl, col, key, open);
     if (__any_sync(0xffffffffu, open)) {
         const HierQuery q = make_query(ox, oyl, col);
-        open = !hier_rings_warp(open, a.planes, a.g, pair, q, (int)s.max_rings, 0, a.S1, s_le, s_ge, key, &s_ws[warp]);
+        open = !hier_rings_warp(open, a.planes, a.g, pair, q, (int)s.max_rings, 0, a.S1, s_le, s_ge, key, &s_ws[warp], a.dbg_err);
     }
     export_open(a, open, pair, qi, key);
     publish_result<true>(s, pair, qi, key, valid && !open);
@@ -748,7 +765,7 @@ __global__ void __launch_bounds__(128, STEPTH_FAR_MINB) search_far_kernel(HierAr
         }
         const HierQuery q = make_query(ox, oyl, col);
         const bool open = !hier_rings_warp(valid, a.planes, a.g, pair, q, (int)s.max_rings, a.S0, a.S1, s_le, s_ge, key,
-                                           &s_ws[threadIdx.x >> 5]);
+                                           &s_ws[threadIdx.x >> 5], a.dbg_err);
         if (a.wl_out) export_open(a, open, pair, qi, key);
         publish_result(s, pair, qi, key, valid && !open);
     }

@@ -77,6 +77,12 @@ inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const Search
     STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(wl0, 0, 64, st));
     STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(wl1, 0, 64, st));
     h.wl_cap = (uint32_t)cap;
+#ifdef STEPTH_DEBUG_CHECKS
+    rc = ensure(ctx, ctx->dbg, 256);
+    if (rc != STEPTH_OK) return rc;
+    STEPTH_CUDA_TRY(ctx, cudaMemsetAsync(ctx->dbg.p, 0, 4, st));
+    h.dbg_err = (uint32_t *)ctx->dbg.p;
+#endif
 
     // NEAR: ring 0 + the first coarse rings
     // dense mode: 2 (default) = one warp per origin tile (search_otile.cuh), 1 = rings 0..1 from TMA-staged tile records
@@ -175,6 +181,14 @@ inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const Search
     else search_far_kernel<false><<<far_grid, 128, 0, st>>>(h);
     ctx->launches++;
     STEPTH_CUDA_TRY(ctx, cudaGetLastError());
+#ifdef STEPTH_DEBUG_CHECKS
+    {   // debug builds wait for the search and report the index checks that failed
+        uint32_t bad = 0;
+        STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(&bad, ctx->dbg.p, 4, cudaMemcpyDeviceToHost, st));
+        STEPTH_CUDA_TRY(ctx, cudaStreamSynchronize(st));
+        if (bad) return set_err(ctx, STEPTH_ERR_CUDA, "STEPTH_DEBUG_CHECKS: index checks failed, mask 0x%x (search_hier.cuh / search_otile.cuh)", bad);
+    }
+#endif
     return STEPTH_OK;
 }
 

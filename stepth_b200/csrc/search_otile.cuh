@@ -49,7 +49,7 @@ struct OtWarp {
 
 // the warp tests the listed tiles, 32 at a time
 __device__ __forceinline__ void ot_run_tasks(OtWarp *ws, const HierView &v, int T0x, int T0y, int D, const unsigned long long *tab_le,
-                                             const unsigned long long *tab_ge, uint32_t lane) {
+                                             const unsigned long long *tab_ge, uint32_t lane, uint32_t *dbg = nullptr, int n_list = 256) {
     __syncwarp();
     const int nt = (int)min(ws->n_task, (uint32_t)OT_TASKS);
     for (int t0 = 0; t0 < nt; t0 += 32) {
@@ -57,6 +57,11 @@ __device__ __forceinline__ void ot_run_tasks(OtWarp *ws, const HierView &v, int 
             const uint32_t task = ws->task[t0 + lane];
             const uint32_t e = task & 0xffu;
             const int dx = (int)((task >> 8) & 31u) - 16, dy = (int)((task >> 13) & 31u) - 16;
+#ifdef STEPTH_DEBUG_CHECKS
+            if (dbg && ((int)e >= n_list || (unsigned)(T0x + dx) >= (unsigned)v.ntx || (unsigned)(T0y + dy) >= (unsigned)v.nty || dx < -15 || dx > 15 ||
+                        dy < -15 || dy > 15))
+                atomicOr(dbg, 1u << 0);
+#endif
             const uint32_t ent = ws->ent[e];
             const uint32_t lq = ent >> 24;
             const HierQuery q = make_query(8 * T0x + (int)((lq & 15u) >> 1), 8 * T0y + (int)(lq >> 5), ent & 0xffffffu);
@@ -123,6 +128,7 @@ __device__ __forceinline__ void ot_tile(const HierArgs &a, const uint32_t pair, 
             const uint32_t bal = __ballot_sync(0xffffffffu, open);
             if (open) {
                 const int pos = n + __popc(bal & lt_mask);
+                STEPTH_CHECK(a, pos >= 0 && pos < 256, 1);
                 ws->ent[pos] = col | ((uint32_t)(it * 32) + lane) << 24;
                 ws->best[pos] = KEY_NONE;
             }
@@ -164,6 +170,8 @@ __device__ __forceinline__ void ot_tile(const HierArgs &a, const uint32_t pair, 
             // every pixel outside the (2S-1)^2 tile block lies at ring >= 8 (S-1) + slack + 1
             const bool fin = has && (all_final || (S > 0 && best != KEY_NONE && (int)(best >> 12) <= 8 * (S - 1) + stop_slack(q)));
             if (fin) {
+                STEPTH_CHECK(a, row_base + (int)(lq >> 4) >= 0 && row_base + (int)(lq >> 4) < (int)s.h && x_base + (int)(lq & 15u) >= 0 &&
+                                    x_base + (int)(lq & 15u) < (int)s.w, 3);
                 const uint32_t d = best == KEY_NONE ? 0u : (uint32_t)key_to_d8(best);
                 d8[(uint32_t)(row_base + (int)(lq >> 4)) * s.w + (uint32_t)(x_base + (int)(lq & 15u))] = (uint8_t)d;
                 mx = max(mx, d);
@@ -173,6 +181,7 @@ __device__ __forceinline__ void ot_tile(const HierArgs &a, const uint32_t pair, 
             const int pos = n_new + __popc(bal & lt_mask);
             __syncwarp();   // every lane has read its entry of this batch: the packed ones may overwrite them
             if (keep) {
+                STEPTH_CHECK(a, pos >= 0 && pos <= e && e < 256, 2);   // packing in place never overtakes the read position
                 ws->ent[pos] = ent;
                 ws->best[pos] = best;
             }
@@ -221,13 +230,13 @@ __device__ __forceinline__ void ot_tile(const HierArgs &a, const uint32_t pair, 
                 }
                 __syncwarp();
                 const bool more = __any_sync(0xffffffffu, (f0 | f1 | f2 | f3) != 0u);
-                if (more || ws->n_task > (uint32_t)(OT_TASKS - 96)) ot_run_tasks(ws, v, T0x, T0y, D, s_le, s_ge, lane);
+                if (more || ws->n_task > (uint32_t)(OT_TASKS - 96)) ot_run_tasks(ws, v, T0x, T0y, D, s_le, s_ge, lane, a.dbg_err, n_new > n ? n_new : n);
                 if (!more) break;
             }
         }
         n = n_new;
         if (n == 0) break;
-        if (walk) ot_run_tasks(ws, v, T0x, T0y, D, s_le, s_ge, lane);
+        if (walk) ot_run_tasks(ws, v, T0x, T0y, D, s_le, s_ge, lane, a.dbg_err, n_new > n ? n_new : n);
     }
 
     // ---- what is still open goes to the far kernel ------------------------------------------------------------------------------

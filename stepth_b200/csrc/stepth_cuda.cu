@@ -129,7 +129,7 @@ extern "C" void stepth_cuda_ctx_destroy(stepth_ctx *ctx) {
     stepth_ctx::Buf *bufs[] = {&ctx->main_rgba, &ctx->add_rgb, &ctx->d8,   &ctx->depth, &ctx->mask, &ctx->rgba_out,
                                &ctx->blocks,    &ctx->plane,   &ctx->small, &ctx->u16a,  &ctx->u16b, &ctx->u16o,
                                &ctx->work,      &ctx->planes, &ctx->worklist, &ctx->planes2, &ctx->worklist2, &ctx->work2,
-                               &ctx->main_rgb, &ctx->disc_counts, &ctx->codec_a, &ctx->codec_b};
+                               &ctx->main_rgb, &ctx->disc_counts, &ctx->codec_a, &ctx->codec_b, &ctx->dbg};
     for (auto *b : bufs)
         if (b->p) cudaFree(b->p);
     for (auto &kv : ctx->taps)
