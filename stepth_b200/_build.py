@@ -55,5 +55,16 @@ def build(force: bool = False, verbose: bool = False, out: str | None = None, de
     return out
 
 
+DEBUG_LIB_PATH = os.path.join(_HERE, "libstepth_cuda_dbg.so")
+
+
+def build_debug(force: bool = False) -> str:
+    """the -DSTEPTH_DEBUG_CHECKS variant (index checks of the search kernels; tests/test_gpu_parity.py runs cases through it)"""
+    if not force and os.path.exists(DEBUG_LIB_PATH) and all(
+            not os.path.exists(s) or os.path.getmtime(s) <= os.path.getmtime(DEBUG_LIB_PATH) for s in sources()):
+        return DEBUG_LIB_PATH
+    return build(out=DEBUG_LIB_PATH, defs=["STEPTH_DEBUG_CHECKS=1"])
+
+
 if __name__ == "__main__":
     print(build(force=True, verbose=True))

@@ -1066,3 +1066,48 @@ def test_jpeg_decode_and_encode_on_the_device(ctx, assets, tmp_path):
     finally:
         del os.environ["STEPTH_GPU_DECODE"]
     assert img.image.shape == (400, 600, 4) and np.array_equal(img.image[..., :3], got)
+
+
+# ---- the -DSTEPTH_DEBUG_CHECKS build (compute-sanitizer is closed on this pool) ----------------------------------------------
+_DEBUG_CASE = r"""
+import sys
+sys.path.insert(0, %r)
+import numpy as np
+import stepth_b200 as sb
+from stepth_b200 import synth
+from oracle import oracle
+ctx = sb.Context(0)
+for (w, h, rings, kind, tile) in ((161, 77, 64, "nat", 2), (96, 200, 255, "geo", 2), (257, 33, 300, "nat", 2), (640, 360, 128, "nat", 0), (64, 64, 40, "worst", 2)):
+    import os
+    m, a = synth.make_pair(kind, w, h, 5)
+    m, a = m.numpy(), a.numpy()
+    got = ctx.depth_dense(m, a, [36] * 3, rings, sb.RESAMPLE_U8, want_raw=True)
+    _, raw = oracle.depth_dense(m, a, [36] * 3, rings, resample=oracle.RESAMPLE_U8, threads=4, want_raw=True)
+    assert np.array_equal(got["raw"], raw), (kind, w, h)
+m, a = synth.make_pair("nat", 200, 120, 3)
+m, a = m.numpy(), a.numpy()
+blocks = sb.discretise_v0(m, [36] * 3, 10)
+gb = ctx.depth_from_blocks(a, blocks, 200, 120, [36] * 3, 255, sb.RESAMPLE_U8, want_raw=True)
+_, rb = oracle.depth_from_blocks(a, blocks, [36] * 3, 200, 120, 255, resample=oracle.RESAMPLE_U8, threads=4, want_raw=True)
+assert np.array_equal(gb["raw"], rb)
+print("debug-checks build ok")
+"""
+
+
+@pytest.mark.gpu
+def test_search_kernels_index_checks_build(tmp_path):
+    """the same library compiled with -DSTEPTH_DEBUG_CHECKS: every index the search kernels form (shared-memory lists, tile grid,
+    outputs) is checked on the device and a failed check fails the call; a set of dense / block cases runs clean and bit-exact"""
+    import os
+    import subprocess
+    import sys
+
+    from stepth_b200 import _build
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib = _build.build_debug()
+    env = dict(os.environ, STEPTH_LIB=lib)
+    for near in ("2", "0"):   # the origin-tile stage and the walking kernel
+        env["STEPTH_NEAR_TILE"] = near
+        r = subprocess.run([sys.executable, "-c", _DEBUG_CASE % root], env=env, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0 and "debug-checks build ok" in r.stdout, r.stdout + r.stderr
