@@ -134,28 +134,74 @@ __global__ void __launch_bounds__(128) disc_kernel(DiscArgs a) {
     if (!WRITE) a.counts[t] = n;
 }
 
-// exclusive scan of counts[0 .. n) in place, the total into counts[n]; one CTA of 1024 threads, n <= 65536
-__global__ void __launch_bounds__(1024) disc_scan_kernel(uint32_t *counts, uint32_t n) {
-    __shared__ uint32_t s_part[1024];
-    const uint32_t tid = threadIdx.x, per = (n + 1023) / 1024;
-    const uint32_t i0 = tid * per, i1 = min(n, i0 + per);
-    uint32_t sum = 0;
-    for (uint32_t i = i0; i < i1; ++i) sum += counts[i];
-    s_part[tid] = sum;
+// exclusive scan of counts[0 .. n) in place, the total into counts[n]; ONE CTA of 512 threads.  A thread owns 64 consecutive counts
+// per round (read as sixteen 16-byte words, kept in registers); the 512 per-thread sums are scanned with warp shuffles; rounds
+// of 32768 counts carry their total forward.
+constexpr uint32_t DISC_SCAN_THREADS = 512;
+__global__ void __launch_bounds__(DISC_SCAN_THREADS) disc_scan_kernel(uint32_t *counts, uint32_t n) {
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_carry;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    constexpr uint32_t PER = 64, NW = DISC_SCAN_THREADS / 32;
+    if (tid == 0) s_carry = 0;
     __syncthreads();
-    for (uint32_t d = 1; d < 1024; d <<= 1) {   // inclusive scan of the per-thread sums
-        const uint32_t v = tid >= d ? s_part[tid - d] : 0u;
+    for (uint32_t r0 = 0; r0 < n; r0 += DISC_SCAN_THREADS * PER) {
+        const uint32_t i0 = r0 + tid * PER;
+        const bool vec = i0 + PER <= n && (n & 3u) == 0;   // counts comes from cudaMalloc: 16-byte words are aligned
+        uint32_t v[PER];
+        if (vec) {
+            const uint4 *p = reinterpret_cast<const uint4 *>(counts + i0);
+#pragma unroll
+            for (uint32_t k = 0; k < PER / 4; ++k) {
+                const uint4 q = p[k];
+                v[4 * k] = q.x; v[4 * k + 1] = q.y; v[4 * k + 2] = q.z; v[4 * k + 3] = q.w;
+            }
+        } else {
+#pragma unroll
+            for (uint32_t k = 0; k < PER; ++k) v[k] = i0 + k < n ? counts[i0 + k] : 0u;
+        }
+        uint32_t sum = 0;
+#pragma unroll
+        for (uint32_t k = 0; k < PER; ++k) sum += v[k];
+        uint32_t inc = sum;   // inclusive scan of the per-thread sums: inside the warp, then over the warp totals
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
+            if ((int)lane >= d) inc += t;
+        }
+        if (lane == 31) s_warp[warp] = inc;
         __syncthreads();
-        s_part[tid] += v;
+        if (warp == 0) {
+            uint32_t w = lane < NW ? s_warp[lane] : 0u;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, w, d);
+                if ((int)lane >= d) w += t;
+            }
+            s_warp[lane] = w;   // inclusive totals of warps 0 .. lane
+        }
+        __syncthreads();
+        uint32_t run = s_carry + inc - sum + (warp ? s_warp[warp - 1] : 0u);   // everything before this thread's first count
+#pragma unroll
+        for (uint32_t k = 0; k < PER; ++k) {
+            const uint32_t c = v[k];
+            v[k] = run;
+            run += c;
+        }
+        if (vec) {
+            uint4 *p = reinterpret_cast<uint4 *>(counts + i0);
+#pragma unroll
+            for (uint32_t k = 0; k < PER / 4; ++k) p[k] = make_uint4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+        } else {
+#pragma unroll
+            for (uint32_t k = 0; k < PER; ++k)
+                if (i0 + k < n) counts[i0 + k] = v[k];
+        }
+        __syncthreads();   // everybody has read s_carry and s_warp
+        if (tid == 0) s_carry += s_warp[NW - 1];
         __syncthreads();
     }
-    uint32_t run = s_part[tid] - sum;
-    for (uint32_t i = i0; i < i1; ++i) {
-        const uint32_t c = counts[i];
-        counts[i] = run;
-        run += c;
-    }
-    if (tid == 1023) counts[n] = s_part[1023];
+    if (tid == 0) counts[n] = s_carry;
 }
 
 #endif  // __CUDACC__

@@ -1120,7 +1120,7 @@ int32_t disc_count(stepth_ctx *ctx, cudaStream_t st, const uint8_t *px_dev, uint
     disc_kernel<false><<<(n_top + 127) / 128, 128, 0, st>>>(a);
     ctx->launches++;
     STEPTH_CUDA_TRY(ctx, cudaGetLastError());
-    disc_scan_kernel<<<1, 1024, 0, st>>>(a.counts, n_top);
+    disc_scan_kernel<<<1, DISC_SCAN_THREADS, 0, st>>>(a.counts, n_top);
     ctx->launches++;
     STEPTH_CUDA_TRY(ctx, cudaGetLastError());
     return STEPTH_OK;
