@@ -56,6 +56,7 @@ struct stepth_ctx {
     uint8_t *finish_mirror[8] = {};  // row bands: where the next dev_finish call also stores its outputs (peer.cuh); cleared by the caller
     uint32_t finish_n_mirror = 0;
     int finish_mirrored = 0;         // set by dev_finish when it did
+    int tail_kernel = 1;             // STEPTH_TAIL=0: the last search stage always walks its list with one lane per query
     int k0_tensor_map = 1;           // STEPTH_K0_TMAP=0: K0's strips by per-row bulk copies / plain loads only
     int peer_enabled = 1;            // STEPTH_PEER=0: the row-band exchanges go through NCCL instead of peer windows
     void *nvj_handle = nullptr, *nvj_state = nullptr, *nvj_enc_state = nullptr, *nvj_enc_params = nullptr;   // codec.cuh (nvJPEG, created on first use)

@@ -344,6 +344,7 @@ struct HierArgs {
     uint32_t *wl_in_cursor;
     uint32_t wl_cap;   // entries wl_out can hold
     int S0, S1;        // coarse rings this launch walks
+    int tail_split;    // last stage only: lists of at most this many entries go to search_tail_kernel, longer ones to search_far_kernel
     uint32_t *dbg_err; // -DSTEPTH_DEBUG_CHECKS builds only: bit mask of the index checks that failed (null otherwise)
 };
 
@@ -735,6 +736,12 @@ __global__ void __launch_bounds__(256, STEPTH_NEAR_MINB) search_near_kernel(Hier
     publish_result<true>(s, pair, qi, key, valid && !open);
 }
 
+// A work list this short is a matter of latency, not of throughput: the last stage hands it to search_tail_kernel (one WARP per
+// query) instead of walking it with one lane per query.  Both kernels are launched; the list's length, known on the device only,
+// decides which of them works.
+// (HierArgs::tail_split = the longest list the tail kernel takes; 0 = none.  Measured on one README pair, 255 rings: block list
+// 0.210 -> 0.183 ms, dense 0.150 -> 0.131 ms; one 1080p pair at 128 rings, four rings left for this stage: no gain)
+
 // FAR kernel: resumes the listed queries at coarse ring S0; a warp pulls 32 consecutive entries at a time.
 template <bool BLOCKS>
 __global__ void __launch_bounds__(128, STEPTH_FAR_MINB) search_far_kernel(HierArgs a) {
@@ -744,6 +751,7 @@ __global__ void __launch_bounds__(128, STEPTH_FAR_MINB) search_far_kernel(HierAr
     const SearchArgs &s = a.s;
     const int lane = threadIdx.x & 31;
     const uint32_t n_entries = min(*a.wl_in_count, a.wl_cap);
+    if (n_entries <= (uint32_t)a.tail_split) return;   // search_tail_kernel takes this list
     for (;;) {
         uint32_t e0 = 0;
         if (lane == 0) e0 = atomicAdd(a.wl_in_cursor, 32u);
@@ -768,6 +776,70 @@ __global__ void __launch_bounds__(128, STEPTH_FAR_MINB) search_far_kernel(HierAr
                                            &s_ws[threadIdx.x >> 5], a.dbg_err);
         if (a.wl_out) export_open(a, open, pair, qi, key);
         publish_result(s, pair, qi, key, valid && !open);
+    }
+}
+
+// TAIL kernel: the same rings for a SHORT list, one warp per query.  A ring has four sides of at most 65 / 63 tiles = ten runs of at
+// most 32 tiles; the lanes take the thirty runs of three consecutive rings, each reads its occupancy window (one 64-tile window
+// holds any run of 32) and tests its flagged tiles itself; a warp minimum folds the keys.  A query that walks twenty empty rings
+// pays seven window round trips instead of twenty times four (the README pair at 255 rings: 62 -> about 15 us for the stage).
+template <bool BLOCKS>
+__global__ void __launch_bounds__(128) search_tail_kernel(HierArgs a) {
+    __shared__ unsigned long long s_le[DIAG_N], s_ge[DIAG_N];
+    load_diag_tables(s_le, s_ge);
+    const SearchArgs &s = a.s;
+    const int lane = threadIdx.x & 31;
+    const uint32_t n_entries = min(*a.wl_in_count, a.wl_cap);
+    if (n_entries > (uint32_t)a.tail_split) return;   // search_far_kernel takes this list
+    const int D = (int)s.max_rings, Smax = (D + 6) >> 3;
+    const uint32_t warps = gridDim.x * (blockDim.x >> 5);
+    const int g = lane / 10, item = lane - 10 * g;   // ring of the group, run of the ring (lanes 30, 31: none)
+#pragma unroll 1
+    for (uint32_t e = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); e < n_entries; e += warps) {
+        const uint2 ent = a.wl_in[e];
+        const uint32_t qi = ent.x, pair = ent.y >> 21, k21 = ent.y & KEY21_NONE;
+        uint32_t best = k21 == KEY21_NONE ? KEY_NONE : k21;
+        int ox, oyg;
+        uint32_t col;
+        query_of<BLOCKS>(s, pair, qi, ox, oyg, col);
+        const HierQuery q = make_query(ox, oyg - (int)s.add_y0, col);
+        const HierView v = make_view(a.planes, a.g, pair);
+        const int T0x = q.ox >> 3, T0y = q.oy >> 3, xmax = v.ntx - 1, ymax = v.nty - 1;
+        const int slack = stop_slack(q);
+#pragma unroll 1
+        for (int S = a.S0; S <= Smax; S += 3) {
+            if (T0x - S < 0 && T0x + S > xmax && T0y - S < 0 && T0y + S > ymax) break;   // the coarse square has left the tile grid
+            const int R = S + g;
+            uint32_t kb = best;
+            if (g < 3 && R <= Smax) {
+                // runs: 0-2 row T0y+R, 3-5 row T0y-R (tiles T0x-R .. T0x+R); 6-7 column T0x+R, 8-9 column T0x-R (tiles T0y-R+1 .. T0y+R-1)
+                const bool is_col = item >= 6;
+                const int side = is_col ? 2 + (item - 6) / 2 : item / 3, seg = is_col ? (item - 6) & 1 : item % 3;
+                const int line = (is_col ? T0x : T0y) + ((side & 1) ? -R : R);
+                const int first = is_col ? T0y - R + 1 : T0x - R, last = is_col ? T0y + R - 1 : T0x + R;
+                int lo = first + 32 * seg, hi = lo + 31 < last ? lo + 31 : last;
+                const int lim = is_col ? ymax : xmax;
+                lo = lo < 0 ? 0 : lo;
+                hi = hi > lim ? lim : hi;
+                if ((unsigned)line < (unsigned)(is_col ? v.ntx : v.nty) && lo <= hi) {
+                    const unsigned long long w = coarse_window(is_col ? v.ccp : v.crp, (uint32_t)(line * (is_col ? v.nyw : v.nxw) + (lo >> 5)), q);
+                    uint32_t m = __funnelshift_r((uint32_t)w, (uint32_t)(w >> 32), lo & 31) & ((2u << (hi - lo)) - 1u);
+                    while (m) {
+                        const int p = lo + __ffs((int)m) - 1;
+                        m &= m - 1;
+                        fine_test(v, q, is_col ? line : p, is_col ? p : line, D, s_le, s_ge, kb);
+                    }
+                }
+            }
+            best = __reduce_min_sync(0xffffffffu, kb);
+            const int R_last = S + 2 < Smax ? S + 2 : Smax;
+            if (best != KEY_NONE && (int)(best >> 12) <= 8 * R_last + slack) break;
+        }
+        if (lane == 0) {
+            const uint32_t d = best == KEY_NONE ? 0u : (uint32_t)key_to_d8(best);
+            s.d8[(size_t)pair * s.n_queries + qi] = (uint8_t)d;
+            if (d && d > *(volatile uint32_t *)(s.max_out + pair)) atomicMax(s.max_out + pair, d);
+        }
     }
 }
 

@@ -177,10 +177,24 @@ inline int32_t launch_search_hier(stepth_ctx *ctx, cudaStream_t st, const Search
     h.wl_in_cursor = (uint32_t *)in + 1;
     h.wl_out = nullptr;
     h.wl_out_count = nullptr;
+    // a short list (one README pair, one 1080p pair) is walked by one warp per query (search_tail_kernel), a long one by one lane
+    // per query: both kernels are launched, the list's length decides on the device which of them works.  The tail kernel's runs of
+    // 32 tiles cover sides of up to 96 tiles: rings <= 32, max_rings <= 257
+    {
+        const int smax = ((int)a.max_rings + 6) / 8, left = smax - h.S0;   // coarse rings this stage may have to walk
+        h.tail_split = (ctx->tail_kernel && smax <= 32 && left > 0) ? (left >= 12 ? 24576 : 6144) : 0;
+    }
     if (a.blocks) search_far_kernel<true><<<far_grid, 128, 0, st>>>(h);
     else search_far_kernel<false><<<far_grid, 128, 0, st>>>(h);
     ctx->launches++;
     STEPTH_CUDA_TRY(ctx, cudaGetLastError());
+    if (h.tail_split) {
+        const uint32_t tail_grid = (uint32_t)ctx->sm_count * 8;
+        if (a.blocks) search_tail_kernel<true><<<tail_grid, 128, 0, st>>>(h);
+        else search_tail_kernel<false><<<tail_grid, 128, 0, st>>>(h);
+        ctx->launches++;
+        STEPTH_CUDA_TRY(ctx, cudaGetLastError());
+    }
 #ifdef STEPTH_DEBUG_CHECKS
     {   // debug builds wait for the search and report the index checks that failed
         uint32_t bad = 0;

@@ -93,6 +93,7 @@ extern "C" int32_t stepth_cuda_ctx_create(int32_t device, stepth_ctx **ctx_out) 
     if (const char *ev = getenv("STEPTH_TRACE")) ctx->trace = atoi(ev);
     if (const char *ev = getenv("STEPTH_PEER")) ctx->peer_enabled = atoi(ev);
     if (const char *ev = getenv("STEPTH_K0_TMAP")) ctx->k0_tensor_map = atoi(ev);
+    if (const char *ev = getenv("STEPTH_TAIL")) ctx->tail_kernel = atoi(ev);
     if (const char *ev = getenv("STEPTH_UPLOAD_FULL_ROWS")) ctx->upload_full_rows = atoi(ev);
     {   // copy threads behind pageable host buffers: half of the CPUs this process may run on (its affinity mask -- a launcher
         // that binds one process per GPU to the GPU's NUMA neighbourhood narrows it), at most 16 (64 x 4K, pageable: 8 threads
