@@ -213,6 +213,26 @@ int32_t stepth_cuda_dev_discretise_v0(stepth_ctx *ctx, void *stream, const uint8
                                       uint32_t h, const uint8_t precision[3], uint32_t min_splits, uint32_t max_splits,
                                       stepth_block *blocks_out, size_t cap, uint32_t *n_out);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  stepth_cuda_dev_discretise_v0 with the same
+ * arguments and the same result (block list, order, *n_out), except that this call allocates nothing -- no cudaMalloc, cudaFree
+ * or allocating library routine, on the first call or any later one: the kernels' scratch (the per-region counts) is a
+ * file-scope device array of STEPTH_NOALLOC_DISC_SCRATCH_BYTES that every GPU which loads this library holds until exit.
+ * Limits, rejected with STEPTH_ERR_INVALID_ARG and a text in stepth_cuda_last_error(ctx) where the allocating call would clamp
+ * or carry on:  min(min_splits, max_splits) <= STEPTH_NOALLOC_DISC_MAX_TOP (2^16 forced regions fill the scratch; the
+ * reference's own min_splits is 16, depth_image.rs:101) and w * h <= STEPTH_NOALLOC_DISC_MAX_PIXELS (at most 2^16 threads
+ * walk the image: 1024 pixels apiece at the limit).
+ * EVERY call on a device shares the one array: calls that overlap on that GPU (two streams, two host threads, two contexts)
+ * race on it -- serialise them.  The array keeps the last call's contents; nothing in it has to be cleared (a call writes every
+ * word it reads).  The first call on a device looks the array's address up (cudaGetSymbolAddress, no allocation): make one
+ * call outside a capture before capturing. */
+#define STEPTH_NOALLOC_DISC_MAX_TOP 16
+#define STEPTH_NOALLOC_DISC_SCRATCH_BYTES 262400 /* (2^16 + 1) u32 counts, rounded up to 256 */
+#define STEPTH_NOALLOC_DISC_MAX_PIXELS 67108864ull /* 2^26 */
+int32_t stepth_cuda_dev_discretise_v0_noalloc(stepth_ctx *ctx, void *stream, const uint8_t *main_px, uint32_t stride, uint32_t w,
+                                              uint32_t h, const uint8_t precision[3], uint32_t min_splits, uint32_t max_splits,
+                                              stepth_block *blocks_out, size_t cap, uint32_t *n_out);
+
 /* paint: plane_out[h,w] = d8[b] over each block rectangle (DiscreteImage::collect + luma, depth_image.rs:130-132).
  * The plane holds RAW distances: the normalisation of :125-129 is a per-byte map and is applied by dev_finish. */
 int32_t stepth_cuda_dev_paint_blocks(stepth_ctx *ctx, void *stream, const stepth_block *blocks,

@@ -87,6 +87,7 @@ SIGNATURES = {
     "stepth_host_discretise_v0": (_sz, [_u8p, _u32, _u32, _u32, _u8p, _u32, _u32, _vp, _sz]),
     "stepth_cuda_discretise_v0": (_i32, [_vp, _u8p, _u32, _u32, _u32, _u8p, _u32, _u32, _vp, _sz, C.POINTER(_sz)]),
     "stepth_cuda_dev_discretise_v0": (_i32, [_vp, _vp, _u8p, _u32, _u32, _u32, _u8p, _u32, _u32, _vp, _sz, _u32p]),
+    "stepth_cuda_dev_discretise_v0_noalloc": (_i32, [_vp, _vp, _u8p, _u32, _u32, _u32, _u8p, _u32, _u32, _vp, _sz, _u32p]),
     "stepth_cuda_depth_from_additional": (_i32, [_vp, _u8p, _u32, _u32, _u8p, _u32, _u32, _PP, _u32, _u32, _u8p, _u8p, _u8p, _u8p,
                                                  C.POINTER(_sz)]),
     "stepth_cuda_decode_jpeg": (_i32, [_vp, _u8p, _sz, _u32p, _u32p, _u8p, _sz]),

@@ -1172,6 +1172,89 @@ extern "C" int32_t stepth_cuda_dev_discretise_v0(stepth_ctx *ctx, void *stream, 
     return STEPTH_OK;
 }
 
+// ---- the device discretiser without any allocation ---------------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc (CUDA
+// graph capture, tight serving loops).  The per-region counts -- the only scratch of disc_kernel / disc_scan_kernel, which
+// stepth_cuda_dev_discretise_v0 keeps in a context buffer that grows with cudaMalloc -- live in a file-scope device array of
+// a fixed size instead: every GPU that loads this library holds its STEPTH_NOALLOC_DISC_SCRATCH_BYTES until the process exits.
+// Every call on a device shares the array: calls that overlap on that GPU (two streams, two threads) race on it.  Nothing in
+// it has to start at zero: pass 1 writes counts[0 .. 2^top), the scan writes counts[2^top], and only those words are read.
+static_assert(STEPTH_NOALLOC_DISC_MAX_TOP <= stepth::DISC_MAX_TOP, "the kernels' own limit");
+static_assert(STEPTH_NOALLOC_DISC_SCRATCH_BYTES >= sizeof(uint32_t) * ((1u << STEPTH_NOALLOC_DISC_MAX_TOP) + 1), "counts + the total");
+static __device__ __align__(256) uint32_t g_noalloc_disc_counts[STEPTH_NOALLOC_DISC_SCRATCH_BYTES / sizeof(uint32_t)];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+uint32_t *g_noalloc_counts_dev[NOALLOC_MAX_DEVICES] = {};   // the array's DEVICE address, per device (the name above is a host-side stand-in)
+
+// once per device, with that device current: where the array lives in that GPU's memory
+int32_t noalloc_counts(stepth_ctx *ctx, uint32_t **out) {
+    if (ctx->device < 0 || ctx->device >= NOALLOC_MAX_DEVICES)
+        return set_err(ctx, STEPTH_ERR_INVALID_ARG, "dev_discretise_v0_noalloc: device %d beyond the %d this entry point keeps addresses for",
+                       ctx->device, NOALLOC_MAX_DEVICES);
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_counts_dev[ctx->device]) {
+        int cur = -1;
+        STEPTH_CUDA_TRY(ctx, cudaGetDevice(&cur));
+        if (cur != ctx->device) STEPTH_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+        uint32_t *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void **)&p, g_noalloc_disc_counts);
+        if (cur != ctx->device && cur >= 0) cudaSetDevice(cur);
+        if (e != cudaSuccess || !p)
+            return set_err(ctx, STEPTH_ERR_CUDA, "cudaGetSymbolAddress(g_noalloc_disc_counts) failed on device %d: %s", ctx->device,
+                           cudaGetErrorString(e));
+        g_noalloc_counts_dev[ctx->device] = p;
+    }
+    *out = g_noalloc_counts_dev[ctx->device];
+    return STEPTH_OK;
+}
+}  // namespace
+
+extern "C" int32_t stepth_cuda_dev_discretise_v0_noalloc(stepth_ctx *ctx, void *stream, const uint8_t *main_px, uint32_t stride,
+                                                         uint32_t w, uint32_t h, const uint8_t precision[3], uint32_t min_splits,
+                                                         uint32_t max_splits, stepth_block *blocks_out, size_t cap, uint32_t *n_out) {
+    using namespace stepth;
+    if (!ctx) return STEPTH_ERR_INVALID_ARG;
+    if (!disc_args_ok(main_px, stride, w, h, precision) || ((uintptr_t)blocks_out & 3))
+        return set_err(ctx, STEPTH_ERR_INVALID_ARG, "dev_discretise_v0_noalloc: null or invalid argument");
+    const uint32_t top = std::min(min_splits, max_splits);
+    if (top > STEPTH_NOALLOC_DISC_MAX_TOP)
+        return set_err(ctx, STEPTH_ERR_INVALID_ARG,
+                       "dev_discretise_v0_noalloc: min(min_splits, max_splits) = %u asks for 2^%u forced regions; the static scratch holds "
+                       "2^%d (%d bytes): use stepth_cuda_dev_discretise_v0",
+                       top, top, STEPTH_NOALLOC_DISC_MAX_TOP, STEPTH_NOALLOC_DISC_SCRATCH_BYTES);
+    if ((uint64_t)w * h > STEPTH_NOALLOC_DISC_MAX_PIXELS)
+        return set_err(ctx, STEPTH_ERR_INVALID_ARG,
+                       "dev_discretise_v0_noalloc: %u x %u pixels; the limit of this entry point is %llu: use stepth_cuda_dev_discretise_v0", w, h,
+                       (unsigned long long)STEPTH_NOALLOC_DISC_MAX_PIXELS);
+    uint32_t *counts = nullptr;
+    TRY_RC(noalloc_counts(ctx, &counts));
+    cudaStream_t st = (cudaStream_t)stream;
+    DiscArgs a;
+    memset(&a, 0, sizeof a);
+    a.px = main_px; a.stride = stride; a.w = w; a.h = h;
+    a.pr = precision[0]; a.pg = precision[1]; a.pb = precision[2];
+    a.min_s = min_splits; a.max_s = max_splits;
+    a.top = top;
+    a.counts = counts;
+    const uint32_t n_top = 1u << a.top;
+    disc_kernel<false><<<(n_top + 127) / 128, 128, 0, st>>>(a);
+    ctx->launches++;
+    STEPTH_CUDA_TRY(ctx, cudaGetLastError());
+    disc_scan_kernel<<<1, DISC_SCAN_THREADS, 0, st>>>(a.counts, n_top);
+    ctx->launches++;
+    STEPTH_CUDA_TRY(ctx, cudaGetLastError());
+    if (blocks_out && cap) {
+        a.out = blocks_out; a.cap = cap;
+        disc_kernel<true><<<(n_top + 127) / 128, 128, 0, st>>>(a);
+        ctx->launches++;
+        STEPTH_CUDA_TRY(ctx, cudaGetLastError());
+    }
+    if (n_out) STEPTH_CUDA_TRY(ctx, cudaMemcpyAsync(n_out, a.counts + n_top, sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+    return STEPTH_OK;
+}
+
 extern "C" int32_t stepth_cuda_discretise_v0(stepth_ctx *ctx, const uint8_t *main_px, uint32_t stride, uint32_t w, uint32_t h,
                                              const uint8_t precision[3], uint32_t min_splits, uint32_t max_splits,
                                              stepth_block *blocks_out, size_t cap, size_t *n_out) {
