@@ -112,3 +112,94 @@ def test_discretise_v0_tiles_the_image():
     # identical pixels everywhere: stops right at the forced depth
     flat = np.full((256, 256, 3), 7, np.uint8)
     assert len(stepth_b200.discretise_v0(flat, [36, 36, 36])) == 65536
+
+
+# ---- the Rust FFI crate (source only: no Rust toolchain in the build image) against the header --------------------------------
+_C2RUST = {"int32_t": "i32", "uint32_t": "u32", "uint64_t": "u64", "size_t": "usize", "double": "c_double", "float": "c_float",
+           "uint8_t": "u8", "uint16_t": "u16", "char": "c_char", "void": "c_void"}
+
+
+def _c_param_to_rust(p):
+    """`const uint8_t *const *main_rgba` -> `*const *const u8`; `uint8_t id_out[128]` -> `*mut u8`; `uint32_t w` -> `u32`"""
+    p = p.strip()
+    arr = re.search(r"\[\d*\]$", p)
+    if arr:
+        p = p[:arr.start()]
+    m = re.match(r"^(const\s+)?(\w+)\s*((?:\*\s*(?:const\s*)?)*)\s*(\w+)?$", p)
+    assert m, p
+    base_const, base, stars, _name = m.groups()
+    ty = _C2RUST.get(base, base)   # struct names (stepth_ctx ..) are the same on both sides
+    # pointers, innermost first: the first `*` points at the (const?) base; a `const` after a `*` qualifies THAT pointer,
+    # i.e. the pointee of the next `*`
+    levels = re.findall(r"\*\s*(const)?", stars)
+    pointee_const = bool(base_const)
+    for lv in levels:
+        ty = ("*const " if pointee_const else "*mut ") + ty
+        pointee_const = lv == "const"
+    if arr:
+        ty = ("*const " if base_const else "*mut ") + ty
+    return ty
+
+
+def _header_prototypes():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    src = "\n".join(l for l in src.splitlines() if not l.lstrip().startswith("#"))
+    protos = {}
+    for ret, name, params in re.findall(r"([\w\s\*]+?)\b(stepth_(?:cuda|host)_\w+)\s*\(([^)]*)\)\s*;", src):
+        ret = ret.replace("extern \"C\" {", "").strip()
+        ps = [] if params.strip() == "void" else [_c_param_to_rust(p) for p in params.split(",")]
+        rret = None if ret == "void" else _c_param_to_rust(ret + " _")
+        assert name not in protos, name
+        protos[name] = (ps, rret)
+    return protos
+
+
+def _rust_prototypes():
+    src = open(os.path.join(ROOT, "rust", "stepth-cuda-sys", "src", "lib.rs")).read()
+    src = re.sub(r"//[^\n]*", "", src)
+    block = src[src.index('extern "C" {'):]
+    out = []
+    for name, params, ret in re.findall(r"pub fn (\w+)\s*\(([^)]*)\)\s*(?:->\s*([^;]+))?;", block):
+        ps = [re.sub(r"\s+", " ", p.split(":", 1)[1].strip()) for p in params.split(",") if p.strip()]
+        out.append((name, ps, ret.strip() if ret else None))
+    return out
+
+
+def test_c_to_rust_type_mapping():
+    assert _c_param_to_rust("const uint8_t *const *main_rgba") == "*const *const u8"
+    assert _c_param_to_rust("uint8_t *const *depth_out") == "*const *mut u8"
+    assert _c_param_to_rust("stepth_ctx **ctx_out") == "*mut *mut stepth_ctx"
+    assert _c_param_to_rust("const uint8_t precision[3]") == "*const u8"
+    assert _c_param_to_rust("float ms_out[4]") == "*mut c_float"
+    assert _c_param_to_rust("void *stream") == "*mut c_void"
+    assert _c_param_to_rust("uint32_t w") == "u32"
+
+
+def test_rust_sys_crate_matches_the_header():
+    """rust/stepth-cuda-sys/src/lib.rs declares every function of include/stepth_cuda.h exactly once, with the same number of
+    parameters, the same parameter types and the same return type (the cgo / bindgen stand-in while no Rust toolchain exists)."""
+    header = _header_prototypes()
+    rust = _rust_prototypes()
+    names = [n for n, _, _ in rust]
+    assert len(names) == len(set(names)), sorted(n for n in set(names) if names.count(n) > 1)   # a duplicate does not compile
+    assert sorted(names) == sorted(header), (sorted(set(header) - set(names)), sorted(set(names) - set(header)))
+    for name, ps, ret in rust:
+        hps, hret = header[name]
+        assert ps == hps, (name, ps, hps)
+        assert ret == hret, (name, ret, hret)
+    # constants: every numeric #define of the header exists on the Rust side with the same value
+    hsrc = re.sub(r"/\*.*?\*/", "", open(HEADER).read(), flags=re.S)
+    rsrc = open(os.path.join(ROOT, "rust", "stepth-cuda-sys", "src", "lib.rs")).read()
+    for name, val in re.findall(r"#define\s+(STEPTH_[A-Z0-9_]+)\s+(.+)", hsrc):
+        if name == "STEPTH_CUDA_H":
+            continue
+        v = val.strip().replace("ull", "").replace("u", "")
+        want = eval(v)   # `(1 << 2)`, `100`, `262400`
+        m = re.search(rf"pub const {name}: \w+ = ([^;]+);", rsrc)
+        assert m, f"{name} missing in lib.rs"
+        assert eval(m.group(1)) == want, (name, m.group(1), want)
+    # struct sizes on the Rust side follow the same field lists (repr(C))
+    for struct, fields in (("stepth_dev_shape", 9), ("stepth_params", 4), ("stepth_block", 6)):
+        body = re.search(rf"pub struct {struct} \{{(.*?)\}}", rsrc, flags=re.S).group(1)
+        assert len(re.findall(r"pub \w+:", body)) == fields, struct
