@@ -203,3 +203,25 @@ def test_rust_sys_crate_matches_the_header():
     for struct, fields in (("stepth_dev_shape", 9), ("stepth_params", 4), ("stepth_block", 6)):
         body = re.search(rf"pub struct {struct} \{{(.*?)\}}", rsrc, flags=re.S).group(1)
         assert len(re.findall(r"pub \w+:", body)) == fields, struct
+
+
+def test_headers_compile_as_plain_c_and_cpp(tmp_path):
+    """include/stepth_cuda.h is a C header (C99, pedantic, no warnings) with the record sizes the bindings assume; include/stepth.hpp
+    (the C++ host mirror) and its test driver parse as C++17.  The GPU suite links and runs the driver (test_cpp_host_mirror)."""
+    import shutil
+    import subprocess
+
+    if not shutil.which("gcc") or not shutil.which("g++"):
+        pytest.skip("no host compiler")
+    inc = os.path.join(ROOT, "include")
+    src = tmp_path / "abi.c"
+    src.write_text('#include "stepth_cuda.h"\n'
+                   "int main(void) { return sizeof(stepth_block) == 20 && sizeof(stepth_params) == 12 && "
+                   "sizeof(stepth_dev_shape) == 36 ? 0 : 1; }\n")
+    exe = tmp_path / "abi"
+    subprocess.run(["gcc", "-std=c99", "-pedantic", "-Wall", "-Wextra", "-Werror", f"-I{inc}", str(src), "-o", str(exe)],
+                   check=True, capture_output=True)
+    assert subprocess.run([str(exe)]).returncode == 0
+    r = subprocess.run(["g++", "-std=c++17", "-fsyntax-only", f"-I{inc}", f"-I{os.path.join(ROOT, 'oracle')}",
+                        os.path.join(ROOT, "tests", "cpp", "test_host.cpp")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
