@@ -233,6 +233,31 @@ def test_assets_depth_soft_pin(orc, assets):
     assert r_sat < r
 
 
+def test_assets_depth_soft_pin_block_mode(orc, assets):
+    """The README call runs in BLOCK mode (depth_image.rs:104-122).  With the stand-in discretiser at the reference's parameters
+    (min 16 splits, max ceil(log2(w*h))) the restatement comes closer to assets/depth.jpg than the dense limit case does, and the
+    unpinned PixelOpps alternatives rank below the default (tests/golden/soft_evidence.py prints the whole table)."""
+    import stepth_b200
+
+    main, add, depth = assets["main"], assets["additional"], assets["depth"].astype(np.float64)
+    h, w = depth.shape
+    p = [255 // 7] * 3
+    blocks = stepth_b200.discretise_v0(main, p)   # host code of the product library: no GPU involved
+    assert 65536 <= len(blocks) <= w * h
+
+    def r_mae(out):
+        o = out.reshape(-1).astype(np.float64)
+        return np.corrcoef(o, depth.reshape(-1))[0, 1], np.abs(o - depth.reshape(-1)).mean()
+
+    r_blk, mae_blk = r_mae(orc.depth_from_blocks(add, blocks, p, w, h, 255))
+    r_dense, mae_dense = r_mae(orc.depth_dense(main, add, p, 255))
+    assert r_blk >= 0.985 and mae_blk < 1.1, (r_blk, mae_blk)
+    assert r_blk >= r_dense - 1e-3 and mae_blk <= mae_dense + 0.05, (r_blk, r_dense, mae_blk, mae_dense)
+    r_sum, _ = r_mae(orc.depth_from_blocks(add, blocks, p, w, h, 255, pixelopps=orc.PIXELOPPS_ABS_SUM))
+    r_sat, _ = r_mae(orc.depth_from_blocks(add, blocks, p, w, h, 255, pixelopps=orc.PIXELOPPS_SAT_ALL))
+    assert r_blk > r_sat > r_sum, (r_blk, r_sat, r_sum)
+
+
 def test_assets_foreground_known_answer(orc, assets):
     """Readme.md:18-24: invert_depth -> select_foreground -> apply_mask on depth.jpg gives foreground.jpg.
     Pure stepth code (no disage): the closest thing to a known-answer test the reference has."""
