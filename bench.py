@@ -1052,7 +1052,7 @@ RUNNERS = {"dense": run_dense, "blocks": run_blocks, "bands": run_giant}
 def compact(line):
     """an other_workloads entry: the same keys as a line, minus what only the main line needs"""
     return {k: line[k] for k in ("value", "ms_per_step", "steps", "scaling", "config", "roofline", "cpu_baseline", "e2e", "parity",
-                                 "gpu_launches", "stage_ms_per_rank") if k in line}
+                                 "gpu_launches", "stage_ms_per_rank", "graph_replay") if k in line}
 
 
 def run_ours(args):

@@ -504,6 +504,58 @@ def test_device_pipeline_matches_host_api(ctx, orc):
         assert tuple(pipe.ranges[i, :2].tolist()) == host["from_to"]
 
 
+def test_stage_api_under_cuda_graph_capture(ctx, orc):
+    """The stage API only enqueues work on the caller's stream and, once it has seen a shape, neither allocates nor synchronises:
+    a caller may capture a whole step into a CUDA graph and replay it (bench.py: graph_replay).  Dense mode with the fused tail,
+    replayed on fresh inputs of the same shape, and block mode with the device discretiser, against the host API and the oracle."""
+    import stepth_b200 as sb
+    from stepth_b200 import device
+
+    w, h, rings = 100, 60, 64
+    flags = sb.RESAMPLE_U8 | sb.FLAG_INVERT | sb.FLAG_FOREGROUND | sb.FLAG_APPLY
+    first, second = synth_pair("geo", w, h, seed=4), synth_pair("geo", w, h, seed=5)
+    mains = torch.from_numpy(first[0][None]).cuda().contiguous()
+    adds = torch.from_numpy(first[1][None]).cuda().contiguous()
+    pipe = device.DensePipeline(ctx, 1, w, h, w, h, P36, rings, flags)
+    # block mode: its own (constant) inputs, the list rebuilt on the device inside the graph
+    blocks = sb.discretise_v0(first[0], P36, min_splits=8)
+    bmain, badd = mains[0].clone(), adds[0].clone()
+    bpipe = device.BlockPipeline(ctx, len(blocks), w, h, w, h, P36, rings, sb.RESAMPLE_U8)
+    blocks_t = torch.zeros((len(blocks), 20), dtype=torch.uint8, device="cuda")
+    want_blocks = orc.depth_from_blocks(first[1], blocks, P36, w, h, rings)
+
+    def step():
+        pipe.run(mains, adds)
+        bpipe.discretise(bmain, blocks_t, min_splits=8)
+        bpipe.run(blocks_t, badd)
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        step()   # the first call of a shape sizes the library's scratch: outside the capture
+    side.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=side, capture_error_mode="thread_local"):
+        step()
+    torch.cuda.synchronize()
+    for pair in (second, first):
+        mains.copy_(torch.from_numpy(pair[0][None]))
+        adds.copy_(torch.from_numpy(pair[1][None]))
+        for t in (pipe.depth, pipe.mask, pipe.rgba_out, bpipe.depth, blocks_t):
+            t.zero_()
+        g.replay()
+        torch.cuda.synchronize()
+        host = ctx.depth_dense(pair[0], pair[1], P36, rings, flags)
+        want = orc.invert_depth(orc.depth_dense(pair[0], pair[1], P36, rings, resample=orc.RESAMPLE_U8))
+        assert np.array_equal(pipe.depth[0].cpu().numpy(), want)
+        assert np.array_equal(pipe.depth[0].cpu().numpy(), host["depth"])
+        assert np.array_equal(pipe.mask[0].cpu().numpy(), host["mask"])
+        assert np.array_equal(pipe.rgba_out[0].cpu().numpy(), host["rgba"])
+        assert int(bpipe.n_blocks[0]) == len(blocks) and blocks_t.cpu().numpy().tobytes() == blocks.tobytes()
+        assert int(bpipe.status[0]) == 0
+        assert np.array_equal(bpipe.depth[0].cpu().numpy(), want_blocks)
+
+
 def test_row_bands_equal_whole_image(ctx, orc):
     """config 5's decomposition on one GPU: search + finish per row band (with halos) == the whole image"""
     from stepth_b200 import device
